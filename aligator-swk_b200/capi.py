@@ -1,0 +1,311 @@
+"""ctypes binding of the C ABI (include/garb200.h -> libgarb200.so).
+
+There is no CPU fallback: if the shared library is missing, or no CUDA device is present,
+the calls raise.  ``lib()`` itself only needs the .so (so symbol checks run on CPU boxes).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgarb200.so")
+_LIB = None
+
+OK, ERR_INVALID, ERR_CUDA, ERR_NUMERIC, ERR_STATE = 0, 1, 2, 3, 4
+STORE_ALL_VALUES = 1
+
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int)
+
+
+class GarB200Error(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"garb200 error {code}: {msg}")
+        self.code = code
+
+
+class Config(C.Structure):
+    _fields_ = [("nx", C.c_int), ("nu", C.c_int), ("nc", C.c_int), ("nth", C.c_int),
+                ("horizon", C.c_int), ("nc0", C.c_int), ("batch", C.c_int),
+                ("num_legs", C.c_int), ("device", C.c_int), ("flags", C.c_int),
+                ("nu_t", _ip), ("nc_t", _ip), ("nu_term", C.c_int), ("nc_term", C.c_int)]
+
+
+class KnotView(C.Structure):
+    _fields_ = [("nu", C.c_int), ("nc", C.c_int)] + [
+        (n, _dp) for n in ("Q", "S", "R", "q", "r", "A", "B", "E", "f", "C", "D", "d",
+                           "Gth", "Gx", "Gu", "gamma")]
+
+
+# every symbol include/garb200.h declares (tests/test_capi_symbols.py checks the export list)
+SYMBOLS = [
+    "garb200_create", "garb200_destroy", "garb200_last_error", "garb200_version",
+    "garb200_set_stream", "garb200_synchronize", "garb200_get_layouts", "garb200_layouts",
+    "garb200_upload_packed", "garb200_stage_knot", "garb200_stage_initial", "garb200_commit",
+    "garb200_device_problem", "garb200_generate", "garb200_download_packed",
+    "garb200_backward", "garb200_forward", "garb200_forward_device",
+    "garb200_device_trajectory", "garb200_get_gains", "garb200_download_gains",
+    "garb200_device_gains", "garb200_get_value", "garb200_get_initial", "garb200_get_flags",
+    "garb200_get_refinement_steps", "garb200_collapse_feedback", "garb200_cycle_append",
+    "garb200_kkt_error", "garb200_upload_trajectory", "garb200_kernel_launches", "garb200_last_timings",
+    "garb200_fp64_peak",
+]
+
+
+def lib():
+    """Load libgarb200.so (built by ``__graft_entry__.build()``); raise loudly if absent."""
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise GarB200Error(ERR_CUDA, f"{LIB_PATH} not built: run __graft_entry__.build(); "
+                                         "there is no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        L.garb200_last_error.restype = C.c_char_p
+        L.garb200_version.restype = C.c_char_p
+        L.garb200_kernel_launches.restype = C.c_int64
+        L.garb200_destroy.restype = None
+        L.garb200_layouts.restype = None
+        L.garb200_backward.argtypes = [C.c_void_p, C.c_double, C.c_double]
+        L.garb200_kkt_error.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_void_p, C.c_void_p]
+        L.garb200_generate.argtypes = [C.c_void_p, C.c_uint64, C.c_int]
+        for name in ("garb200_forward", "garb200_forward_device"):
+            getattr(L, name).argtypes = [C.c_void_p] * 6 if name == "garb200_forward_device" else [C.c_void_p] * 6
+        L.garb200_upload_packed.argtypes = [C.c_void_p] * 4
+        L.garb200_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+        L.garb200_synchronize.argtypes = [C.c_void_p]
+        L.garb200_destroy.argtypes = [C.c_void_p]
+        L.garb200_get_gains.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.garb200_download_gains.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.garb200_get_value.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.garb200_get_initial.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 4
+        L.garb200_get_flags.argtypes = [C.c_void_p, C.c_void_p]
+        L.garb200_get_refinement_steps.argtypes = [C.c_void_p, C.c_void_p]
+        L.garb200_collapse_feedback.argtypes = [C.c_void_p]
+        L.garb200_cycle_append.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+        L.garb200_download_packed.argtypes = [C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 3
+        L.garb200_device_problem.argtypes = [C.c_void_p] * 4
+        L.garb200_device_trajectory.argtypes = [C.c_void_p] * 5
+        L.garb200_device_gains.argtypes = [C.c_void_p, C.c_void_p]
+        L.garb200_stage_knot.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.garb200_stage_initial.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        L.garb200_commit.argtypes = [C.c_void_p]
+        L.garb200_kernel_launches.argtypes = [C.c_void_p]
+        L.garb200_last_timings.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.garb200_fp64_peak.argtypes = [C.c_int, C.c_int, C.c_void_p]
+        L.garb200_create.argtypes = [C.c_void_p, C.c_void_p]
+        L.garb200_upload_trajectory.argtypes = [C.c_void_p] * 5
+        L.garb200_get_layouts.argtypes = [C.c_void_p] * 4
+        _LIB = L
+    return _LIB
+
+
+def check(rc):
+    if rc != OK:
+        raise GarB200Error(rc, lib().garb200_last_error().decode())
+
+
+def _ptr(a):
+    """numpy array / int device address / None -> c_void_p"""
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        assert a.flags["C_CONTIGUOUS"], "array must be C-contiguous"
+        return a.ctypes.data_as(C.c_void_p)
+    return C.c_void_p(int(a))
+
+
+def c_layouts(nx, nu, nc, nth):
+    k = np.zeros(17, np.int32); g = np.zeros(5, np.int32); v = np.zeros(8, np.int32)
+    lib().garb200_layouts(nx, nu, nc, nth, k.ctypes.data_as(_ip), g.ctypes.data_as(_ip),
+                          v.ctypes.data_as(_ip))
+    return k, g, v
+
+
+def fp64_peak(device=0, kind=0) -> float:
+    out = C.c_double(0.0)
+    check(lib().garb200_fp64_peak(device, kind, C.byref(out)))
+    return out.value
+
+
+class Solver:
+    """Thin RAII wrapper over a ``garb200_solver*`` handle."""
+
+    def __init__(self, nx, nu, nc=0, nth=0, horizon=1, nc0=None, batch=1, num_legs=0, device=0,
+                 flags=0, nu_t=None, nc_t=None, nu_term=0, nc_term=0):
+        self._h = None
+        cfg = Config()
+        cfg.nx, cfg.nu, cfg.nc, cfg.nth = nx, nu, nc, nth
+        cfg.horizon, cfg.nc0, cfg.batch = horizon, (nx if nc0 is None else nc0), batch
+        cfg.num_legs, cfg.device, cfg.flags = num_legs, device, flags
+        self._nu_t = None if nu_t is None else np.ascontiguousarray(nu_t, dtype=np.int32)
+        self._nc_t = None if nc_t is None else np.ascontiguousarray(nc_t, dtype=np.int32)
+        cfg.nu_t = None if self._nu_t is None else self._nu_t.ctypes.data_as(_ip)
+        cfg.nc_t = None if self._nc_t is None else self._nc_t.ctypes.data_as(_ip)
+        cfg.nu_term, cfg.nc_term = nu_term, nc_term
+        h = C.c_void_p()
+        check(lib().garb200_create(C.byref(cfg), C.byref(h)))
+        self._h = h
+        self.cfg = cfg
+        T = horizon
+        self.nu_t = (np.array([nu] * T + [nu_term], np.int32) if nu_t is None else self._nu_t)
+        self.nc_t = (np.array([nc] * T + [nc_term], np.int32) if nc_t is None else self._nc_t)
+        self.nx, self.nu, self.nc, self.nth = nx, nu, nc, nth
+        self.horizon, self.nc0, self.batch, self.num_legs = T, cfg.nc0, batch, num_legs
+        self.nth_eff = nx if num_legs >= 2 else nth
+
+    @classmethod
+    def for_problems(cls, pp, **kw):
+        L = pp.layout
+        return cls(L.nx, L.nu, L.nc, L.nth, pp.horizon, pp.nc0, pp.batch,
+                   nu_t=pp.nu_t, nc_t=pp.nc_t, **kw)
+
+    def close(self):
+        if self._h is not None:
+            lib().garb200_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- plumbing
+    def set_stream(self, stream_ptr):
+        check(lib().garb200_set_stream(self._h, C.c_void_p(int(stream_ptr))))
+
+    def synchronize(self):
+        check(lib().garb200_synchronize(self._h))
+
+    # ---- problem data
+    def upload_packed(self, knots, G0, g0):
+        check(lib().garb200_upload_packed(self._h, _ptr(knots), _ptr(G0), _ptr(g0)))
+
+    def upload(self, pp):
+        self._keep = (np.ascontiguousarray(pp.knots), np.ascontiguousarray(pp.G0),
+                      np.ascontiguousarray(pp.g0))
+        self.upload_packed(*self._keep)
+        self.synchronize_stream_only()
+
+    def synchronize_stream_only(self):
+        rc = lib().garb200_synchronize(self._h)
+        if rc not in (OK, ERR_NUMERIC):
+            check(rc)
+
+    def generate(self, seed=42, dist=0):
+        check(lib().garb200_generate(self._h, C.c_uint64(seed), int(dist)))
+
+    def download_packed(self, first, count):
+        from .layout import KnotLayout
+        L = KnotLayout(self.nx, self.nu, self.nc, self.nth)
+        knots = np.zeros((count, self.horizon + 1, L.stride))
+        G0 = np.zeros((count, self.nc0 * self.nx)); g0 = np.zeros((count, self.nc0))
+        check(lib().garb200_download_packed(self._h, first, count, _ptr(knots), _ptr(G0), _ptr(g0)))
+        return knots, G0, g0
+
+    def device_problem(self):
+        a, b, c = C.c_void_p(), C.c_void_p(), C.c_void_p()
+        check(lib().garb200_device_problem(self._h, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+    def stage_knot(self, problem, t, view: KnotView):
+        check(lib().garb200_stage_knot(self._h, problem, t, C.byref(view)))
+
+    def stage_initial(self, problem, G0, g0):
+        check(lib().garb200_stage_initial(self._h, problem, _ptr(G0), _ptr(g0)))
+
+    def commit(self):
+        check(lib().garb200_commit(self._h))
+
+    # ---- hot path
+    def backward(self, mudyn, mueq):
+        check(lib().garb200_backward(self._h, float(mudyn), float(mueq)))
+
+    def traj_arrays(self):
+        B, T = self.batch, self.horizon
+        return (np.zeros((B, T + 1, self.nx)), np.zeros((B, T + 1, self.nu)),
+                np.zeros((B, T + 1, self.nc)), np.zeros((B, self.nc0 + T * self.nx)))
+
+    def forward(self, theta=None, out=None):
+        xs, us, vs, lb = out if out is not None else self.traj_arrays()
+        th = None if theta is None else np.ascontiguousarray(
+            np.broadcast_to(np.asarray(theta, dtype=np.float64), (self.batch, self.nth)))
+        check(lib().garb200_forward(self._h, _ptr(th), _ptr(xs), _ptr(us), _ptr(vs), _ptr(lb)))
+        return xs, us, vs, lb
+
+    def forward_device(self, d_theta=None, d_xs=None, d_us=None, d_vs=None, d_lbdas=None):
+        check(lib().garb200_forward_device(self._h, _ptr(d_theta), _ptr(d_xs), _ptr(d_us),
+                                           _ptr(d_vs), _ptr(d_lbdas)))
+
+    def device_trajectory(self):
+        p = [C.c_void_p() for _ in range(4)]
+        check(lib().garb200_device_trajectory(self._h, *[C.byref(q) for q in p]))
+        return tuple(q.value for q in p)
+
+    # ---- readers
+    def gain_stride(self):
+        from .layout import GainLayout
+        return GainLayout(self.nx, self.nu, self.nc, self.nth_eff).stride
+
+    def download_gains(self, first=0, count=None):
+        count = self.batch - first if count is None else count
+        g = np.zeros((count, self.horizon + 1, self.gain_stride()))
+        check(lib().garb200_download_gains(self._h, first, count, _ptr(g)))
+        return g
+
+    def get_gains(self, problem, t):
+        nr = int(self.nu_t[t] + self.nc_t[t] + 2 * self.nx)
+        ff = np.zeros(nr); fb = np.zeros((nr, self.nx)); fth = np.zeros((nr, self.nth_eff))
+        check(lib().garb200_get_gains(self._h, problem, t, _ptr(ff), _ptr(fb), _ptr(fth)))
+        return ff, fb, fth
+
+    def get_value(self, problem, t):
+        from .layout import ValueLayout
+        V = ValueLayout(self.nx, self.nth_eff)
+        rec = np.zeros(V.stride)
+        check(lib().garb200_get_value(self._h, problem, t, _ptr(rec)))
+        return V.unpack(rec)
+
+    def get_initial(self, problem):
+        s0, h = self.nx + self.nc0, self.nth
+        ff = np.zeros(s0); fth = np.zeros((s0, h)); g = np.zeros(h); H = np.zeros((h, h))
+        check(lib().garb200_get_initial(self._h, problem, _ptr(ff), _ptr(fth), _ptr(g), _ptr(H)))
+        return ff, fth, g, H.T.copy()
+
+    def get_flags(self):
+        f = np.zeros(self.batch, np.int32)
+        check(lib().garb200_get_flags(self._h, _ptr(f)))
+        return f
+
+    def get_refinement_steps(self):
+        f = np.zeros(self.batch, np.int32)
+        check(lib().garb200_get_refinement_steps(self._h, _ptr(f)))
+        return f
+
+    def collapse_feedback(self):
+        check(lib().garb200_collapse_feedback(self._h))
+
+    def cycle_append(self, views, shared=False):
+        arr = (KnotView * len(views))(*views)
+        check(lib().garb200_cycle_append(self._h, arr, int(shared)))
+
+    def kkt_error(self, mudyn, mueq, theta=None):
+        out = np.zeros((self.batch, 3))
+        th = None if theta is None else np.ascontiguousarray(
+            np.broadcast_to(np.asarray(theta, dtype=np.float64), (self.batch, self.nth)))
+        check(lib().garb200_kkt_error(self._h, float(mudyn), float(mueq), _ptr(th), _ptr(out)))
+        return out
+
+    def upload_trajectory(self, xs, us, vs, lbdas):
+        check(lib().garb200_upload_trajectory(self._h, _ptr(xs), _ptr(us), _ptr(vs), _ptr(lbdas)))
+
+    def kernel_launches(self) -> int:
+        return int(lib().garb200_kernel_launches(self._h))
+
+    def last_timings(self):
+        a, b = C.c_float(0), C.c_float(0)
+        check(lib().garb200_last_timings(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value

@@ -1,0 +1,601 @@
+// capi.cu — the C ABI of include/garb200.h: host-side solver object over the CUDA kernels.
+// No CPU fallback lives here: every compute entry point launches sm_100a kernels or
+// fails with GARB200_ERR_CUDA.
+#include <cuda_runtime.h>
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "kernels.cuh"
+
+namespace garb200 { size_t backward_smem_bytes(const DevParams &p); }
+using namespace garb200;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string &msg) { g_err = msg; return code; }
+#define CK(call)                                                                              \
+  do {                                                                                        \
+    cudaError_t e_ = (call);                                                                  \
+    if (e_ != cudaSuccess)                                                                    \
+      return fail(GARB200_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));      \
+  } while (0)
+
+struct garb200_solver {
+  garb200_config cfg{};
+  DevParams p{};
+  std::vector<int> nu_t, nc_t;
+  std::vector<void *> dev_allocs;
+  cudaStream_t stream = nullptr;
+  double *h_stage = nullptr;     // pinned staging of the packed problem (small batches only)
+  double *h_G0 = nullptr, *h_g0 = nullptr;
+  double *h_scratch = nullptr;   // pinned: one gains/value record, flags, kkt out ...
+  size_t scratch_doubles = 0;
+  double *h_cycle = nullptr;     // pinned [batch][kstride] for cycleAppend
+  double *d_kkt_out = nullptr;
+  int64_t launches = 0;
+  bool has_problem = false, did_backward = false, did_forward = false;
+  cudaEvent_t ev[4]{};
+  size_t knots_doubles = 0;
+  int nblk = 0;                  // blocks of the condensed system (2 * legs)
+  size_t csys_len = 0;           // nc0 + (nblk-1) nx
+};
+
+static const size_t kMaxPinnedStage = (size_t)1 << 30;  // 1 GiB
+
+template <class T> static int dmalloc(garb200_solver *s, T **ptr, size_t count) {
+  *ptr = nullptr;
+  if (count == 0) count = 1;
+  void *q = nullptr;
+  CK(cudaMalloc(&q, count * sizeof(T)));
+  s->dev_allocs.push_back(q);
+  *ptr = static_cast<T *>(q);
+  return GARB200_OK;
+}
+#define TRY(x) do { int rc_ = (x); if (rc_ != GARB200_OK) return rc_; } while (0)
+
+extern "C" {
+
+const char *garb200_last_error(void) { return g_err.c_str(); }
+const char *garb200_version(void) { return "garb200 0.1 (sm_100a)"; }
+
+void garb200_layouts(int nx, int nu, int nc, int nth, int *knot, int *gain, int *value) {
+  const garb200_knot_layout L = garb200_make_knot_layout(nx, nu, nc, nth);
+  const int k[17] = {L.Q, L.S, L.R, L.q, L.r, L.A, L.B, L.E, L.f, L.C, L.D, L.d,
+                     L.Gth, L.Gx, L.Gu, L.gamma, L.stride};
+  for (int i = 0; i < 17; i++) knot[i] = k[i];
+  const garb200_gain_layout G = garb200_make_gain_layout(nx, nu, nc, nth);
+  gain[0] = G.nrows; gain[1] = G.ff; gain[2] = G.fb; gain[3] = G.fth; gain[4] = G.stride;
+  const garb200_value_layout V = garb200_make_value_layout(nx, nth);
+  const int v[8] = {V.Pmat, V.pvec, V.Vxx, V.vx, V.Vxt, V.Vtt, V.vt, V.stride};
+  for (int i = 0; i < 8; i++) value[i] = v[i];
+}
+
+void garb200_destroy(garb200_solver *s) {
+  if (!s) return;
+  cudaSetDevice(s->cfg.device);
+  if (s->stream) cudaStreamSynchronize(s->stream); else cudaDeviceSynchronize();
+  for (void *q : s->dev_allocs) cudaFree(q);
+  if (s->h_stage) cudaFreeHost(s->h_stage);
+  if (s->h_G0) cudaFreeHost(s->h_G0);
+  if (s->h_g0) cudaFreeHost(s->h_g0);
+  if (s->h_scratch) cudaFreeHost(s->h_scratch);
+  if (s->h_cycle) cudaFreeHost(s->h_cycle);
+  for (auto &e : s->ev) if (e) cudaEventDestroy(e);
+  delete s;
+}
+
+int garb200_create(const garb200_config *cfg, garb200_solver **out) {
+  if (!cfg || !out) return fail(GARB200_ERR_INVALID, "null argument");
+  *out = nullptr;
+  const garb200_config &c = *cfg;
+  if (c.nx < 1 || c.nu < 0 || c.nc < 0 || c.nth < 0 || c.horizon < 0 || c.batch < 1 || c.nc0 < 0)
+    return fail(GARB200_ERR_INVALID, "negative or zero dimension");
+  if (c.nc0 > c.nx) return fail(GARB200_ERR_INVALID, "nc0 > nx is not supported");
+  const bool legs = c.num_legs >= 2;
+  if (legs && c.nth != 0)   // the reference overwrites the parameterization (parallel-solver.hxx:51-61)
+    return fail(GARB200_ERR_INVALID, "parallel-in-time mode requires nth == 0");
+  if (legs && c.num_legs > c.horizon + 1)
+    return fail(GARB200_ERR_INVALID, "more legs than knots");
+  int ndev = 0;
+  CK(cudaGetDeviceCount(&ndev));
+  if (c.device < 0 || c.device >= ndev) return fail(GARB200_ERR_CUDA, "no such CUDA device");
+  CK(cudaSetDevice(c.device));
+
+  garb200_solver *s = new garb200_solver();
+  s->cfg = c;
+  const int T = c.horizon;
+  s->nu_t.resize(T + 1); s->nc_t.resize(T + 1);
+  for (int t = 0; t <= T; t++) {
+    s->nu_t[t] = c.nu_t ? c.nu_t[t] : (t < T ? c.nu : c.nu_term);
+    s->nc_t[t] = c.nc_t ? c.nc_t[t] : (t < T ? c.nc : c.nc_term);
+    if (s->nu_t[t] < 0 || s->nu_t[t] > c.nu || s->nc_t[t] < 0 || s->nc_t[t] > c.nc) {
+      delete s;
+      return fail(GARB200_ERR_INVALID, "per-knot nu/nc outside [0, max]");
+    }
+  }
+  s->cfg.nu_t = nullptr; s->cfg.nc_t = nullptr;
+  DevParams &p = s->p;
+  p.nx = c.nx; p.nu = c.nu; p.nc = c.nc; p.nth = c.nth;
+  p.hleg = legs ? c.nx : 0;
+  p.T = T; p.nc0 = c.nc0; p.batch = c.batch; p.num_legs = legs ? c.num_legs : 0;
+  p.shift = 0;
+  p.store_all_values = (c.flags & GARB200_STORE_ALL_VALUES) ? 1 : 0;
+  p.nslots = p.store_all_values ? T + 1 : (legs ? c.num_legs : 1);
+  const int nth_eff = legs ? c.nx : c.nth;
+  p.KL = garb200_make_knot_layout(c.nx, c.nu, c.nc, c.nth);
+  p.GL = garb200_make_gain_layout(c.nx, c.nu, c.nc, nth_eff);
+  p.VL = garb200_make_value_layout(c.nx, nth_eff);
+  p.mudyn = p.mueq = 0.0;
+  if (backward_smem_bytes(p) > 227u * 1024u) {
+    char buf[256];
+    snprintf(buf, sizeof buf, "dimensions need %zu bytes of shared memory per CTA (> 227 KB): "
+             "nx=%d nu=%d nc=%d nth=%d not supported by this kernel generation",
+             backward_smem_bytes(p), c.nx, c.nu, c.nc, nth_eff);
+    delete s;
+    return fail(GARB200_ERR_INVALID, buf);
+  }
+  auto bail = [&](int rc) { garb200_destroy(s); return rc; };
+#define TRYB(x) do { int rc_ = (x); if (rc_ != GARB200_OK) return bail(rc_); } while (0)
+  const size_t B = c.batch, n = c.nx;
+  s->knots_doubles = B * (T + 1) * p.KL.stride;
+  int *d_nu = nullptr, *d_nc = nullptr;
+  TRYB(dmalloc(s, &d_nu, T + 1)); TRYB(dmalloc(s, &d_nc, T + 1));
+  if (cudaMemcpy(d_nu, s->nu_t.data(), (T + 1) * sizeof(int), cudaMemcpyHostToDevice) != cudaSuccess ||
+      cudaMemcpy(d_nc, s->nc_t.data(), (T + 1) * sizeof(int), cudaMemcpyHostToDevice) != cudaSuccess)
+    return bail(fail(GARB200_ERR_CUDA, "memcpy of per-knot dims failed"));
+  p.nu_t = d_nu; p.nc_t = d_nc;
+  TRYB(dmalloc(s, &p.knots, s->knots_doubles));
+  TRYB(dmalloc(s, &p.G0, B * c.nc0 * n));
+  TRYB(dmalloc(s, &p.g0, B * c.nc0));
+  TRYB(dmalloc(s, &p.gains, B * (T + 1) * p.GL.stride));
+  TRYB(dmalloc(s, &p.values, B * p.nslots * p.VL.stride));
+  TRYB(dmalloc(s, &p.kkt0_ff, B * (n + c.nc0)));
+  TRYB(dmalloc(s, &p.kkt0_fth, B * (n + c.nc0) * c.nth));
+  TRYB(dmalloc(s, &p.thGrad, B * c.nth));
+  TRYB(dmalloc(s, &p.thHess, B * c.nth * c.nth));
+  TRYB(dmalloc(s, &p.xs, B * (T + 1) * n));
+  TRYB(dmalloc(s, &p.us, B * (T + 1) * c.nu));
+  TRYB(dmalloc(s, &p.vs, B * (T + 1) * c.nc));
+  TRYB(dmalloc(s, &p.lbdas, B * (c.nc0 + (size_t)T * n)));
+  TRYB(dmalloc(s, &p.theta, B * c.nth));
+  TRYB(dmalloc(s, &p.flags, B));
+  TRYB(dmalloc(s, &p.refine_steps, B));
+  TRYB(dmalloc(s, &s->d_kkt_out, B * 3));
+  cudaMemset(p.flags, 0, B * sizeof(int32_t));
+  cudaMemset(p.refine_steps, 0, B * sizeof(int32_t));
+  cudaMemset(p.values, 0, B * p.nslots * p.VL.stride * sizeof(double));
+  cudaMemset(p.gains, 0, B * (T + 1) * p.GL.stride * sizeof(double));
+  if (legs) {
+    s->nblk = 2 * c.num_legs;
+    s->csys_len = c.nc0 + (size_t)(s->nblk - 1) * n;
+    const size_t nb = s->nblk, bb = n * n;
+    TRYB(dmalloc(s, &p.cdiag, B * nb * bb));
+    TRYB(dmalloc(s, &p.csuper, B * nb * bb));
+    TRYB(dmalloc(s, &p.csub, B * nb * bb));
+    TRYB(dmalloc(s, &p.cdiagF, B * nb * bb));
+    TRYB(dmalloc(s, &p.csubF, B * nb * bb));
+    TRYB(dmalloc(s, &p.csubd, B * nb * n));
+    TRYB(dmalloc(s, &p.cpiv, B * nb * n));
+    TRYB(dmalloc(s, &p.crhs, B * s->csys_len));
+    TRYB(dmalloc(s, &p.csol, B * s->csys_len));
+    TRYB(dmalloc(s, &p.cerr, B * s->csys_len));
+  }
+  // pinned host buffers
+  if (s->knots_doubles * sizeof(double) <= kMaxPinnedStage) {
+    if (cudaMallocHost(&s->h_stage, std::max<size_t>(s->knots_doubles, 1) * sizeof(double)) != cudaSuccess ||
+        cudaMallocHost(&s->h_G0, std::max<size_t>(B * c.nc0 * n, 1) * sizeof(double)) != cudaSuccess ||
+        cudaMallocHost(&s->h_g0, std::max<size_t>(B * c.nc0, 1) * sizeof(double)) != cudaSuccess)
+      return bail(fail(GARB200_ERR_CUDA, "cudaMallocHost (problem staging) failed"));
+    memset(s->h_stage, 0, s->knots_doubles * sizeof(double));
+    memset(s->h_G0, 0, B * c.nc0 * n * sizeof(double));
+    memset(s->h_g0, 0, B * c.nc0 * sizeof(double));
+  }
+  s->scratch_doubles = std::max<size_t>({(size_t)p.GL.stride, (size_t)p.VL.stride, 3 * B, B,
+                                         (size_t)(n + c.nc0) * (1 + c.nth) + c.nth * (1 + c.nth)}) + 16;
+  if (cudaMallocHost(&s->h_scratch, s->scratch_doubles * sizeof(double)) != cudaSuccess)
+    return bail(fail(GARB200_ERR_CUDA, "cudaMallocHost (scratch) failed"));
+  if (B * p.KL.stride * sizeof(double) <= kMaxPinnedStage / 4)
+    if (cudaMallocHost(&s->h_cycle, B * p.KL.stride * sizeof(double)) != cudaSuccess)
+      return bail(fail(GARB200_ERR_CUDA, "cudaMallocHost (cycle) failed"));
+  for (auto &e : s->ev)
+    if (cudaEventCreate(&e) != cudaSuccess) return bail(fail(GARB200_ERR_CUDA, "cudaEventCreate failed"));
+#undef TRYB
+  *out = s;
+  return GARB200_OK;
+}
+
+int garb200_set_stream(garb200_solver *s, void *cuda_stream) {
+  if (!s) return fail(GARB200_ERR_INVALID, "null solver");
+  s->stream = static_cast<cudaStream_t>(cuda_stream);
+  return GARB200_OK;
+}
+
+static int check_flags(garb200_solver *s) {
+  // caller has synchronised the stream
+  const size_t B = s->cfg.batch;
+  int32_t *hf = reinterpret_cast<int32_t *>(s->h_scratch);
+  CK(cudaMemcpyAsync(hf, s->p.flags, B * sizeof(int32_t), cudaMemcpyDeviceToHost, s->stream));
+  CK(cudaStreamSynchronize(s->stream));
+  int bad = 0;
+  for (size_t i = 0; i < B; i++) bad += hf[i] != 0;
+  if (bad) {
+    char buf[128];
+    snprintf(buf, sizeof buf, "%d of %zu problems raised a numerical flag (garb200_get_flags)", bad, B);
+    return fail(GARB200_ERR_NUMERIC, buf);
+  }
+  return GARB200_OK;
+}
+
+int garb200_synchronize(garb200_solver *s) {
+  if (!s) return fail(GARB200_ERR_INVALID, "null solver");
+  CK(cudaSetDevice(s->cfg.device));
+  CK(cudaStreamSynchronize(s->stream));
+  return s->did_backward ? check_flags(s) : GARB200_OK;
+}
+
+int garb200_get_layouts(const garb200_solver *s, garb200_knot_layout *knot,
+                        garb200_gain_layout *gain, garb200_value_layout *value) {
+  if (!s) return fail(GARB200_ERR_INVALID, "null solver");
+  if (knot) *knot = s->p.KL;
+  if (gain) *gain = s->p.GL;
+  if (value) *value = s->p.VL;
+  return GARB200_OK;
+}
+
+// ---- problem data ----------------------------------------------------------------------
+int garb200_upload_packed(garb200_solver *s, const double *knots, const double *G0,
+                          const double *g0) {
+  if (!s || !knots) return fail(GARB200_ERR_INVALID, "null argument");
+  CK(cudaSetDevice(s->cfg.device));
+  const DevParams &p = s->p;
+  const size_t B = p.batch, n = p.nx;
+  if (p.shift != 0) return fail(GARB200_ERR_STATE, "upload_packed after cycle_append: re-create the solver");
+  CK(cudaMemcpyAsync(p.knots, knots, s->knots_doubles * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  if (G0) CK(cudaMemcpyAsync(p.G0, G0, B * p.nc0 * n * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  if (g0) CK(cudaMemcpyAsync(p.g0, g0, B * p.nc0 * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  s->has_problem = true;
+  return GARB200_OK;
+}
+
+static void pack_block(double *dst, const double *src, int count) {
+  if (count <= 0) return;
+  if (src) memcpy(dst, src, (size_t)count * sizeof(double));
+  else memset(dst, 0, (size_t)count * sizeof(double));
+}
+
+static void pack_knot(const garb200_knot_layout &L, const garb200_knot_view &k, double *rec) {
+  const int n = L.nx, m = k.nu, c = k.nc, h = L.nth;
+  pack_block(rec + L.Q, k.Q, n * n); pack_block(rec + L.S, k.S, n * m); pack_block(rec + L.R, k.R, m * m);
+  pack_block(rec + L.q, k.q, n);     pack_block(rec + L.r, k.r, m);
+  pack_block(rec + L.A, k.A, n * n); pack_block(rec + L.B, k.B, n * m); pack_block(rec + L.E, k.E, n * n);
+  pack_block(rec + L.f, k.f, n);
+  pack_block(rec + L.C, k.C, c * n); pack_block(rec + L.D, k.D, c * m); pack_block(rec + L.d, k.d, c);
+  pack_block(rec + L.Gth, k.Gth, h * h); pack_block(rec + L.Gx, k.Gx, n * h);
+  pack_block(rec + L.Gu, k.Gu, m * h);   pack_block(rec + L.gamma, k.gamma, h);
+}
+
+int garb200_stage_knot(garb200_solver *s, int problem, int t, const garb200_knot_view *k) {
+  if (!s || !k) return fail(GARB200_ERR_INVALID, "null argument");
+  const DevParams &p = s->p;
+  if (!s->h_stage) return fail(GARB200_ERR_STATE, "batch too large for pinned staging: use garb200_upload_packed");
+  if (problem < 0 || problem >= p.batch || t < 0 || t > p.T) return fail(GARB200_ERR_INVALID, "index out of range");
+  if (k->nu != s->nu_t[t] || k->nc != s->nc_t[t]) return fail(GARB200_ERR_INVALID, "knot dims differ from the solver's");
+  pack_knot(p.KL, *k, s->h_stage + ((size_t)problem * (p.T + 1) + phys_t(p, t)) * p.KL.stride);
+  return GARB200_OK;
+}
+
+int garb200_stage_initial(garb200_solver *s, int problem, const double *G0, const double *g0) {
+  if (!s) return fail(GARB200_ERR_INVALID, "null solver");
+  const DevParams &p = s->p;
+  if (!s->h_stage) return fail(GARB200_ERR_STATE, "batch too large for pinned staging");
+  if (problem < 0 || problem >= p.batch) return fail(GARB200_ERR_INVALID, "index out of range");
+  pack_block(s->h_G0 + (size_t)problem * p.nc0 * p.nx, G0, p.nc0 * p.nx);
+  pack_block(s->h_g0 + (size_t)problem * p.nc0, g0, p.nc0);
+  return GARB200_OK;
+}
+
+int garb200_commit(garb200_solver *s) {
+  if (!s) return fail(GARB200_ERR_INVALID, "null solver");
+  if (!s->h_stage) return fail(GARB200_ERR_STATE, "batch too large for pinned staging");
+  CK(cudaSetDevice(s->cfg.device));
+  const DevParams &p = s->p;
+  const size_t B = p.batch, n = p.nx;
+  CK(cudaMemcpyAsync(p.knots, s->h_stage, s->knots_doubles * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  CK(cudaMemcpyAsync(p.G0, s->h_G0, B * p.nc0 * n * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  CK(cudaMemcpyAsync(p.g0, s->h_g0, B * p.nc0 * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  s->has_problem = true;
+  return GARB200_OK;
+}
+
+int garb200_device_problem(garb200_solver *s, double **d_knots, double **d_G0, double **d_g0) {
+  if (!s) return fail(GARB200_ERR_INVALID, "null solver");
+  if (d_knots) *d_knots = s->p.knots;
+  if (d_G0) *d_G0 = s->p.G0;
+  if (d_g0) *d_g0 = s->p.g0;
+  s->has_problem = true;  // the caller fills it on device
+  return GARB200_OK;
+}
+
+int garb200_generate(garb200_solver *s, uint64_t seed, int dist) {
+  if (!s) return fail(GARB200_ERR_INVALID, "null solver");
+  CK(cudaSetDevice(s->cfg.device));
+  const int rc = launch_generate(s->p, seed, dist, s->stream);
+  if (rc < 0) return fail(rc == -1 ? GARB200_ERR_INVALID : GARB200_ERR_CUDA, "generate kernel launch failed");
+  s->launches += rc;
+  s->has_problem = true;
+  return GARB200_OK;
+}
+
+int garb200_download_packed(garb200_solver *s, int first, int count, double *knots, double *G0,
+                            double *g0) {
+  if (!s) return fail(GARB200_ERR_INVALID, "null solver");
+  const DevParams &p = s->p;
+  if (first < 0 || count < 0 || first + count > p.batch) return fail(GARB200_ERR_INVALID, "range");
+  if (p.shift != 0) return fail(GARB200_ERR_STATE, "download_packed after cycle_append is not supported");
+  CK(cudaSetDevice(s->cfg.device));
+  const size_t ps = (size_t)(p.T + 1) * p.KL.stride, n = p.nx;
+  if (knots) CK(cudaMemcpyAsync(knots, p.knots + first * ps, count * ps * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  if (G0) CK(cudaMemcpyAsync(G0, p.G0 + (size_t)first * p.nc0 * n, (size_t)count * p.nc0 * n * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  if (g0) CK(cudaMemcpyAsync(g0, p.g0 + (size_t)first * p.nc0, (size_t)count * p.nc0 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  CK(cudaStreamSynchronize(s->stream));
+  return GARB200_OK;
+}
+
+// ---- the hot path ----------------------------------------------------------------------
+int garb200_backward(garb200_solver *s, double mudyn, double mueq) {
+  if (!s) return fail(GARB200_ERR_INVALID, "null solver");
+  if (!s->has_problem) return fail(GARB200_ERR_STATE, "no problem uploaded");
+  CK(cudaSetDevice(s->cfg.device));
+  DevParams &p = s->p;
+  p.mudyn = mudyn; p.mueq = mueq;
+  CK(cudaMemsetAsync(p.flags, 0, (size_t)p.batch * sizeof(int32_t), s->stream));
+  CK(cudaEventRecord(s->ev[0], s->stream));
+  int rc = launch_backward(p, s->stream);
+  if (rc < 0) return fail(rc == -1 ? GARB200_ERR_INVALID : GARB200_ERR_CUDA,
+                          std::string("backward launch failed: ") + cudaGetErrorString(cudaGetLastError()));
+  s->launches += rc;
+  if (p.num_legs >= 2) {
+    rc = launch_condensed(p, s->stream);
+    if (rc < 0) return fail(GARB200_ERR_CUDA, "condensed-system launch failed");
+    s->launches += rc;
+  }
+  CK(cudaEventRecord(s->ev[1], s->stream));
+  s->did_backward = true;
+  s->did_forward = false;
+  return GARB200_OK;
+}
+
+int garb200_forward_device(garb200_solver *s, const double *d_theta, double *d_xs, double *d_us,
+                           double *d_vs, double *d_lbdas) {
+  if (!s) return fail(GARB200_ERR_INVALID, "null solver");
+  if (!s->did_backward) return fail(GARB200_ERR_STATE, "forward before backward");
+  CK(cudaSetDevice(s->cfg.device));
+  const DevParams &p = s->p;
+  CK(cudaEventRecord(s->ev[2], s->stream));
+  const int rc = launch_forward(p, (p.nth > 0 && p.num_legs < 2) ? d_theta : nullptr,
+                                d_xs ? d_xs : p.xs, d_us ? d_us : p.us, d_vs ? d_vs : p.vs,
+                                d_lbdas ? d_lbdas : p.lbdas, s->stream);
+  if (rc < 0) return fail(rc == -1 ? GARB200_ERR_INVALID : GARB200_ERR_CUDA, "forward launch failed");
+  s->launches += rc;
+  CK(cudaEventRecord(s->ev[3], s->stream));
+  s->did_forward = (!d_xs && !d_us && !d_vs && !d_lbdas);
+  return GARB200_OK;
+}
+
+int garb200_forward(garb200_solver *s, const double *theta, double *xs, double *us, double *vs,
+                    double *lbdas) {
+  if (!s) return fail(GARB200_ERR_INVALID, "null solver");
+  if (!s->did_backward) return fail(GARB200_ERR_STATE, "forward before backward");
+  CK(cudaSetDevice(s->cfg.device));
+  const DevParams &p = s->p;
+  const size_t B = p.batch, n = p.nx, T = p.T;
+  const double *d_theta = nullptr;
+  if (theta && p.nth > 0 && p.num_legs < 2) {
+    CK(cudaMemcpyAsync(p.theta, theta, B * p.nth * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+    d_theta = p.theta;
+  }
+  TRY(garb200_forward_device(s, d_theta, nullptr, nullptr, nullptr, nullptr));
+  if (xs) CK(cudaMemcpyAsync(xs, p.xs, B * (T + 1) * n * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  if (us && p.nu) CK(cudaMemcpyAsync(us, p.us, B * (T + 1) * p.nu * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  if (vs && p.nc) CK(cudaMemcpyAsync(vs, p.vs, B * (T + 1) * p.nc * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  if (lbdas) CK(cudaMemcpyAsync(lbdas, p.lbdas, B * (p.nc0 + T * n) * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  CK(cudaStreamSynchronize(s->stream));
+  return check_flags(s);
+}
+
+int garb200_device_trajectory(garb200_solver *s, double **d_xs, double **d_us, double **d_vs,
+                              double **d_lbdas) {
+  if (!s) return fail(GARB200_ERR_INVALID, "null solver");
+  if (d_xs) *d_xs = s->p.xs;
+  if (d_us) *d_us = s->p.us;
+  if (d_vs) *d_vs = s->p.vs;
+  if (d_lbdas) *d_lbdas = s->p.lbdas;
+  return GARB200_OK;
+}
+
+// ---- solver state readers ----------------------------------------------------------------
+static int fetch(garb200_solver *s, double *dst_host, const double *src_dev, size_t count) {
+  CK(cudaMemcpyAsync(dst_host, src_dev, count * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  CK(cudaStreamSynchronize(s->stream));
+  return GARB200_OK;
+}
+
+int garb200_get_gains(garb200_solver *s, int problem, int t, double *ff, double *fb, double *fth) {
+  if (!s) return fail(GARB200_ERR_INVALID, "null solver");
+  const DevParams &p = s->p;
+  if (!s->did_backward) return fail(GARB200_ERR_STATE, "no factorization yet");
+  if (problem < 0 || problem >= p.batch || t < 0 || t > p.T) return fail(GARB200_ERR_INVALID, "index out of range");
+  CK(cudaSetDevice(s->cfg.device));
+  const double *rec = p.gains + ((size_t)problem * (p.T + 1) + phys_t(p, t)) * p.GL.stride;
+  TRY(fetch(s, s->h_scratch, rec, p.GL.stride));
+  const int nr = s->nu_t[t] + s->nc_t[t] + 2 * p.nx;
+  if (ff) memcpy(ff, s->h_scratch + p.GL.ff, nr * sizeof(double));
+  if (fb) memcpy(fb, s->h_scratch + p.GL.fb, (size_t)nr * p.nx * sizeof(double));
+  if (fth && p.GL.nth) memcpy(fth, s->h_scratch + p.GL.fth, (size_t)nr * p.GL.nth * sizeof(double));
+  return GARB200_OK;
+}
+
+int garb200_download_gains(garb200_solver *s, int first, int count, double *gains) {
+  if (!s || !gains) return fail(GARB200_ERR_INVALID, "null argument");
+  const DevParams &p = s->p;
+  if (!s->did_backward) return fail(GARB200_ERR_STATE, "no factorization yet");
+  if (first < 0 || count < 0 || first + count > p.batch) return fail(GARB200_ERR_INVALID, "range");
+  CK(cudaSetDevice(s->cfg.device));
+  const size_t ps = (size_t)(p.T + 1) * p.GL.stride;
+  if (p.shift == 0) return fetch(s, gains, p.gains + first * ps, count * ps);
+  for (int b = first; b < first + count; b++)      // undo the ring offset: logical time order out
+    for (int t = 0; t <= p.T; t++)
+      CK(cudaMemcpyAsync(gains + ((size_t)(b - first) * (p.T + 1) + t) * p.GL.stride,
+                         p.gains + ((size_t)b * (p.T + 1) + phys_t(p, t)) * p.GL.stride,
+                         p.GL.stride * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  CK(cudaStreamSynchronize(s->stream));
+  return GARB200_OK;
+}
+
+int garb200_device_gains(garb200_solver *s, double **d_gains) {
+  if (!s || !d_gains) return fail(GARB200_ERR_INVALID, "null argument");
+  *d_gains = s->p.gains;
+  return GARB200_OK;
+}
+
+int garb200_get_value(garb200_solver *s, int problem, int t, double *value_record) {
+  if (!s || !value_record) return fail(GARB200_ERR_INVALID, "null argument");
+  const DevParams &p = s->p;
+  if (!s->did_backward) return fail(GARB200_ERR_STATE, "no factorization yet");
+  if (problem < 0 || problem >= p.batch || t < 0 || t > p.T) return fail(GARB200_ERR_INVALID, "index out of range");
+  const int slot = value_slot(p, t);
+  if (slot < 0) return fail(GARB200_ERR_STATE, "value function of this knot was not kept: create with GARB200_STORE_ALL_VALUES");
+  CK(cudaSetDevice(s->cfg.device));
+  return fetch(s, value_record, p.values + ((size_t)problem * p.nslots + slot) * p.VL.stride, p.VL.stride);
+}
+
+int garb200_get_initial(garb200_solver *s, int problem, double *kkt0_ff, double *kkt0_fth,
+                        double *thGrad, double *thHess) {
+  if (!s) return fail(GARB200_ERR_INVALID, "null solver");
+  const DevParams &p = s->p;
+  if (!s->did_backward) return fail(GARB200_ERR_STATE, "no factorization yet");
+  if (p.num_legs >= 2) return fail(GARB200_ERR_STATE, "the parallel-in-time solver has no kkt0 (parallel-solver.hpp)");
+  if (problem < 0 || problem >= p.batch) return fail(GARB200_ERR_INVALID, "index out of range");
+  CK(cudaSetDevice(s->cfg.device));
+  const size_t s0 = p.nx + p.nc0, h = p.nth, b = problem;
+  if (kkt0_ff) TRY(fetch(s, kkt0_ff, p.kkt0_ff + b * s0, s0));
+  if (kkt0_fth && h) TRY(fetch(s, kkt0_fth, p.kkt0_fth + b * s0 * h, s0 * h));
+  if (thGrad && h) TRY(fetch(s, thGrad, p.thGrad + b * h, h));
+  if (thHess && h) TRY(fetch(s, thHess, p.thHess + b * h * h, h * h));
+  return GARB200_OK;
+}
+
+int garb200_get_flags(garb200_solver *s, int32_t *flags) {
+  if (!s || !flags) return fail(GARB200_ERR_INVALID, "null argument");
+  CK(cudaSetDevice(s->cfg.device));
+  CK(cudaMemcpyAsync(flags, s->p.flags, (size_t)s->p.batch * sizeof(int32_t), cudaMemcpyDeviceToHost, s->stream));
+  CK(cudaStreamSynchronize(s->stream));
+  return GARB200_OK;
+}
+
+int garb200_get_refinement_steps(garb200_solver *s, int32_t *steps) {
+  if (!s || !steps) return fail(GARB200_ERR_INVALID, "null argument");
+  CK(cudaSetDevice(s->cfg.device));
+  CK(cudaMemcpyAsync(steps, s->p.refine_steps, (size_t)s->p.batch * sizeof(int32_t), cudaMemcpyDeviceToHost, s->stream));
+  CK(cudaStreamSynchronize(s->stream));
+  return GARB200_OK;
+}
+
+int garb200_collapse_feedback(garb200_solver *s) {
+  if (!s) return fail(GARB200_ERR_INVALID, "null solver");
+  if (s->p.num_legs < 2) return GARB200_OK;   // RiccatiSolverBase::collapseFeedback() {} (riccati-base.hpp:29)
+  if (!s->did_backward) return fail(GARB200_ERR_STATE, "no factorization yet");
+  CK(cudaSetDevice(s->cfg.device));
+  const int rc = launch_collapse(s->p, s->stream);
+  if (rc < 0) return fail(GARB200_ERR_CUDA, "collapse launch failed");
+  s->launches += rc;
+  return GARB200_OK;
+}
+
+int garb200_cycle_append(garb200_solver *s, const garb200_knot_view *knots, int shared) {
+  if (!s || !knots) return fail(GARB200_ERR_INVALID, "null argument");
+  DevParams &p = s->p;
+  if (p.T < 1) return fail(GARB200_ERR_INVALID, "cycle_append needs horizon >= 1");
+  if (!s->h_cycle) return fail(GARB200_ERR_STATE, "batch too large for cycle_append staging");
+  CK(cudaSetDevice(s->cfg.device));
+  // the rotating knots must share dims (ring offset instead of the reference's copy-rotate)
+  for (int t = 1; t < p.T; t++)
+    if (s->nu_t[t] != s->nu_t[0] || s->nc_t[t] != s->nc_t[0])
+      return fail(GARB200_ERR_INVALID, "cycle_append needs uniform nu/nc over knots 0..T-1");
+  for (int b = 0; b < p.batch; b++) {
+    const garb200_knot_view &k = shared ? knots[0] : knots[b];
+    if (k.nu != s->nu_t[0] || k.nc != s->nc_t[0]) return fail(GARB200_ERR_INVALID, "knot dims differ from the solver's");
+    pack_knot(p.KL, k, s->h_cycle + (size_t)b * p.KL.stride);
+  }
+  CK(cudaStreamSynchronize(s->stream));         // nothing in flight still reads the old offset
+  p.shift = (p.shift + 1) % p.T;                // rotate_vec_left(datas, 0, 1)  (mpc-util.hpp:17-22)
+  const int slot = phys_t(p, p.T - 1);
+  const size_t pitch_k = (size_t)(p.T + 1) * p.KL.stride * sizeof(double);
+  CK(cudaMemcpy2DAsync(p.knots + (size_t)slot * p.KL.stride, pitch_k, s->h_cycle,
+                       p.KL.stride * sizeof(double), p.KL.stride * sizeof(double), p.batch,
+                       cudaMemcpyHostToDevice, s->stream));
+  // fresh StageFactor at N-1, kkt0 / thGrad / thHess reset (proximal-riccati.hxx:83-87)
+  const size_t pitch_g = (size_t)(p.T + 1) * p.GL.stride * sizeof(double);
+  CK(cudaMemset2DAsync(p.gains + (size_t)slot * p.GL.stride, pitch_g, 0, p.GL.stride * sizeof(double), p.batch, s->stream));
+  const size_t B = p.batch;
+  CK(cudaMemsetAsync(p.kkt0_ff, 0, std::max<size_t>(B * (p.nx + p.nc0), 1) * sizeof(double), s->stream));
+  CK(cudaMemsetAsync(p.thGrad, 0, std::max<size_t>(B * p.nth, 1) * sizeof(double), s->stream));
+  CK(cudaMemsetAsync(p.thHess, 0, std::max<size_t>(B * p.nth * p.nth, 1) * sizeof(double), s->stream));
+  s->did_forward = false;
+  return GARB200_OK;
+}
+
+// ---- metric -------------------------------------------------------------------------------
+int garb200_kkt_error(garb200_solver *s, double mudyn, double mueq, const double *theta, double *out) {
+  if (!s || !out) return fail(GARB200_ERR_INVALID, "null argument");
+  if (!s->did_forward) return fail(GARB200_ERR_STATE, "kkt_error needs a forward() into the solver-owned trajectory");
+  CK(cudaSetDevice(s->cfg.device));
+  const DevParams &p = s->p;
+  const size_t B = p.batch;
+  const double *d_theta = nullptr;
+  if (theta && p.nth > 0 && p.num_legs < 2) {
+    CK(cudaMemcpyAsync(p.theta, theta, B * p.nth * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+    d_theta = p.theta;
+  }
+  const int rc = launch_kkt_error(p, d_theta, mudyn, mueq, s->d_kkt_out, s->stream);
+  if (rc < 0) return fail(rc == -1 ? GARB200_ERR_INVALID : GARB200_ERR_CUDA, "kkt_error launch failed");
+  s->launches += rc;
+  return fetch(s, out, s->d_kkt_out, 3 * B);
+}
+
+int garb200_upload_trajectory(garb200_solver *s, const double *xs, const double *us,
+                              const double *vs, const double *lbdas) {
+  if (!s || !xs || !lbdas) return fail(GARB200_ERR_INVALID, "null argument");
+  CK(cudaSetDevice(s->cfg.device));
+  const DevParams &p = s->p;
+  const size_t B = p.batch, n = p.nx, T = p.T;
+  CK(cudaMemcpyAsync(p.xs, xs, B * (T + 1) * n * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  if (us && p.nu) CK(cudaMemcpyAsync(p.us, us, B * (T + 1) * p.nu * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  if (vs && p.nc) CK(cudaMemcpyAsync(p.vs, vs, B * (T + 1) * p.nc * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  CK(cudaMemcpyAsync(p.lbdas, lbdas, B * (p.nc0 + T * n) * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  CK(cudaStreamSynchronize(s->stream));
+  s->did_forward = true;
+  return GARB200_OK;
+}
+
+// ---- introspection --------------------------------------------------------------------------
+int64_t garb200_kernel_launches(const garb200_solver *s) { return s ? s->launches : 0; }
+
+int garb200_last_timings(garb200_solver *s, float *backward_ms, float *forward_ms) {
+  if (!s) return fail(GARB200_ERR_INVALID, "null solver");
+  CK(cudaSetDevice(s->cfg.device));
+  CK(cudaStreamSynchronize(s->stream));
+  if (backward_ms) { *backward_ms = 0.f; if (s->did_backward) CK(cudaEventElapsedTime(backward_ms, s->ev[0], s->ev[1])); }
+  if (forward_ms) { *forward_ms = 0.f; if (s->did_forward) CK(cudaEventElapsedTime(forward_ms, s->ev[2], s->ev[3])); }
+  return GARB200_OK;
+}
+
+int garb200_fp64_peak(int device, int kind, double *tflops) {
+  if (!tflops) return fail(GARB200_ERR_INVALID, "null argument");
+  CK(cudaSetDevice(device));
+  const int rc = fp64_peak(kind, tflops);
+  return rc == 0 ? GARB200_OK : fail(GARB200_ERR_CUDA, "fp64 micro-benchmark failed");
+}
+
+} // extern "C"

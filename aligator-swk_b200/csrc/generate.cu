@@ -1,0 +1,91 @@
+// generate.cu — synthetic random LQ problems generated ON DEVICE (bench data source).
+// Distributions restate the reference generator tests/gar/test_util.cpp:8-66 (see
+// aligator-swk_b200/synth.py for the host twin): Wishart [Q S; S^T R] with nx+nu+1 dof,
+// top-left floor(nx/2)^2 block of Q zeroed on non-terminal knots, q,r,A ~ N(0,1),
+// B ~ U[-1,1], E ~ 1000 N(0,1), f ~ N(0,100^2), C,D,d ~ N(0,1), parameter block N(0,1) /
+// Wishart(nth+2); G0 = I, g0 = -x0, x0 ~ N(0,1).  dist 1 ("explicit"): E = -I,
+// A = 0.9 I + 0.1/sqrt(nx) N(0,1)  — what ProxDDP feeds (explicit-dynamics.hxx:32).
+// RNG: Philox4x32-10 (curand device API), one subsequence per (problem, knot, thread).
+#include <curand_kernel.h>
+#include "kernels.cuh"
+
+namespace garb200 {
+
+__global__ void __launch_bounds__(128) generate_kernel(const DevParams p, unsigned long long seed, int dist) {
+  extern __shared__ __align__(16) double sm[];
+  const int n = p.nx, T = p.T;
+  const int b = blockIdx.x / (T + 1), t = blockIdx.x % (T + 1);
+  const int m = p.nu_t[t], c = p.nc_t[t], h = p.nth;
+  const int tid = threadIdx.x, NT = blockDim.x;
+  const garb200_knot_layout &KL = p.KL;
+  double *rec = p.knots + ((size_t)b * (T + 1) + phys_t(p, t)) * KL.stride;
+  curandStatePhilox4_32_10_t st;
+  curand_init(seed, (unsigned long long)blockIdx.x * NT + tid, 0, &st);
+  auto nrm = [&]() { return curand_normal_double(&st); };
+  const int d = n + m, dof = d + 1;
+  double *W = sm;  // d x dof
+  for (int e = tid; e < d * dof; e += NT) W[e] = nrm();
+  for (int e = tid; e < KL.stride; e += NT) rec[e] = 0.0;
+  __syncthreads();
+  const bool singular = t < T;
+  for (int e = tid; e < d * d; e += NT) {
+    const int i = e % d, j = e / d;
+    double acc = 0.0;
+    for (int k = 0; k < dof; k++) acc = fma(W[i + k * d], W[j + k * d], acc);
+    if (i < n && j < n) rec[KL.Q + i + j * n] = (singular && i < n / 2 && j < n / 2) ? 0.0 : acc;
+    else if (i < n && j >= n) rec[KL.S + i + (j - n) * n] = acc;
+    else if (i >= n && j >= n) rec[KL.R + (i - n) + (j - n) * m] = acc;
+  }
+  for (int i = tid; i < n; i += NT) { rec[KL.q + i] = nrm(); rec[KL.f + i] = 100.0 * nrm(); }
+  for (int i = tid; i < m; i += NT) rec[KL.r + i] = nrm();
+  const double ascale = 0.1 / sqrt((double)n);
+  for (int e = tid; e < n * n; e += NT) {
+    const double a = nrm(), ee = nrm();
+    if (dist == 1) {
+      rec[KL.A + e] = ((e % n) == (e / n) ? 0.9 : 0.0) + ascale * a;
+      rec[KL.E + e] = ((e % n) == (e / n)) ? -1.0 : 0.0;
+    } else {
+      rec[KL.A + e] = a;
+      rec[KL.E + e] = 1000.0 * ee;
+    }
+  }
+  for (int e = tid; e < n * m; e += NT) rec[KL.B + e] = 2.0 * curand_uniform_double(&st) - 1.0;
+  for (int e = tid; e < c * n; e += NT) rec[KL.C + e] = nrm();
+  for (int e = tid; e < c * m; e += NT) rec[KL.D + e] = nrm();
+  for (int i = tid; i < c; i += NT) rec[KL.d + i] = nrm();
+  if (h > 0) {
+    __syncthreads();
+    const int hd = h + 2;
+    for (int e = tid; e < h * hd; e += NT) W[e] = nrm();
+    __syncthreads();
+    for (int e = tid; e < h * h; e += NT) {
+      const int i = e % h, j = e / h;
+      double acc = 0.0;
+      for (int k = 0; k < hd; k++) acc = fma(W[i + k * h], W[j + k * h], acc);
+      rec[KL.Gth + e] = acc;
+    }
+    for (int e = tid; e < n * h; e += NT) rec[KL.Gx + e] = nrm();
+    for (int e = tid; e < m * h; e += NT) rec[KL.Gu + e] = nrm();
+    for (int i = tid; i < h; i += NT) rec[KL.gamma + i] = nrm();
+  }
+  if (t == 0) {
+    double *G0 = p.G0 + (size_t)b * p.nc0 * n, *g0 = p.g0 + (size_t)b * p.nc0;
+    for (int e = tid; e < p.nc0 * n; e += NT) G0[e] = ((e % p.nc0) == (e / p.nc0)) ? 1.0 : 0.0;
+    for (int i = tid; i < p.nc0; i += NT) g0[i] = -nrm();
+  }
+}
+
+int launch_generate(const DevParams &p, uint64_t seed, int dist, cudaStream_t st) {
+  const int d = p.nx + p.nu;
+  size_t w = (size_t)d * (d + 1);
+  const size_t wh = (size_t)p.nth * (p.nth + 2);
+  if (wh > w) w = wh;
+  const size_t smem = (w + 2) * sizeof(double);
+  if (smem > 227u * 1024u) return -1;
+  if (cudaFuncSetAttribute(generate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+    return -2;
+  generate_kernel<<<p.batch * (p.T + 1), 128, smem, st>>>(p, (unsigned long long)seed, dist);
+  return cudaGetLastError() == cudaSuccess ? 1 : -2;
+}
+
+} // namespace garb200

@@ -1,0 +1,68 @@
+// kernels.cuh — shared declarations between the CUDA translation units.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/garb200.h"
+
+namespace garb200 {
+
+/// work.hpp:17-22 — balanced leg partition [beg, end) of the T+1 knots.
+__host__ __device__ inline void get_work(int horz, int tid, int nthreads, int &beg, int &end) {
+  beg = (int)((long long)tid * (horz + 1) / nthreads);
+  end = (int)((long long)(tid + 1) * (horz + 1) / nthreads);
+}
+
+/// Everything a kernel needs to know about one solver (passed by value).
+struct DevParams {
+  int nx, nu, nc, nth;  // layout dims (nth: user parameter dim; 0 in leg mode)
+  int hleg;             // parameter dim of the non-last legs (nx) in leg mode, else 0
+  int T, nc0, batch, num_legs;
+  int shift;            // ring offset of the time axis (cycleAppend)
+  int store_all_values;
+  int nslots;           // value slots per problem (T+1 when storing all, else #legs or 1)
+  const int *nu_t, *nc_t;         // [T+1] logical-time dims
+  double *knots;                  // [batch][T+1][KL.stride]   (physical time order)
+  double *G0, *g0;                // [batch][nc0*nx], [batch][nc0]
+  double *gains;                  // [batch][T+1][GL.stride]   (physical time order)
+  double *values;                 // [batch][nslots][VL.stride]
+  double *kkt0_ff, *kkt0_fth, *thGrad, *thHess;  // per problem
+  double *xs, *us, *vs, *lbdas;   // solver-owned trajectories
+  double *theta;                  // [batch][nth] device copy (forward)
+  // condensed system of the parallel-in-time solver (leg mode), per problem:
+  double *cdiag, *csuper, *csub, *cdiagF, *csubF, *crhs, *csol, *cerr, *csubd;
+  int *cpiv;
+  int32_t *flags, *refine_steps;
+  double mudyn, mueq;
+  garb200_knot_layout KL;
+  garb200_gain_layout GL;   // built with nth_eff = (leg mode ? nx : nth)
+  garb200_value_layout VL;  // same
+};
+
+__host__ __device__ inline int phys_t(const DevParams &p, int t) {
+  // logical knot t -> physical record index; the terminal knot never moves
+  return (t >= p.T || p.T == 0) ? t : (t + p.shift) % p.T;
+}
+__host__ __device__ inline int value_slot(const DevParams &p, int t) {
+  if (p.store_all_values) return t;
+  if (p.num_legs < 2) return t == 0 ? 0 : -1;
+  for (int j = 0; j < p.num_legs; j++) {
+    int b, e; get_work(p.T, j, p.num_legs, b, e);
+    if (b == t) return j;
+  }
+  return -1;
+}
+
+struct LaunchCfg { int threads; size_t smem; int grid; };
+
+// launchers (each returns the number of kernels it launched, < 0 on error)
+int launch_backward(const DevParams &p, cudaStream_t st);
+int launch_forward(const DevParams &p, const double *d_theta, double *xs, double *us, double *vs,
+                   double *lbdas, cudaStream_t st);
+int launch_condensed(const DevParams &p, cudaStream_t st);
+int launch_collapse(const DevParams &p, cudaStream_t st);
+int launch_kkt_error(const DevParams &p, const double *d_theta, double mudyn, double mueq,
+                     double *d_out, cudaStream_t st);
+int launch_generate(const DevParams &p, uint64_t seed, int dist, cudaStream_t st);
+int fp64_peak(int kind, double *tflops);
+
+} // namespace garb200

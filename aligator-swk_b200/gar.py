@@ -1,0 +1,282 @@
+"""Host-side mirror of the reference's ``aligator.gar`` surface, backed by the CUDA C-ABI.
+
+Same names, argument meaning and error behaviour as the reference bindings
+(/root/reference/bindings/python/src/gar/expose-gar.cpp:55-130, expose-prox-riccati.cpp:14-56,
+expose-parallel.cpp:16-24, expose-utils.cpp:33-53) so the parity tests read like
+/root/reference/tests/gar/*.cpp.  One solver object drives ONE problem here (batch = 1
+through the same kernels); batched use goes through ``capi.Solver`` with packed arrays.
+
+Nothing in this module computes on the CPU: backward / forward / KKT residuals all run
+the sm_100a kernels; numpy is only used to hold the caller's matrices.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+from . import capi
+from .layout import GainLayout, KnotLayout
+from .synth import PackedProblems
+
+
+class LqrKnot:
+    """lqr-problem.hpp:32-196.  Cost 1/2 [x;u]^T [Q S; S^T R] [x;u] + q^T x + r^T u,
+    dynamics E x' + A x + B u + f = 0, constraint C x + D u + d = 0."""
+
+    _MATS = ("Q", "S", "R", "q", "r", "A", "B", "E", "f", "C", "D", "d", "Gth", "Gx", "Gu", "Gv", "gamma")
+
+    def __init__(self, nx, nu, nc, nx2=None, nth=0):
+        nx2 = nx if nx2 is None else nx2
+        if nx2 != nx:
+            raise ValueError("garb200 supports nx2 == nx only")
+        self.nx, self.nu, self.nc, self.nx2, self.nth = nx, nu, nc, nx2, nth
+        z = np.zeros
+        self.Q, self.S, self.R = z((nx, nx)), z((nx, nu)), z((nu, nu))
+        self.q, self.r = z(nx), z(nu)
+        self.A, self.B, self.E, self.f = z((nx, nx)), z((nx, nu)), z((nx, nx)), z(nx)
+        self.C, self.D, self.d = z((nc, nx)), z((nc, nu)), z(nc)
+        self._alloc_param(nth)
+
+    def _alloc_param(self, nth):
+        z = np.zeros
+        self.nth = nth
+        self.Gth, self.Gx, self.Gu = z((nth, nth)), z((self.nx, nth)), z((self.nu, nth))
+        self.Gv, self.gamma = z((self.nc, nth)), z(nth)
+
+    def addParameterization(self, nth):        # lqr-problem.hxx:215-223
+        self._alloc_param(nth)
+        return self
+
+    def copy(self):
+        k = LqrKnot(self.nx, self.nu, self.nc, self.nx2, self.nth)
+        for n in self._MATS:
+            setattr(k, n, np.array(getattr(self, n), dtype=np.float64, copy=True))
+        return k
+
+    def isApprox(self, other, prec=np.finfo(float).eps):
+        return all(np.allclose(getattr(self, n), getattr(other, n), rtol=prec, atol=0) for n in self._MATS)
+
+    def fields(self):
+        return {n: np.asarray(getattr(self, n), dtype=np.float64) for n in self._MATS if n != "Gv"}
+
+
+class LqrProblem:
+    """lqr-problem.hpp:198-289."""
+
+    def __init__(self, stages, nc0):
+        self.stages = [k.copy() for k in stages]   # "constructor creates a copy"
+        nx0 = self.stages[0].nx if self.stages else 0
+        self.G0 = np.zeros((nc0, nx0))
+        self.g0 = np.zeros(nc0)
+
+    @property
+    def horizon(self):
+        return len(self.stages) - 1
+
+    @property
+    def nc0(self):
+        return int(np.asarray(self.g0).shape[0])
+
+    @property
+    def ntheta(self):
+        return self.stages[0].nth
+
+    @property
+    def isInitialized(self):
+        return len(self.stages) > 0
+
+    @property
+    def isParameterized(self):
+        return self.isInitialized and self.stages[0].nth > 0
+
+    def addParameterization(self, nth):
+        for k in self.stages:
+            k.addParameterization(nth)
+
+    def pack(self) -> PackedProblems:
+        st = self.stages
+        nx = st[0].nx
+        if any(k.nx != nx for k in st):
+            raise ValueError("garb200 needs the same nx at every knot")
+        nth = st[0].nth
+        if any(k.nth != nth for k in st):
+            raise ValueError("garb200 needs the same nth at every knot")
+        nu, nc = max(k.nu for k in st), max(k.nc for k in st)
+        L = KnotLayout(nx, nu, nc, nth)
+        T = self.horizon
+        knots = np.zeros((1, T + 1, L.stride))
+        for t, k in enumerate(st):
+            L.pack(knots[0, t], k.fields(), nu=k.nu, nc=k.nc)
+        G0 = np.asarray(self.G0, dtype=np.float64).reshape(self.nc0, nx)
+        return PackedProblems(L, T, self.nc0,
+                              np.array([k.nu for k in st], np.int32),
+                              np.array([k.nc for k in st], np.int32),
+                              knots, G0.reshape(1, -1, order="F").copy(),
+                              np.asarray(self.g0, dtype=np.float64).reshape(1, -1).copy())
+
+
+def lqrInitializeSolution(problem: LqrProblem):
+    """utils.hpp:139-168."""
+    st = problem.stages
+    N = problem.horizon
+    xs = [np.zeros(k.nx) for k in st]
+    us = [np.zeros(k.nu) for k in st]
+    vs = [np.zeros(k.nc) for k in st]
+    lbdas = [np.zeros(problem.nc0)] + [np.zeros(st[i].nx2) for i in range(N)]
+    if st[-1].nu == 0:
+        us.pop()
+    return xs, us, vs, lbdas
+
+
+class RiccatiSolverBase:
+    """riccati-base.hpp:12-34 — the drop-in boundary."""
+
+    def backward(self, mudyn, mueq):  # pragma: no cover - interface
+        raise NotImplementedError
+
+    def forward(self, xs, us, vs, lbdas, theta=None):  # pragma: no cover - interface
+        raise NotImplementedError
+
+    def cycleAppend(self, knot):  # pragma: no cover - interface
+        raise NotImplementedError
+
+    def collapseFeedback(self):
+        pass
+
+    def getFeedforward(self, i):  # pragma: no cover - interface
+        raise NotImplementedError
+
+    def getFeedback(self, i):  # pragma: no cover - interface
+        raise NotImplementedError
+
+
+class _GpuSolver(RiccatiSolverBase):
+    def __init__(self, problem: LqrProblem, num_legs=0, device=0):
+        self.problem_ = problem
+        pp = problem.pack()
+        self._pp = pp
+        self._solver = capi.Solver.for_problems(pp, num_legs=num_legs, device=device,
+                                                flags=capi.STORE_ALL_VALUES)
+
+    def _upload(self):
+        # the reference re-reads problem_->stages on every backward() (proximal-riccati.hxx:37)
+        self._pp = self.problem_.pack()
+        self._solver.upload(self._pp)
+
+    def backward(self, mudyn, mueq):
+        self._upload()
+        self._solver.backward(mudyn, mueq)
+        try:
+            self._solver.synchronize()
+        except capi.GarB200Error as e:
+            if e.code == capi.ERR_NUMERIC:
+                return False
+            raise
+        return True
+
+    def _scatter(self, xs, us, vs, lbdas, X, U, V, Lb):
+        st = self.problem_.stages
+        N, nx, nc0 = self.problem_.horizon, st[0].nx, self.problem_.nc0
+        for t, k in enumerate(st):
+            xs[t][:] = X[0, t]
+            if t < len(us):
+                us[t][:] = U[0, t, :k.nu]
+            vs[t][:] = V[0, t, :k.nc]
+        lbdas[0][:] = Lb[0, :nc0]
+        for t in range(1, N + 1):
+            lbdas[t][:] = Lb[0, nc0 + (t - 1) * nx: nc0 + t * nx]
+
+    def getFeedforward(self, i):
+        return self._solver.get_gains(0, i)[0]
+
+    def getFeedback(self, i):
+        return self._solver.get_gains(0, i)[1]
+
+    def getParamFeedback(self, i):
+        return self._solver.get_gains(0, i)[2]
+
+    def value(self, i):
+        """datas[i].vm (riccati-kernel.hpp:39-60)."""
+        return self._solver.get_value(0, i)
+
+    def kktError(self, mudyn, mueq, theta=None):
+        return self._solver.kkt_error(mudyn, mueq, theta)[0]
+
+
+class ProximalRiccatiSolver(_GpuSolver):
+    """proximal-riccati.hpp:12-45, GPU-backed."""
+
+    def __init__(self, problem: LqrProblem, device=0):
+        super().__init__(problem, 0, device)
+
+    def forward(self, xs, us, vs, lbdas, theta=None):
+        X, U, V, Lb = self._solver.forward(theta)
+        self._scatter(xs, us, vs, lbdas, X, U, V, Lb)
+        return True
+
+    def cycleAppend(self, knot: LqrKnot):
+        pk = KnotLayout(self._pp.layout.nx, knot.nu, knot.nc, knot.nth)
+        f = {n: np.ascontiguousarray(np.asarray(v, dtype=np.float64).reshape(-1, order="F"))
+             for n, v in knot.fields().items()}
+        view = capi.KnotView()
+        view.nu, view.nc = knot.nu, knot.nc
+        self._keep = f
+        for n, a in f.items():
+            setattr(view, n, a.ctypes.data_as(capi._dp) if a.size else None)
+        self._solver.cycle_append([view], shared=True)
+
+    @property
+    def kkt0(self):
+        ff, fth, _, _ = self._solver.get_initial(0)
+        return {"ff": ff, "fth": fth}
+
+    @property
+    def thGrad(self):
+        return self._solver.get_initial(0)[2]
+
+    @property
+    def thHess(self):
+        return self._solver.get_initial(0)[3]
+
+
+class ParallelRiccatiSolver(_GpuSolver):
+    """parallel-solver.hpp:24-108, GPU-backed: legs are CTAs instead of OpenMP threads."""
+
+    def __init__(self, problem: LqrProblem, num_threads: int, device=0):
+        if num_threads < 2:   # ALIGATOR_RUNTIME_ERROR, parallel-solver.hxx:25-29
+            raise RuntimeError(f"(ParallelRiccatiSolver) num_threads (={num_threads}) should be "
+                               "greater than or equal to 2.")
+        self.numThreads = num_threads
+        super().__init__(problem, num_threads, device)
+
+    def forward(self, xs, us, vs, lbdas, theta=None):   # theta ignored (parallel-solver.hxx:184)
+        X, U, V, Lb = self._solver.forward(None)
+        self._scatter(xs, us, vs, lbdas, X, U, V, Lb)
+        return True
+
+    def collapseFeedback(self):
+        self._solver.collapse_feedback()
+
+    def refinementSteps(self):
+        return int(self._solver.get_refinement_steps()[0])
+
+
+def lqrComputeKktError(problem: LqrProblem, xs, us, vs, lbdas, mudyn, mueq, theta=None,
+                       verbose=False, device=0):
+    """utils.hxx:94-192 on the GPU: uploads the trajectory next to the problem and runs the
+    residual kernel.  Returns [dyn, cstr, dual]."""
+    pp = problem.pack()
+    s = capi.Solver.for_problems(pp, device=device)
+    s.upload(pp)
+    L = pp.layout
+    T, nx, nc0 = pp.horizon, L.nx, pp.nc0
+    X, U, V, Lb = s.traj_arrays()
+    for t, k in enumerate(problem.stages):
+        X[0, t] = xs[t]
+        if t < len(us):
+            U[0, t, :k.nu] = us[t]
+        V[0, t, :k.nc] = vs[t]
+    Lb[0, :nc0] = lbdas[0]
+    for t in range(1, T + 1):
+        Lb[0, nc0 + (t - 1) * nx: nc0 + t * nx] = lbdas[t]
+    s.upload_trajectory(X, U, V, Lb)
+    return s.kkt_error(mudyn, mueq, theta)[0]

@@ -1,0 +1,193 @@
+/* garb200.h — C ABI of the B200-native batched backend for aligator's `gar` LQ solver.
+ *
+ * Drop-in boundary: `gar::RiccatiSolverBase<double>`
+ * (/root/reference/include/aligator/gar/riccati-base.hpp:12-34) and its concrete
+ * solvers ProximalRiccatiSolver (proximal-riccati.hpp:12-45) and ParallelRiccatiSolver
+ * (parallel-solver.hpp:24-108).  Every entry point below names the reference interface
+ * it replaces.  Plain pointers and sizes only: no Eigen, no torch, no C++ types.
+ *
+ * One solver handle owns `batch` INDEPENDENT LQ problems of identical dimensions
+ * (the reference solves one problem per solver object).  All device and pinned memory
+ * is allocated in garb200_create(); nothing is allocated afterwards — the reference's
+ * ALIGATOR_NOMALLOC_SCOPED contract (proximal-riccati.hxx:35, parallel-solver.hxx:115).
+ *
+ * Error convention: every call returns a status (0 = GARB200_OK).  The reference's
+ * `bool backward()` becomes a status plus a per-problem int32 flag array
+ * (garb200_get_flags).  There is NO CPU fallback: without a CUDA device every compute
+ * call returns GARB200_ERR_CUDA.
+ *
+ * Record formats: include/garb200_layout.h.  Trajectory arrays, per problem:
+ *   xs    (T+1) x nx                         xs[t]  at t*nx
+ *   us    (T+1) x nu   (rows of knots with nu_t < nu are zero padded; us[T] unused when
+ *                       the terminal knot has nu = 0, utils.hpp:163-165)
+ *   vs    (T+1) x nc
+ *   lbdas nc0 + T*nx   lbdas[0] (nc0 entries, utils.hpp:150) then lbdas[t] at nc0+(t-1)*nx
+ * and problem b follows problem b-1 contiguously in every array.
+ */
+#ifndef GARB200_H
+#define GARB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+#include "garb200_layout.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GARB200_OK 0
+#define GARB200_ERR_INVALID 1   /* bad argument / unsupported dimensions            */
+#define GARB200_ERR_CUDA 2      /* CUDA runtime error (see garb200_last_error)       */
+#define GARB200_ERR_NUMERIC 3   /* >= 1 problem hit a zero pivot / non-finite value  */
+#define GARB200_ERR_STATE 4     /* call order violated (e.g. forward before backward)*/
+
+/* per-problem flag bits (garb200_get_flags) */
+#define GARB200_FLAG_LU_SINGULAR 1   /* PartialPivLU(E) met a zero pivot (riccati-kernel.hxx:172) */
+#define GARB200_FLAG_LLT_NOT_PD 2    /* LLT(I + mu*Ptilde) met a non-positive pivot (:185)       */
+#define GARB200_FLAG_BK_SINGULAR 4   /* BunchKaufman -> NumericalIssue (bunchkaufman.hpp:56-57)  */
+#define GARB200_FLAG_NONFINITE 8     /* NaN/Inf in the produced gains                            */
+#define GARB200_FLAG_TRIDIAG_FAIL 16 /* block-tridiagonal BK failed (block-tridiagonal.hpp:102)  */
+
+/* garb200_config.flags */
+#define GARB200_STORE_ALL_VALUES 1   /* keep StageFactor::vm of EVERY knot (default: knot 0 and
+                                        leg heads only — what the algorithm itself consumes)  */
+
+typedef struct garb200_solver garb200_solver; /* opaque */
+
+typedef struct garb200_config {
+  int nx;          /* state dim (nx2 == nx for every knot)                              */
+  int nu;          /* max control dim over knots                                        */
+  int nc;          /* max equality-constraint dim over knots                            */
+  int nth;         /* parameter dim (LqrProblemTpl::ntheta, lqr-problem.hpp:250)        */
+  int horizon;     /* T: the problem has T+1 knots (LqrProblemTpl::horizon)             */
+  int nc0;         /* rows of the initial constraint G0 x0 + g0 = 0 (nc0())             */
+  int batch;       /* number of independent problems                                    */
+  int num_legs;    /* 0/1: ProximalRiccatiSolver; >= 2: ParallelRiccatiSolver with that
+                      many parallel-in-time legs (`num_threads`, parallel-solver.hpp:38) */
+  int device;      /* CUDA device ordinal                                               */
+  int flags;       /* GARB200_STORE_ALL_VALUES | ...                                    */
+  const int *nu_t; /* optional [T+1] per-knot nu (NULL: nu for t < T, nu_term at T)     */
+  const int *nc_t; /* optional [T+1] per-knot nc (NULL: nc for t < T, nc_term at T)     */
+  int nu_term;     /* used when nu_t == NULL (generated problems: 0, test_util.cpp:60)  */
+  int nc_term;     /* used when nc_t == NULL                                            */
+} garb200_config;
+
+/* One knot as the reference stores it: 16 column-major matrices, each with its own
+ * pointer (`ManagedMatrix::data()`, memory/managed-matrix.hpp:279-282) — so a binding can
+ * pass LqrKnotTpl fields without copying.  NULL = all zeros. Gv is not read
+ * (riccati-kernel.hxx:128,272). */
+typedef struct garb200_knot_view {
+  int nu, nc; /* this knot's own dims (<= config) */
+  const double *Q, *S, *R, *q, *r;
+  const double *A, *B, *E, *f;
+  const double *C, *D, *d;
+  const double *Gth, *Gx, *Gu, *gamma;
+} garb200_knot_view;
+
+/* ---- life cycle -------------------------------------------------------------------
+ * replaces ProximalRiccatiSolver(const LqrProblemTpl&)  proximal-riccati.hxx:12-30
+ *      and ParallelRiccatiSolver(LqrProblemTpl&, uint)  parallel-solver.hxx:18-49      */
+int garb200_create(const garb200_config *cfg, garb200_solver **out);
+void garb200_destroy(garb200_solver *s);
+const char *garb200_last_error(void);
+const char *garb200_version(void);
+
+/* Run subsequent kernels/copies on this CUDA stream (a cudaStream_t, passed as void*). */
+int garb200_set_stream(garb200_solver *s, void *cuda_stream);
+/* Block until everything queued by this solver has finished. */
+int garb200_synchronize(garb200_solver *s);
+
+/* layouts actually used by this solver (gains/values use nth_eff = nx in leg mode) */
+int garb200_get_layouts(const garb200_solver *s, garb200_knot_layout *knot,
+                        garb200_gain_layout *gain, garb200_value_layout *value);
+/* same, without a solver (pure function of the dims) */
+void garb200_layouts(int nx, int nu, int nc, int nth, int *knot17, int *gain5, int *value8);
+
+/* ---- problem data (the solver keeps a device-resident copy; the reference re-reads
+ * `problem_->stages` on every backward(), proximal-riccati.hxx:37)  -------------------- */
+/* whole batch, already packed: knots [batch][T+1][stride], G0 [batch][nc0*nx] col-major,
+ * g0 [batch][nc0]; host pointers */
+int garb200_upload_packed(garb200_solver *s, const double *knots, const double *G0,
+                          const double *g0);
+/* one knot from reference-style matrices into the pinned staging buffer */
+int garb200_stage_knot(garb200_solver *s, int problem, int t, const garb200_knot_view *k);
+int garb200_stage_initial(garb200_solver *s, int problem, const double *G0, const double *g0);
+/* H2D of everything staged so far */
+int garb200_commit(garb200_solver *s);
+/* raw device pointers of the resident problem (for upstream device producers) */
+int garb200_device_problem(garb200_solver *s, double **d_knots, double **d_G0, double **d_g0);
+/* fill the resident problem with synthetic random data ON DEVICE (bench data source;
+ * distributions of tests/gar/test_util.cpp:13-66; dist 0 = "ref", 1 = "explicit" E=-I) */
+int garb200_generate(garb200_solver *s, uint64_t seed, int dist);
+/* D2H of the packed problem of `count` problems starting at `first` */
+int garb200_download_packed(garb200_solver *s, int first, int count, double *knots, double *G0,
+                            double *g0);
+
+/* ---- the hot path -------------------------------------------------------------------
+ * bool RiccatiSolverBase::backward(mudyn, mueq)          riccati-base.hpp:18
+ *   ProximalRiccatiSolver::backward                      proximal-riccati.hxx:32-64
+ *   ParallelRiccatiSolver::backward                      parallel-solver.hxx:111-179   */
+int garb200_backward(garb200_solver *s, double mudyn, double mueq);
+
+/* bool RiccatiSolverBase::forward(xs, us, vs, lbdas, theta)   riccati-base.hpp:20-23
+ * theta: host, [batch][nth] or NULL (ignored in leg mode, parallel-solver.hxx:184).
+ * Outputs: HOST pointers (any may be NULL to skip the D2H copy of that array).         */
+int garb200_forward(garb200_solver *s, const double *theta, double *xs, double *us,
+                    double *vs, double *lbdas);
+/* same with DEVICE pointers for theta and outputs (NULL output = solver-owned buffer) */
+int garb200_forward_device(garb200_solver *s, const double *d_theta, double *d_xs,
+                           double *d_us, double *d_vs, double *d_lbdas);
+/* solver-owned device trajectory buffers (valid after forward*) */
+int garb200_device_trajectory(garb200_solver *s, double **d_xs, double **d_us, double **d_vs,
+                              double **d_lbdas);
+
+/* ---- solver state readers ------------------------------------------------------------
+ * getFeedforward(i) / getFeedback(i)                      riccati-base.hpp:30-31
+ * datas[t].{ff,fb,fth}                                    riccati-kernel.hpp:76-78      */
+int garb200_get_gains(garb200_solver *s, int problem, int t, double *ff, double *fb_rowmajor,
+                      double *fth_rowmajor);
+/* whole packed gains record(s) [count][T+1][gain stride] */
+int garb200_download_gains(garb200_solver *s, int first, int count, double *gains);
+int garb200_device_gains(garb200_solver *s, double **d_gains);
+/* datas[t].vm (riccati-kernel.hpp:39-60); one packed value record. Needs
+ * GARB200_STORE_ALL_VALUES unless t is 0 (or a leg head in leg mode). */
+int garb200_get_value(garb200_solver *s, int problem, int t, double *value_record);
+/* kkt0.ff [nx+nc0], kkt0.fth [(nx+nc0) x nth] row-major, thGrad [nth], thHess [nth x nth]
+ * column-major (proximal-riccati.hpp:39-41) */
+int garb200_get_initial(garb200_solver *s, int problem, double *kkt0_ff, double *kkt0_fth,
+                        double *thGrad, double *thHess);
+int garb200_get_flags(garb200_solver *s, int32_t *flags /* [batch] */);
+/* leg mode: number of iterative-refinement steps taken per problem (parallel-solver.hxx:155-175) */
+int garb200_get_refinement_steps(garb200_solver *s, int32_t *steps /* [batch] */);
+
+/* void collapseFeedback()                                 parallel-solver.hpp:55-66     */
+int garb200_collapse_feedback(garb200_solver *s);
+/* void cycleAppend(const LqrKnot&)   proximal-riccati.hxx:80-88, parallel-solver.hxx:217-238
+ * Rotates the time axis of problem AND factor storage left by one (ring offset, no copy)
+ * and installs `knots[b]` (one view per problem, or one shared view if `shared` != 0)
+ * as the new knot T-1.                                                                  */
+int garb200_cycle_append(garb200_solver *s, const garb200_knot_view *knots, int shared);
+
+/* ---- metric: lqrComputeKktError                         utils.hxx:94-192
+ * On the trajectories of the last forward*; out [batch][3] = {dyn, cstr, dual} (host). */
+int garb200_kkt_error(garb200_solver *s, double mudyn, double mueq, const double *theta,
+                      double *out);
+
+/* Host trajectory -> solver-owned device buffers (so garb200_kkt_error can score a solution
+ * that was produced elsewhere, like the reference's free function does). */
+int garb200_upload_trajectory(garb200_solver *s, const double *xs, const double *us,
+                              const double *vs, const double *lbdas);
+
+/* ---- introspection for bench / roofline ---------------------------------------------- */
+/* number of kernels launched by this solver since creation */
+int64_t garb200_kernel_launches(const garb200_solver *s);
+/* device-event time (ms) of the last backward and forward kernels sequences */
+int garb200_last_timings(garb200_solver *s, float *backward_ms, float *forward_ms);
+/* FP64 micro-benchmarks used as roofline denominators: returns TFLOP/s
+ * kind 0 = DFMA register loop, 1 = DMMA mma.sync.m8n8k4.f64 loop */
+int garb200_fp64_peak(int device, int kind, double *tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GARB200_H */

@@ -1,0 +1,213 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on the same
+bytes.  FP64 tolerance from BASELINE.json north_star: relative 1e-10 on (xs, us, vs, lbdas)
+and gains, KKT residuals reported/asserted the way the reference's tests do
+(/root/reference/tests/gar/riccati.cpp: <= 1e-9 / 1e-10).
+"""
+import os
+
+import numpy as np
+import pytest
+
+from aligator_swk_b200.layout import GainLayout
+from aligator_swk_b200.synth import generate_problems
+from conftest import relerr
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-10          # north_star: "within a relative 1e-10 in fp64"
+RTOL_GAINS = 1e-9     # gains of ill-conditioned knots amplify rounding; still far below test tolerances
+
+
+@pytest.fixture(scope="module")
+def capi():
+    from aligator_swk_b200 import capi as c
+    c.lib()
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return c
+
+
+def solve_gpu(capi, pp, mu, theta=None, num_legs=0, flags=0):
+    s = capi.Solver.for_problems(pp, num_legs=num_legs, flags=flags)
+    s.upload(pp)
+    s.backward(mu, mu)
+    xs, us, vs, lb = s.forward(theta)
+    return s, xs, us, vs, lb
+
+
+def compare_traj(oracle, pp, mu, xs, us, vs, lb, theta=None, legs=0, rtol=RTOL, problems=None):
+    worst = 0.0
+    for b in (problems if problems is not None else range(pp.batch)):
+        ref = (oracle.parallel_solve(pp, mu, mu, legs, b=b) if legs >= 2
+               else oracle.prox_solve(pp, mu, mu, theta=theta, b=b))
+        for got, key in ((xs[b], "xs"), (us[b], "us"), (vs[b], "vs"), (lb[b], "lbdas")):
+            e = relerr(got, ref[key])
+            worst = max(worst, e)
+            assert e < rtol, (b, key, e)
+    return worst
+
+
+CASES = [
+    # nx, nu, nc, nth, T, batch, mu, dist
+    (2, 2, 0, 0, 0, 3, 1e-13, "ref"),        # one_knot_prob (riccati.cpp:93-111)
+    (2, 2, 0, 0, 8, 5, 1e-14, "explicit"),
+    (12, 4, 0, 0, 50, 32, 1e-11, "ref"),     # C2 shape
+    (36, 12, 0, 0, 100, 6, 1e-11, "ref"),    # C1 shape, bench mu
+    (36, 12, 0, 0, 100, 2, 1e-14, "ref"),    # random_long_problem mu (riccati.cpp:113-121)
+    (36, 12, 6, 4, 25, 3, 1e-11, "ref"),     # C3 shape (shorter horizon)
+    (3, 2, 0, 1, 100, 4, 1e-12, "ref"),      # parametric (riccati.cpp:160-205)
+    (8, 3, 2, 0, 15, 4, 1e-8, "explicit"),
+    (7, 5, 3, 2, 9, 4, 1e-6, "ref"),
+    (17, 1, 0, 0, 12, 3, 1e-9, "ref"),
+    (33, 9, 4, 3, 6, 2, 1e-10, "ref"),
+    (5, 0, 2, 0, 6, 2, 1e-9, "ref"),         # nu = 0 everywhere
+    (48, 16, 0, 0, 8, 2, 1e-11, "ref"),
+]
+
+
+@pytest.mark.parametrize("case", CASES, ids=lambda c: "nx%d_nu%d_nc%d_nth%d_T%d_B%d_%g_%s" % c)
+def test_prox_parity(capi, oracle, case):
+    nx, nu, nc, nth, T, B, mu, dist = case
+    pp = generate_problems(B, T, nx, nu, nc, nth, seed=nx * 131 + T, dist=dist)
+    theta = np.random.default_rng(1).standard_normal((B, nth)) if nth else None
+    s = capi.Solver.for_problems(pp, flags=capi.STORE_ALL_VALUES)
+    s.upload(pp)
+    s.backward(mu, mu)
+    xs, us, vs, lb = s.forward(theta)
+    assert (s.get_flags() == 0).all()
+    G = GainLayout(nx, nu, nc, nth)
+    gains = s.download_gains()
+    kkt_gpu = s.kkt_error(mu, mu, theta)
+    for b in range(B):
+        th = None if theta is None else theta[b]
+        ref = oracle.prox_solve(pp, mu, mu, theta=th, b=b)
+        for got, key in ((xs[b], "xs"), (us[b], "us"), (vs[b], "vs"), (lb[b], "lbdas")):
+            assert relerr(got, ref[key]) < RTOL, (b, key, relerr(got, ref[key]))
+        # gains, knot by knot (ff / fb / fth with the knot's own row count)
+        for t in range(T + 1):
+            a = G.unpack(gains[b, t], pp.nu_t[t], pp.nc_t[t])
+            r = G.unpack(ref["gains"][t], pp.nu_t[t], pp.nc_t[t])
+            scale = max(np.abs(r[1]).max() if r[1].size else 0.0, np.abs(r[0]).max() if r[0].size else 0.0, 1e-300)
+            for x, y in zip(a, r):
+                if x.size:
+                    assert np.abs(x - y).max() / scale < RTOL_GAINS, (b, t)
+        # value function + initial stage
+        v0 = s.get_value(b, 0)
+        from aligator_swk_b200.layout import ValueLayout
+        rv0 = ValueLayout(nx, nth).unpack(ref["values"][0])
+        assert relerr(v0["Pmat"], rv0["Pmat"]) < RTOL_GAINS and relerr(v0["pvec"], rv0["pvec"]) < RTOL_GAINS
+        ff0, fth0, thg, thh = s.get_initial(b)
+        assert relerr(ff0, ref["kkt0_ff"]) < RTOL
+        if nth:
+            assert relerr(fth0, ref["kkt0_fth"]) < RTOL_GAINS
+            assert relerr(thg, ref["thGrad"]) < RTOL_GAINS and relerr(thh, ref["thHess"]) < RTOL_GAINS
+        # KKT residual kernel == oracle's lqrComputeKktError on the GPU trajectory
+        ek = oracle.kkt_error(pp, xs[b], us[b], vs[b], lb[b], mu, mu, theta=th, b=b)
+        assert np.allclose(kkt_gpu[b], ek, rtol=1e-6, atol=1e-13), (kkt_gpu[b], ek)
+        # and it is as small as the oracle's own residual (same order of magnitude)
+        assert kkt_gpu[b].max() <= max(10 * ref["kkt"].max(), 1e-12)
+    s.close()
+
+
+def test_reference_test_tolerances(capi, oracle):
+    """random_long_problem (same knot for all t, mu = 1e-14): KKT <= 1e-9 (riccati.cpp:113-135)."""
+    pp = generate_problems(2, 100, 36, 12, seed=42, same_knot=True, x0=np.zeros(36))
+    s, xs, us, vs, lb = solve_gpu(capi, pp, 1e-14)
+    assert s.kkt_error(0.0, 0.0).max() <= 1e-9
+    compare_traj(oracle, pp, 1e-14, xs, us, vs, lb)
+
+
+def test_ragged_knots_short_horz_pb(capi, oracle):
+    """riccati.cpp:20-91: one knot with nc = nu among nc = 0 knots, E = -I."""
+    from test_oracle import short_horz_pb
+    pp = short_horz_pb().pack()
+    s, xs, us, vs, lb = solve_gpu(capi, pp, 1e-14)
+    assert s.kkt_error(0.0, 0.0).max() <= 1e-9
+    compare_traj(oracle, pp, 1e-14, xs, us, vs, lb)
+
+
+def test_golden_fixtures(capi):
+    gd = os.path.join(os.path.dirname(__file__), "golden")
+    from golden.make_golden import load_case
+    for f in sorted(x for x in os.listdir(gd) if x.endswith(".npz")):
+        pp, mu, theta, gold = load_case(os.path.join(gd, f))
+        s, xs, us, vs, lb = solve_gpu(capi, pp, mu, theta)
+        for got, key in ((xs[0], "xs"), (us[0], "us"), (vs[0], "vs"), (lb[0], "lbdas")):
+            assert relerr(got, gold[key]) < RTOL, (f, key, relerr(got, gold[key]))
+
+
+def test_gar_mirror_api(capi, oracle):
+    """The reference-shaped host API (gar.ProximalRiccatiSolver) end to end, incl. getFeedback."""
+    from aligator_swk_b200 import gar
+    from test_oracle import short_horz_pb
+    prob = short_horz_pb()
+    solver = gar.ProximalRiccatiSolver(prob)
+    assert solver.backward(1e-14, 1e-14)
+    xs, us, vs, lbdas = gar.lqrInitializeSolution(prob)
+    assert len(xs) == prob.horizon + 1 and len(us) == prob.horizon + 1 and len(lbdas) == prob.horizon + 1
+    assert solver.forward(xs, us, vs, lbdas)
+    err = gar.lqrComputeKktError(prob, xs, us, vs, lbdas, 0.0, 0.0)
+    assert err.max() <= 1e-9
+    K = solver.getFeedback(0)
+    kff = solver.getFeedforward(0)
+    assert K.shape == (2 + 0 + 4, 2) and kff.shape == (6,)
+    np.testing.assert_allclose(us[0], kff[:2] + K[:2] @ xs[0], rtol=1e-12, atol=1e-14)
+    # the solver re-reads the problem on every backward (proximal-riccati.hxx:37)
+    prob.stages[0].q[:] = 5.0
+    solver.backward(1e-14, 1e-14)
+    xs2, us2, vs2, lb2 = gar.lqrInitializeSolution(prob)
+    solver.forward(xs2, us2, vs2, lb2)
+    assert np.abs(us2[0] - us[0]).max() > 1e-6
+    ref = oracle.prox_solve(prob.pack(), 1e-14, 1e-14)
+    assert relerr(np.array(xs2), ref["xs"]) < RTOL
+
+
+def test_error_conventions(capi):
+    with pytest.raises(capi.GarB200Error):
+        capi.Solver(4, 2, horizon=5, nc0=6)          # nc0 > nx
+    with pytest.raises(capi.GarB200Error):
+        capi.Solver(4, 2, nth=1, horizon=5, num_legs=2)  # legs need nth == 0
+    s = capi.Solver(4, 2, horizon=5)
+    with pytest.raises(capi.GarB200Error) as e:
+        s.backward(1e-8, 1e-8)                         # no problem uploaded
+    assert e.value.code == capi.ERR_STATE
+    pp = generate_problems(1, 5, 4, 2, seed=0)
+    s.upload(pp)
+    with pytest.raises(capi.GarB200Error):
+        s.forward()                                    # forward before backward
+    # singular E is flagged, not silently wrong
+    pp.knots[0, 2, pp.layout.offsets["E"]: pp.layout.offsets["E"] + 16] = 0.0
+    s.upload(pp)
+    s.backward(1e-8, 1e-8)
+    with pytest.raises(capi.GarB200Error) as e:
+        s.synchronize()
+    assert e.value.code == capi.ERR_NUMERIC
+    assert s.get_flags()[0] & 1
+
+
+def test_device_generator_roundtrip(capi, oracle):
+    """bench data source: generate on device, download a sample, oracle on those very bytes."""
+    from aligator_swk_b200.synth import PackedProblems
+    from aligator_swk_b200.layout import KnotLayout
+    nx, nu, T, B, mu = 12, 4, 50, 300, 1e-11
+    s = capi.Solver(nx, nu, horizon=T, batch=B)
+    s.generate(seed=42, dist=0)
+    s.backward(mu, mu)
+    xs, us, vs, lb = s.forward()
+    assert (s.get_flags() == 0).all()
+    kkt = s.kkt_error(mu, mu)
+    assert kkt.max() < 1e-7
+    idx = [0, 1, 149, 299]
+    for b in idx:
+        knots, G0, g0 = s.download_packed(b, 1)
+        pp = PackedProblems(KnotLayout(nx, nu, 0, 0), T, nx, s.nu_t, s.nc_t, knots, G0, g0)
+        ref = oracle.prox_solve(pp, mu, mu)
+        assert relerr(xs[b], ref["xs"]) < RTOL and relerr(us[b], ref["us"]) < RTOL
+        assert relerr(lb[b], ref["lbdas"]) < RTOL
+    # distribution sanity (test_util.cpp:31-35): E ~ 1000 N(0,1), B ~ U[-1,1]
+    knots, _, _ = s.download_packed(0, 32)
+    o = KnotLayout(nx, nu, 0, 0).offsets
+    E = knots[:, :T, o["E"]: o["E"] + nx * nx]
+    Bm = knots[:, :T, o["B"]: o["B"] + nx * nu]
+    assert 900 < E.std() < 1100 and abs(E.mean()) < 20
+    assert Bm.min() >= -1 and Bm.max() <= 1 and 0.55 < Bm.std() < 0.6
