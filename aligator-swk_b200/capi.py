@@ -51,7 +51,7 @@ SYMBOLS = [
     "garb200_device_gains", "garb200_get_value", "garb200_get_initial", "garb200_get_flags",
     "garb200_get_refinement_steps", "garb200_collapse_feedback", "garb200_cycle_append",
     "garb200_kkt_error", "garb200_upload_trajectory", "garb200_kernel_launches", "garb200_last_timings",
-    "garb200_fp64_peak",
+    "garb200_fp64_peak", "garb200_timing_log_start", "garb200_timing_log_read",
 ]
 
 
@@ -95,6 +95,8 @@ def lib():
         L.garb200_kernel_launches.argtypes = [C.c_void_p]
         L.garb200_last_timings.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.garb200_fp64_peak.argtypes = [C.c_int, C.c_int, C.c_void_p]
+        L.garb200_timing_log_start.argtypes = [C.c_void_p, C.c_int]
+        L.garb200_timing_log_read.argtypes = [C.c_void_p] * 4
         L.garb200_create.argtypes = [C.c_void_p, C.c_void_p]
         L.garb200_upload_trajectory.argtypes = [C.c_void_p] * 5
         L.garb200_get_layouts.argtypes = [C.c_void_p] * 4
@@ -304,6 +306,17 @@ class Solver:
 
     def kernel_launches(self) -> int:
         return int(lib().garb200_kernel_launches(self._h))
+
+    def timing_log_start(self, capacity):
+        check(lib().garb200_timing_log_start(self._h, int(capacity)))
+        self._tcap = int(capacity)
+
+    def timing_log_read(self):
+        """-> (backward_ms[count], forward_ms[count]) device-event durations of the logged calls."""
+        b = np.zeros(self._tcap, np.float32); f = np.zeros(self._tcap, np.float32)
+        n = C.c_int(0)
+        check(lib().garb200_timing_log_read(self._h, _ptr(b), _ptr(f), C.byref(n)))
+        return b[: n.value].astype(np.float64), f[: n.value].astype(np.float64)
 
     def last_timings(self):
         a, b = C.c_float(0), C.c_float(0)

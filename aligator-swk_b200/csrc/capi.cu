@@ -36,6 +36,8 @@ struct garb200_solver {
   int64_t launches = 0;
   bool has_problem = false, did_backward = false, did_forward = false;
   cudaEvent_t ev[4]{};
+  std::vector<cudaEvent_t> tlog;   // timing log: 4 events per logged solve (bwd begin/end, fwd begin/end)
+  int tlog_cap = 0, tlog_bwd = 0, tlog_fwd = 0;
   size_t knots_doubles = 0;
   int nblk = 0;                  // blocks of the condensed system (2 * legs)
   size_t csys_len = 0;           // nc0 + (nblk-1) nx
@@ -82,6 +84,7 @@ void garb200_destroy(garb200_solver *s) {
   if (s->h_scratch) cudaFreeHost(s->h_scratch);
   if (s->h_cycle) cudaFreeHost(s->h_cycle);
   for (auto &e : s->ev) if (e) cudaEventDestroy(e);
+  for (auto &e : s->tlog) if (e) cudaEventDestroy(e);
   delete s;
 }
 
@@ -170,9 +173,6 @@ int garb200_create(const garb200_config *cfg, garb200_solver **out) {
     s->nblk = 2 * c.num_legs;
     s->csys_len = c.nc0 + (size_t)(s->nblk - 1) * n;
     const size_t nb = s->nblk, bb = n * n;
-    TRYB(dmalloc(s, &p.cdiag, B * nb * bb));
-    TRYB(dmalloc(s, &p.csuper, B * nb * bb));
-    TRYB(dmalloc(s, &p.csub, B * nb * bb));
     TRYB(dmalloc(s, &p.cdiagF, B * nb * bb));
     TRYB(dmalloc(s, &p.csubF, B * nb * bb));
     TRYB(dmalloc(s, &p.csubd, B * nb * n));
@@ -244,14 +244,34 @@ int garb200_get_layouts(const garb200_solver *s, garb200_knot_layout *knot,
 }
 
 // ---- problem data ----------------------------------------------------------------------
+// Packed knots between the caller's LOGICAL time order and the solver's physical (ring-
+// offset, see garb200_cycle_append) order: logical [0, T-shift) <-> physical [shift, T),
+// logical [T-shift, T) <-> physical [0, shift), the terminal knot never moves.
+static int copy_knots_rotated(garb200_solver *s, double *dev, double *host, int first, int count,
+                              cudaMemcpyKind kind) {
+  const DevParams &p = s->p;
+  const size_t ks = p.KL.stride, T = p.T, sh = p.shift, pitch = (T + 1) * ks * sizeof(double);
+  double *d0 = dev + (size_t)first * (T + 1) * ks;
+  auto seg = [&](size_t logical, size_t phys, size_t nk) -> cudaError_t {
+    if (nk == 0 || count == 0) return cudaSuccess;
+    double *d = d0 + phys * ks, *h = host + logical * ks;
+    return kind == cudaMemcpyHostToDevice
+               ? cudaMemcpy2DAsync(d, pitch, h, pitch, nk * ks * sizeof(double), count, kind, s->stream)
+               : cudaMemcpy2DAsync(h, pitch, d, pitch, nk * ks * sizeof(double), count, kind, s->stream);
+  };
+  if (sh == 0) { CK(seg(0, 0, T + 1)); return GARB200_OK; }
+  CK(seg(0, sh, T - sh));
+  CK(seg(T - sh, 0, sh));
+  CK(seg(T, T, 1));
+  return GARB200_OK;
+}
 int garb200_upload_packed(garb200_solver *s, const double *knots, const double *G0,
                           const double *g0) {
   if (!s || !knots) return fail(GARB200_ERR_INVALID, "null argument");
   CK(cudaSetDevice(s->cfg.device));
   const DevParams &p = s->p;
   const size_t B = p.batch, n = p.nx;
-  if (p.shift != 0) return fail(GARB200_ERR_STATE, "upload_packed after cycle_append: re-create the solver");
-  CK(cudaMemcpyAsync(p.knots, knots, s->knots_doubles * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  TRY(copy_knots_rotated(s, p.knots, const_cast<double *>(knots), 0, p.batch, cudaMemcpyHostToDevice));
   if (G0) CK(cudaMemcpyAsync(p.G0, G0, B * p.nc0 * n * sizeof(double), cudaMemcpyHostToDevice, s->stream));
   if (g0) CK(cudaMemcpyAsync(p.g0, g0, B * p.nc0 * sizeof(double), cudaMemcpyHostToDevice, s->stream));
   s->has_problem = true;
@@ -332,10 +352,9 @@ int garb200_download_packed(garb200_solver *s, int first, int count, double *kno
   if (!s) return fail(GARB200_ERR_INVALID, "null solver");
   const DevParams &p = s->p;
   if (first < 0 || count < 0 || first + count > p.batch) return fail(GARB200_ERR_INVALID, "range");
-  if (p.shift != 0) return fail(GARB200_ERR_STATE, "download_packed after cycle_append is not supported");
   CK(cudaSetDevice(s->cfg.device));
-  const size_t ps = (size_t)(p.T + 1) * p.KL.stride, n = p.nx;
-  if (knots) CK(cudaMemcpyAsync(knots, p.knots + first * ps, count * ps * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+  const size_t n = p.nx;
+  if (knots) TRY(copy_knots_rotated(s, p.knots, knots, first, count, cudaMemcpyDeviceToHost));
   if (G0) CK(cudaMemcpyAsync(G0, p.G0 + (size_t)first * p.nc0 * n, (size_t)count * p.nc0 * n * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
   if (g0) CK(cudaMemcpyAsync(g0, p.g0 + (size_t)first * p.nc0, (size_t)count * p.nc0 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
   CK(cudaStreamSynchronize(s->stream));
@@ -351,6 +370,8 @@ int garb200_backward(garb200_solver *s, double mudyn, double mueq) {
   p.mudyn = mudyn; p.mueq = mueq;
   CK(cudaMemsetAsync(p.flags, 0, (size_t)p.batch * sizeof(int32_t), s->stream));
   CK(cudaEventRecord(s->ev[0], s->stream));
+  const bool logb = s->tlog_bwd < s->tlog_cap;
+  if (logb) CK(cudaEventRecord(s->tlog[4 * s->tlog_bwd + 0], s->stream));
   int rc = launch_backward(p, s->stream);
   if (rc < 0) return fail(rc == -1 ? GARB200_ERR_INVALID : GARB200_ERR_CUDA,
                           std::string("backward launch failed: ") + cudaGetErrorString(cudaGetLastError()));
@@ -361,6 +382,7 @@ int garb200_backward(garb200_solver *s, double mudyn, double mueq) {
     s->launches += rc;
   }
   CK(cudaEventRecord(s->ev[1], s->stream));
+  if (logb) { CK(cudaEventRecord(s->tlog[4 * s->tlog_bwd + 1], s->stream)); s->tlog_bwd++; }
   s->did_backward = true;
   s->did_forward = false;
   return GARB200_OK;
@@ -373,12 +395,15 @@ int garb200_forward_device(garb200_solver *s, const double *d_theta, double *d_x
   CK(cudaSetDevice(s->cfg.device));
   const DevParams &p = s->p;
   CK(cudaEventRecord(s->ev[2], s->stream));
+  const bool logf = s->tlog_fwd < s->tlog_cap;
+  if (logf) CK(cudaEventRecord(s->tlog[4 * s->tlog_fwd + 2], s->stream));
   const int rc = launch_forward(p, (p.nth > 0 && p.num_legs < 2) ? d_theta : nullptr,
                                 d_xs ? d_xs : p.xs, d_us ? d_us : p.us, d_vs ? d_vs : p.vs,
                                 d_lbdas ? d_lbdas : p.lbdas, s->stream);
   if (rc < 0) return fail(rc == -1 ? GARB200_ERR_INVALID : GARB200_ERR_CUDA, "forward launch failed");
   s->launches += rc;
   CK(cudaEventRecord(s->ev[3], s->stream));
+  if (logf) { CK(cudaEventRecord(s->tlog[4 * s->tlog_fwd + 3], s->stream)); s->tlog_fwd++; }
   s->did_forward = (!d_xs && !d_us && !d_vs && !d_lbdas);
   return GARB200_OK;
 }
@@ -588,6 +613,30 @@ int garb200_last_timings(garb200_solver *s, float *backward_ms, float *forward_m
   CK(cudaStreamSynchronize(s->stream));
   if (backward_ms) { *backward_ms = 0.f; if (s->did_backward) CK(cudaEventElapsedTime(backward_ms, s->ev[0], s->ev[1])); }
   if (forward_ms) { *forward_ms = 0.f; if (s->did_forward) CK(cudaEventElapsedTime(forward_ms, s->ev[2], s->ev[3])); }
+  return GARB200_OK;
+}
+
+int garb200_timing_log_start(garb200_solver *s, int capacity) {
+  if (!s || capacity < 0) return fail(GARB200_ERR_INVALID, "bad argument");
+  CK(cudaSetDevice(s->cfg.device));
+  while ((int)s->tlog.size() < 4 * capacity) {
+    cudaEvent_t e;
+    CK(cudaEventCreate(&e));
+    s->tlog.push_back(e);
+  }
+  s->tlog_cap = capacity; s->tlog_bwd = s->tlog_fwd = 0;
+  return GARB200_OK;
+}
+
+int garb200_timing_log_read(garb200_solver *s, float *backward_ms, float *forward_ms, int *count) {
+  if (!s || !count) return fail(GARB200_ERR_INVALID, "null argument");
+  CK(cudaSetDevice(s->cfg.device));
+  CK(cudaStreamSynchronize(s->stream));
+  const int nb = s->tlog_bwd, nf = s->tlog_fwd;
+  for (int i = 0; i < nb && backward_ms; i++) CK(cudaEventElapsedTime(backward_ms + i, s->tlog[4 * i], s->tlog[4 * i + 1]));
+  for (int i = 0; i < nf && forward_ms; i++) CK(cudaEventElapsedTime(forward_ms + i, s->tlog[4 * i + 2], s->tlog[4 * i + 3]));
+  *count = nb < nf ? nb : nf;
+  s->tlog_cap = 0;
   return GARB200_OK;
 }
 

@@ -29,7 +29,8 @@ struct DevParams {
   double *xs, *us, *vs, *lbdas;   // solver-owned trajectories
   double *theta;                  // [batch][nth] device copy (forward)
   // condensed system of the parallel-in-time solver (leg mode), per problem:
-  double *cdiag, *csuper, *csub, *cdiagF, *csubF, *crhs, *csol, *cerr, *csubd;
+  // (blocks themselves are read in place from value / knot records; only factors are stored)
+  double *cdiagF, *csubF, *crhs, *csol, *cerr, *csubd;
   int *cpiv;
   int32_t *flags, *refine_steps;
   double mudyn, mueq;

@@ -1,0 +1,402 @@
+#!/usr/bin/env python
+"""bench.py — batched LQ solves/sec (ProxRiccati backward + forward) on B200.
+
+Contract (one JSON line on stdout, printed by rank 0):
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c2|c1b|c3|c4|c5] [--impl ours|reference]
+  N > 1: launched by torchrun, one rank per GPU; the batch dimension is sharded (no
+  collective inside the sweep); one NCCL gather of the trajectories per step (north_star).
+
+A "step" = one backward + forward over the whole per-GPU batch of synthetic problems.
+  value     solves/s with the problem already resident in HBM (device generator, seed 42)
+  e2e       solves/s through the C ABI with HOST buffers: H2D of the packed problem, sweep,
+            D2H of (xs, us, vs, lbdas), all inside the timed region
+  roofline  dominant kernel (backward sweep): algorithmic bytes / CUDA-event duration vs the
+            measured HBM peak (small-nx, HBM-bound) — flops vs measured FP64 peak also printed
+  cpu_baseline  the CPU oracle port (oracle/, OpenMP over problems) on a bounded sample
+`--impl reference` times that CPU port alone (the reference itself needs Eigen: not buildable
+here) on this repo's config/metric.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "oracle")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+MU = 1e-11  # bench/gar-riccati.cpp:26
+
+# BASELINE.json configs. batch = per-GPU batch (weak scaling: every rank gets the full config batch).
+WORKLOADS = {
+    "c2": dict(nx=12, nu=4, nc=0, nth=0, T=50, batch=16384, legs=0,
+               desc="configs[1]: 16384 independent random LQ problems nx=12 nu=4 T=50"),
+    "c1b": dict(nx=36, nu=12, nc=0, nth=0, T=100, batch=4096, legs=0,
+                desc="north_star target shape nx=36 nu=12 T=100, batch 4096"),
+    "c1": dict(nx=36, nu=12, nc=0, nth=0, T=100, batch=1, legs=0,
+               desc="configs[0]: single problem nx=36 nu=12 T=100 (latency)"),
+    "c3": dict(nx=36, nu=12, nc=6, nth=4, T=200, batch=4096, legs=0,
+               desc="configs[2]: nc=6 nth=4 nx=36 nu=12 T=200 batch 4096"),
+    "c4": dict(nx=36, nu=12, nc=0, nth=0, T=4096, batch=1, legs=64,
+               desc="configs[3]: parallel-in-time T=4096, 64 legs, single problem"),
+    "c5": dict(nx=76, nu=32, nc=0, nth=0, T=100, batch=1024, legs=0,
+               desc="configs[4]: Talos-shaped nx=76 nu=32 T=100 batch 1024"),
+}
+
+
+def flops_model(n, m, c, h, T, c0):
+    """dense op count of the reference algorithm per solve."""
+    fs = (17 * n**3 + 10 * n * n * m + 2 * m * m * n + (m + c) ** 3 / 3 + 2 * (m + c) ** 2 * (n + 1)
+          + 2 * n * n * c + 10 * n * n + 6 * n * m + 2 * n * c)
+    if h > 0:
+        fs += 8 * n * n * h + 8 * n * m * h + 2 * (m + c) ** 2 * h + 2 * h * h * (n + m) + 2 * h * (n + m)
+    ff = 2 * (m + c + 2 * n) * (n + h)
+    fi = (n + c0) ** 3 / 3 + 2 * (n + c0) ** 2 * (1 + h)
+    return T * (fs + ff) + fi, T * fs + fi, T * ff
+
+
+def bytes_model(n, m, c, h, T):
+    """algorithmic bytes per knot: in / gains / out (doubles * 8)."""
+    inn = 3 * n * n + 2 * n * m + m * m + 2 * n + m + c * (n + m + 1)
+    if h > 0:
+        inn += h * h + n * h + m * h + h
+    gains = (m + c + 2 * n) * (n + 1 + h)
+    out = 2 * n + m + c
+    return 8 * inn * (T + 1), 8 * gains * (T + 1), 8 * out * (T + 1)
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks + throttle reasons DURING the timed region (B200_PROFILING.md)."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        super().__init__(daemon=True)
+        self.device, self.rows, self._halt = device, [], threading.Event()
+
+    def run(self):
+        while not self._halt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.device), f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True,
+                                     timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.splitlines()[0].split(",")])
+            except Exception:
+                pass
+            self._halt.wait(0.1)
+
+    def stop(self):
+        self._halt.set()
+        self.join(timeout=6)
+        sm = [float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(self.rows)}
+
+
+def cpu_port_throughput(w, budget_s=12.0):
+    """Time the CPU oracle port (OpenMP over independent problems, all host cores) on a bounded
+    sample of the workload. -> (solves/s, cores, sample description)."""
+    import garb200_pkg
+    garb200_pkg.load()
+    from aligator_swk_b200.synth import generate_problems
+    import pyoracle as po
+    po.build()
+    cores = os.cpu_count() or 1
+    nx, nu, nc, nth, T, legs = w["nx"], w["nu"], w["nc"], w["nth"], w["T"], w["legs"]
+    rng = np.random.default_rng(3)
+
+    def run(nprob, reps):
+        pp = generate_problems(nprob, T, nx, nu, nc, nth, seed=42)
+        theta = rng.standard_normal(nth) if nth else None
+        secs, used = po.bench(pp, MU, MU, theta=theta, num_legs=legs, reps=reps, nthreads=0)
+        return secs, used
+
+    if legs >= 2 or w["batch"] == 1:
+        secs, used = run(1, 1)                      # warm-up
+        reps = int(max(3, min(200, budget_s / max(secs, 1e-6))))
+        secs, used = run(1, reps)
+        return reps / secs, used, f"1 problem x {reps} repetitions, {used} threads" + (f" ({legs} legs)" if legs >= 2 else "")
+    n0 = max(cores, 8)
+    secs, used = run(n0, 1)
+    per = secs / n0 * used                          # core-seconds per solve
+    nprob = int(max(n0, min(w["batch"], 4096, budget_s * used / per / 2)))
+    reps = 2
+    secs, used = run(nprob, reps)
+    return nprob * reps / secs, used, f"{nprob} of {w['batch']} problems x {reps} repetitions, OpenMP over problems, {used} threads"
+
+
+def reference_arm(args, w, rank, world):
+    """--impl reference: the reference's CPU path.  The real reference needs Eigen 3.4 (absent,
+    no network): the Eigen-free oracle port is timed instead (kind = "port")."""
+    if rank != 0:
+        return
+    per_step = []
+    sample = ""
+    cores = 1
+    budget = max(3.0, min(15.0, 60.0 / max(1, args.steps + args.warmup)))
+    for i in range(args.warmup + args.steps):
+        v, cores, sample = cpu_port_throughput(w, budget_s=budget)
+        if i >= args.warmup:
+            per_step.append(v)
+    v = float(np.mean(per_step))
+    ms = 1e3 * w["batch"] * world / v
+    line = {
+        "impl": "reference", "metric": "batched LQ solves/sec (bwd+fwd)", "value": v, "unit": "solves/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": workload_config(args.workload, w, world),
+        "knots_per_s": v * (w["T"] + 1),
+        "cpu_baseline": {"value": v, "unit": "solves/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(name, w, world):
+    return {"workload": f"{name}: {w['desc']}", "nx": w["nx"], "nu": w["nu"], "nc": w["nc"], "nth": w["nth"],
+            "horizon": w["T"], "batch_per_gpu": w["batch"], "global_batch": w["batch"] * world,
+            "num_legs": w["legs"], "mu": MU, "dist": "ref (tests/gar/test_util.cpp distributions, distinct knots)",
+            "l2_policy": "inputs larger than L2 (126 MB) for the batched workloads; none needed for latency rows",
+            "parallelism": f"batch-sharded x{world}"}
+
+
+def gpu_arm(args, w, rank, world, local_rank):
+    import torch
+    import garb200_pkg
+    garb200_pkg.load()
+    from aligator_swk_b200 import capi
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist = dist_mod
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    nx, nu, nc, nth, T, B, legs = w["nx"], w["nu"], w["nc"], w["nth"], w["T"], w["batch"], w["legs"]
+    K, W = args.steps, args.warmup
+    s = capi.Solver(nx, nu, nc, nth, horizon=T, batch=B, num_legs=legs, device=local_rank)
+    s.generate(seed=42 + rank, dist=0)
+    s.synchronize_stream_only()
+    theta_d = None
+    if nth:
+        theta_t = torch.randn(B, nth, dtype=torch.float64, device="cuda", generator=torch.Generator("cuda").manual_seed(1))
+        theta_d = theta_t.data_ptr()
+    torch.cuda.synchronize()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # trajectory gather to rank 0 (north_star: a single NCCL gather, no collective inside the
+    # sweep): the forward kernel writes straight into the send buffer.
+    send = recv = None
+    out_ptrs = {}
+    if dist is not None:
+        sizes = [B * (T + 1) * nx, B * (T + 1) * nu, B * (T + 1) * nc, B * (nx + T * nx)]
+        send = torch.empty(sum(sizes), dtype=torch.float64, device="cuda")
+        recv = [torch.empty_like(send) for _ in range(world)] if rank == 0 else None
+        off = 0
+        for name, sz in zip(("d_xs", "d_us", "d_vs", "d_lbdas"), sizes):
+            out_ptrs[name] = send.data_ptr() + 8 * off
+            off += sz
+
+    def step_device():
+        s.backward(MU, MU)
+        s.forward_device(d_theta=theta_d, **out_ptrs)
+
+    def gather():
+        if dist is not None:
+            dist.gather(send, recv, dst=0)
+
+    # ---- value: device-resident inputs -> device-resident outputs -----------------------
+    for _ in range(W):
+        step_device(); gather()
+    barrier()
+    l0 = s.kernel_launches()
+    s.timing_log_start(K)
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        step_device(); gather()
+    e1.record()
+    barrier()
+    clocks = sampler.stop() if sampler else None
+    ms_total = e0.elapsed_time(e1)
+    launches = s.kernel_launches() - l0
+    bwd_ms, fwd_ms = s.timing_log_read()
+    s.forward_device(d_theta=theta_d)    # into the solver-owned trajectory (scored below)
+    s.synchronize()                      # raises if any problem flagged a numerical failure
+    kkt = s.kkt_error(MU, MU, theta=None if not nth else theta_t.cpu().numpy())
+    t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    ms_step = ms_total / K
+    value = B * world / (ms_step * 1e-3)
+
+    # ---- e2e: host buffers through the C ABI, H2D + D2H inside the timed region ----------
+    e2e = None
+    if not args.no_e2e:
+        e2e = e2e_run(torch, capi, s, w, K, W, dist, world, theta_t.cpu().numpy() if nth else None)
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+    # ---- roofline of the dominant kernel (backward sweep) --------------------------------
+    c0 = nx
+    f_all, f_bwd, f_fwd = flops_model(nx, nu, nc, nx if legs >= 2 else nth, T, c0)
+    b_in, b_gain, b_out = bytes_model(nx, nu, nc, nx if legs >= 2 else nth, T)
+    bwd = float(np.mean(bwd_ms)) * 1e-3
+    fwd = float(np.mean(fwd_ms)) * 1e-3
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    fp64_dfma, fp64_dmma = capi.fp64_peak(local_rank, 0), capi.fp64_peak(local_rank, 1)
+    fp64_peak = max(fp64_dfma, fp64_dmma)
+    ach_gbs = B * (b_in + b_gain) / bwd / 1e9
+    ach_tf = B * f_bwd / bwd / 1e12
+    hbm_bound = (ach_gbs / hbm_peak) >= (ach_tf / fp64_peak)
+    roof = {"kernel": "backward_kernel", "bound": "hbm" if hbm_bound else "fp64",
+            "achieved": ach_gbs if hbm_bound else ach_tf, "peak": hbm_peak if hbm_bound else fp64_peak,
+            "unit": "GB/s" if hbm_bound else "TFLOP/s",
+            "frac": (ach_gbs / hbm_peak) if hbm_bound else (ach_tf / fp64_peak), "traffic": None,
+            "peak_source": ("MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650 GB/s") if hbm_bound
+            else "measured in this run: max(DFMA loop, DMMA m8n8k4 loop)",
+            "hbm_gbs": ach_gbs, "hbm_frac": ach_gbs / hbm_peak, "fp64_tflops": ach_tf, "fp64_frac": ach_tf / fp64_peak,
+            "fp64_peak_dfma": fp64_dfma, "fp64_peak_dmma": fp64_dmma,
+            "kernel_ms": bwd * 1e3, "forward_kernel_ms": fwd * 1e3,
+            "forward_gbs": B * (b_gain + b_out) / fwd / 1e9,
+            "algorithmic_bytes_per_launch": B * (b_in + b_gain), "algorithmic_flops_per_launch": B * f_bwd,
+            "kernel_share_of_step": (bwd * 1e3) / ms_step}
+    cpu_v, cores, sample = cpu_port_throughput(w, budget_s=args.cpu_budget)
+    line = {
+        "metric": "batched LQ solves/sec (bwd+fwd)", "value": value, "unit": "solves/s", "n_gpus": world,
+        "steps": K, "warmup": W, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args.workload, w, world),
+        "knots_per_s": value * (T + 1),
+        "kkt_max": {"dyn": float(kkt[:, 0].max()), "cstr": float(kkt[:, 1].max()), "dual": float(kkt[:, 2].max())},
+        "roofline": roof,
+        "cpu_baseline": {"value": cpu_v, "unit": "solves/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+        "collective": None if world == 1 else "one NCCL gather of (xs,us,vs,lbdas) to rank 0 per step",
+    }
+    print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def e2e_run(torch, capi, s_dev, w, K, W, dist, world, theta):
+    """Same metric through the C ABI with HOST (pinned) buffers: per step H2D of the packed
+    problem, backward, forward, D2H of the trajectories."""
+    nx, nu, nc, nth, T, B, legs = w["nx"], w["nu"], w["nc"], w["nth"], w["T"], w["batch"], w["legs"]
+    stride = s_dev.download_packed(0, 1)[0].shape[-1]
+    per_problem = (T + 1) * stride * 8
+    Be = int(min(B, max(1, (8 << 30) // per_problem)))       # cap pinned staging at 8 GiB
+    note = None if Be == B else f"e2e on a {Be}-problem slice (pinned staging capped at 8 GiB)"
+
+    def pinned(*shape):
+        return torch.empty(shape, dtype=torch.float64, pin_memory=True).numpy()
+
+    knots, G0, g0 = pinned(Be, T + 1, stride), pinned(Be, nx * nx), pinned(Be, nx)
+    k, a, b = s_dev.download_packed(0, Be)
+    knots[:], G0[:], g0[:] = k, a, b
+    del k, a, b
+    s = s_dev if Be == B else capi.Solver(nx, nu, nc, nth, horizon=T, batch=Be, num_legs=legs, device=torch.cuda.current_device())
+    out = (pinned(Be, T + 1, nx), pinned(Be, T + 1, max(nu, 1))[:, :, :nu], pinned(Be, T + 1, max(nc, 1))[:, :, :nc],
+           pinned(Be, nx + T * nx))
+    if nu == 0 or nc == 0:
+        out = tuple(np.ascontiguousarray(o) for o in out)
+    th = None if theta is None else np.ascontiguousarray(theta[:Be])
+
+    def step():
+        s.upload_packed(knots, G0, g0)
+        s.backward(MU, MU)
+        s.forward(th, out=out)
+
+    for _ in range(W):
+        step()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item()) / K
+    h2d = knots.nbytes + G0.nbytes + g0.nbytes + (th.nbytes if th is not None else 0)
+    d2h = sum(o.nbytes for o in out)
+    r = {"value": Be * world / (ms * 1e-3), "unit": "solves/s", "h2d_bytes_per_step": int(h2d),
+         "d2h_bytes_per_step": int(d2h), "ms_per_step": ms, "batch_per_gpu": Be}
+    if note:
+        r["note"] = note
+    if s is not s_dev:
+        s.close()
+    return r
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=0, help="override the per-GPU batch")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU-port timing")
+    args = ap.parse_args()
+    w = dict(WORKLOADS[args.workload])
+    if args.batch > 0:
+        w["batch"] = args.batch
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world == 1 and args.gpus > 1:
+        # not launched by torchrun: re-launch ourselves one rank per GPU
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 2000), os.path.abspath(__file__)] + sys.argv[1:]
+        raise SystemExit(subprocess.call(cmd))
+    if args.impl == "reference":
+        reference_arm(args, w, rank, world)
+        return
+    gpu_arm(args, w, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -183,6 +183,11 @@ int garb200_upload_trajectory(garb200_solver *s, const double *xs, const double 
 int64_t garb200_kernel_launches(const garb200_solver *s);
 /* device-event time (ms) of the last backward and forward kernels sequences */
 int garb200_last_timings(garb200_solver *s, float *backward_ms, float *forward_ms);
+/* Per-call device timing log (bench / roofline): after _start, every backward and forward
+ * brackets its kernels with CUDA events on the solver stream (up to `capacity` of each);
+ * _read synchronises, returns the per-call durations in ms and stops logging. */
+int garb200_timing_log_start(garb200_solver *s, int capacity);
+int garb200_timing_log_read(garb200_solver *s, float *backward_ms, float *forward_ms, int *count);
 /* FP64 micro-benchmarks used as roofline denominators: returns TFLOP/s
  * kind 0 = DFMA register loop, 1 = DMMA mma.sync.m8n8k4.f64 loop */
 int garb200_fp64_peak(int device, int kind, double *tflops);

@@ -18,24 +18,47 @@ _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int)
 
 
+def _cpu_stamp() -> str:
+    """The .so is built -march=native and travels with the repo snapshot to other hosts:
+    rebuild when the host CPU (model + ISA flags) differs from the one it was built on."""
+    import hashlib
+    model = flags = ""
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name") and not model:
+                model = line
+            elif line.startswith("flags") and not flags:
+                flags = line
+            if model and flags:
+                break
+    except OSError:
+        pass
+    return hashlib.sha1((model + flags).encode()).hexdigest()
+
+
 def build(force: bool = False) -> str:
     so = os.path.join(_HERE, "libgar_oracle.so")
+    stamp_file = os.path.join(_HERE, "libgar_oracle.so.cpu")
     srcs = [os.path.join(_HERE, f) for f in os.listdir(_HERE) if f.endswith((".cpp", ".hpp"))]
     srcs.append(os.path.join(_HERE, "..", "include", "garb200_layout.h"))
     stale = (not os.path.exists(so)) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs)
+    stamp = _cpu_stamp()
+    try:
+        stale = stale or open(stamp_file).read().strip() != stamp
+    except OSError:
+        stale = True
     if force or stale:
         subprocess.check_call(["make", "-C", _HERE, "-B", "libgar_oracle.so"],
                               stdout=subprocess.DEVNULL)
+        with open(stamp_file, "w") as f:
+            f.write(stamp)
     return so
 
 
 def lib():
     global _LIB
     if _LIB is None:
-        so = os.path.join(_HERE, "libgar_oracle.so")
-        if not os.path.exists(so):
-            build()
-        _LIB = C.CDLL(so)
+        _LIB = C.CDLL(build())
         _LIB.gar_oracle_bench.restype = C.c_double
     return _LIB
 

@@ -211,3 +211,87 @@ def test_device_generator_roundtrip(capi, oracle):
     Bm = knots[:, :T, o["B"]: o["B"] + nx * nu]
     assert 900 < E.std() < 1100 and abs(E.mean()) < 20
     assert Bm.min() >= -1 and Bm.max() <= 1 and 0.55 < Bm.std() < 0.6
+
+
+LEG_CASES = [
+    # nx, nu, nc, T, legs, batch, mu
+    (32, 12, 0, 50, 6, 2, 1e-9),      # parallel_solver_class (tests/gar/parallel.cpp:199-271)
+    (4, 2, 0, 11, 2, 3, 1e-9),
+    (12, 4, 0, 50, 5, 4, 1e-10),
+    (36, 12, 0, 127, 8, 1, 1e-9),
+    (8, 3, 2, 20, 3, 2, 1e-8),
+    (6, 2, 0, 7, 8, 2, 1e-9),         # one-knot legs
+]
+
+
+@pytest.mark.parametrize("case", LEG_CASES, ids=lambda c: "nx%d_nu%d_nc%d_T%d_J%d_B%d_%g" % c)
+def test_parallel_in_time_parity(capi, oracle, case):
+    """ParallelRiccatiSolver on the GPU (legs = CTAs): serial == parallel <= 1e-10
+    (tests/gar/parallel.cpp:243-260) and == the oracle's restated parallel solver."""
+    nx, nu, nc, T, J, B, mu = case
+    pp = generate_problems(B, T, nx, nu, nc, 0, seed=nx + T + J, dist="explicit")
+    s, xs, us, vs, lb = solve_gpu(capi, pp, mu, num_legs=J)
+    assert (s.get_flags() == 0).all()
+    kkt = s.kkt_error(mu, mu)
+    for b in range(B):
+        ser = oracle.prox_solve(pp, mu, mu, b=b)
+        par = oracle.parallel_solve(pp, mu, mu, J, b=b)
+        assert kkt[b].max() <= max(1e-10, 100 * par["kkt"].max()), (kkt[b], par["kkt"])
+        scale_x = max(np.abs(ser["xs"]).max(), 1.0)
+        scale_l = max(np.abs(ser["lbdas"]).max(), 1.0)
+        assert np.abs(xs[b] - ser["xs"]).max() <= 1e-10 * scale_x
+        assert np.abs(lb[b] - ser["lbdas"]).max() <= 1e-9 * scale_l
+        assert relerr(xs[b], par["xs"]) < 1e-9 and relerr(us[b], par["us"]) < 1e-9
+    # collapseFeedback (parallel-solver.hpp:55-66)
+    g_before = s.get_gains(0, 0)[1].copy()
+    s.collapse_feedback()
+    g_after = s.get_gains(0, 0)[1]
+    ref = oracle.parallel_solve(pp, mu, mu, J, collapse=True, b=0)
+    G = GainLayout(nx, nu, nc, nx)
+    rff, rfb, rfth = G.unpack(ref["gains"][0], pp.nu_t[0], pp.nc_t[0])
+    assert np.abs(g_after - rfb).max() <= 1e-8 * max(np.abs(rfb).max(), 1.0)
+    assert np.abs(g_after[:nu] - g_before[:nu]).max() > 0
+    s.close()
+
+
+def test_cycle_append(capi, oracle):
+    """cycleAppend (proximal-riccati.hxx:80-88, mpc-util.hpp:17-22): factor storage rotates
+    left over [0, N), the new knot becomes knot N-1, and the next solve sees the rotated problem."""
+    nx, nu, T, B, mu = 4, 2, 6, 3, 1e-10
+    pp = generate_problems(B, T, nx, nu, seed=5)
+    extra = generate_problems(1, 1, nx, nu, seed=6)
+    s = capi.Solver.for_problems(pp)
+    s.upload(pp)
+    s.backward(mu, mu)
+    g0 = s.download_gains()
+    L = pp.layout
+    rec = np.ascontiguousarray(extra.knots[0, 0])
+    o = L.offsets
+    view = capi.KnotView()
+    view.nu, view.nc = nu, 0
+    keep = {}
+    for name in ("Q", "S", "R", "q", "r", "A", "B", "E", "f"):
+        r, c = L.shapes()[name]
+        keep[name] = np.ascontiguousarray(rec[o[name]: o[name] + r * c])
+        setattr(view, name, keep[name].ctypes.data_as(capi._dp))
+    for rep in range(2):     # twice: the ring offset accumulates
+        s.cycle_append([view], shared=True)
+        g1 = s.download_gains()
+        assert np.array_equal(g1[:, : T - 1], g0[:, 1:T]) and not g1[:, T - 1].any()
+        assert np.array_equal(g1[:, T], g0[:, T])
+        knots = pp.knots.copy()
+        knots[:, : T - 1] = pp.knots[:, 1:T]
+        knots[:, T - 1] = rec
+        pp = type(pp)(L, T, pp.nc0, pp.nu_t, pp.nc_t, knots, pp.G0, pp.g0)
+        k2, _, _ = s.download_packed(0, B)
+        assert np.array_equal(k2, knots)
+        s.backward(mu, mu)
+        xs, us, vs, lb = s.forward()
+        compare_traj(oracle, pp, mu, xs, us, vs, lb)
+        g0 = s.download_gains()
+    # a full re-upload after cycling lands in the rotated slots too
+    s.upload(pp)
+    s.backward(mu, mu)
+    xs, us, vs, lb = s.forward()
+    compare_traj(oracle, pp, mu, xs, us, vs, lb)
+    s.close()
