@@ -16,6 +16,7 @@ _LIB = None
 
 OK, ERR_INVALID, ERR_CUDA, ERR_NUMERIC, ERR_STATE = 0, 1, 2, 3, 4
 STORE_ALL_VALUES = 1
+FORCE_GENERIC = 2
 
 _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int)
@@ -52,6 +53,7 @@ SYMBOLS = [
     "garb200_get_refinement_steps", "garb200_collapse_feedback", "garb200_cycle_append",
     "garb200_kkt_error", "garb200_upload_trajectory", "garb200_kernel_launches", "garb200_last_timings",
     "garb200_fp64_peak", "garb200_timing_log_start", "garb200_timing_log_read",
+    "garb200_used_fast_path",
 ]
 
 
@@ -95,6 +97,7 @@ def lib():
         L.garb200_kernel_launches.argtypes = [C.c_void_p]
         L.garb200_last_timings.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.garb200_fp64_peak.argtypes = [C.c_int, C.c_int, C.c_void_p]
+        L.garb200_used_fast_path.argtypes = [C.c_void_p]
         L.garb200_timing_log_start.argtypes = [C.c_void_p, C.c_int]
         L.garb200_timing_log_read.argtypes = [C.c_void_p] * 4
         L.garb200_create.argtypes = [C.c_void_p, C.c_void_p]
@@ -306,6 +309,9 @@ class Solver:
 
     def kernel_launches(self) -> int:
         return int(lib().garb200_kernel_launches(self._h))
+
+    def used_fast_path(self) -> bool:
+        return bool(lib().garb200_used_fast_path(self._h))
 
     def timing_log_start(self, capacity):
         check(lib().garb200_timing_log_start(self._h, int(capacity)))

@@ -34,7 +34,7 @@ struct garb200_solver {
   double *h_cycle = nullptr;     // pinned [batch][kstride] for cycleAppend
   double *d_kkt_out = nullptr;
   int64_t launches = 0;
-  bool has_problem = false, did_backward = false, did_forward = false;
+  bool has_problem = false, did_backward = false, did_forward = false, used_fast = false;
   cudaEvent_t ev[4]{};
   std::vector<cudaEvent_t> tlog;   // timing log: 4 events per logged solve (bwd begin/end, fwd begin/end)
   int tlog_cap = 0, tlog_bwd = 0, tlog_fwd = 0;
@@ -153,6 +153,9 @@ int garb200_create(const garb200_config *cfg, garb200_solver **out) {
   TRYB(dmalloc(s, &p.g0, B * c.nc0));
   TRYB(dmalloc(s, &p.gains, B * (T + 1) * p.GL.stride));
   TRYB(dmalloc(s, &p.values, B * p.nslots * p.VL.stride));
+  p.einv = nullptr;
+  if (!(c.flags & GARB200_FORCE_GENERIC) && fast_path_available(c.nx, c.nu, c.nc, c.nth, c.num_legs))
+    TRYB(dmalloc(s, &p.einv, B * (size_t)T * n * n));
   TRYB(dmalloc(s, &p.kkt0_ff, B * (n + c.nc0)));
   TRYB(dmalloc(s, &p.kkt0_fth, B * (n + c.nc0) * c.nth));
   TRYB(dmalloc(s, &p.thGrad, B * c.nth));
@@ -372,7 +375,9 @@ int garb200_backward(garb200_solver *s, double mudyn, double mueq) {
   CK(cudaEventRecord(s->ev[0], s->stream));
   const bool logb = s->tlog_bwd < s->tlog_cap;
   if (logb) CK(cudaEventRecord(s->tlog[4 * s->tlog_bwd + 0], s->stream));
-  int rc = launch_backward(p, s->stream);
+  int rc = (p.einv != nullptr) ? launch_backward_fast(p, s->nu_t.data(), s->nc_t.data(), s->stream) : -3;
+  s->used_fast = (rc >= 0);
+  if (rc == -3) rc = launch_backward(p, s->stream);
   if (rc < 0) return fail(rc == -1 ? GARB200_ERR_INVALID : GARB200_ERR_CUDA,
                           std::string("backward launch failed: ") + cudaGetErrorString(cudaGetLastError()));
   s->launches += rc;
@@ -615,6 +620,8 @@ int garb200_last_timings(garb200_solver *s, float *backward_ms, float *forward_m
   if (forward_ms) { *forward_ms = 0.f; if (s->did_forward) CK(cudaEventElapsedTime(forward_ms, s->ev[2], s->ev[3])); }
   return GARB200_OK;
 }
+
+int garb200_used_fast_path(const garb200_solver *s) { return s && s->used_fast ? 1 : 0; }
 
 int garb200_timing_log_start(garb200_solver *s, int capacity) {
   if (!s || capacity < 0) return fail(GARB200_ERR_INVALID, "bad argument");

@@ -24,6 +24,7 @@ struct DevParams {
   double *knots;                  // [batch][T+1][KL.stride]   (physical time order)
   double *G0, *g0;                // [batch][nc0*nx], [batch][nc0]
   double *gains;                  // [batch][T+1][GL.stride]   (physical time order)
+  double *einv;                   // [batch][T][nx*nx] E^{-1} of every knot (fast path pre-pass) or nullptr
   double *values;                 // [batch][nslots][VL.stride]
   double *kkt0_ff, *kkt0_fth, *thGrad, *thHess;  // per problem
   double *xs, *us, *vs, *lbdas;   // solver-owned trajectories
@@ -57,6 +58,9 @@ struct LaunchCfg { int threads; size_t smem; int grid; };
 
 // launchers (each returns the number of kernels it launched, < 0 on error)
 int launch_backward(const DevParams &p, cudaStream_t st);
+// dimension-specialised sweep (sweep_fast.cu): -3 = no specialisation for these dims
+int launch_backward_fast(const DevParams &p, const int *h_nu_t, const int *h_nc_t, cudaStream_t st);
+bool fast_path_available(int nx, int nu, int nc, int nth, int num_legs);
 int launch_forward(const DevParams &p, const double *d_theta, double *xs, double *us, double *vs,
                    double *lbdas, cudaStream_t st);
 int launch_condensed(const DevParams &p, cudaStream_t st);

@@ -1,0 +1,353 @@
+// sweep_fast.cu — dimension-specialised proximal Riccati backward sweep (sm_100a).
+//
+// Same algorithm as backward.cu (the generic kernel), restated for compile-time
+// (NX, NU, NC) with nth = 0, terminal knot nu = nc = 0 — the shapes of the BASELINE configs:
+//   einv_kernel    Einv_t = PartialPivLU(E_t).solve(I) for EVERY (problem, knot) in one
+//                  embarrassingly parallel pre-pass (riccati-kernel.hxx:172-174).  E_t is
+//                  input data, so its inversion does not belong on the sequential chain.
+//   sweep_kernel   terminalSolve / stageKernelSolve / initial stage
+//                  (riccati-kernel.hxx:90-150, 167-250; proximal-riccati.hxx:44-62), one CTA
+//                  (NW warps) per problem, knot record + Einv staged by 1-D TMA bulk copies,
+//                  all n^3 contractions on the FP64 tensor pipe (DMMA), GEMVs riding along
+//                  as an extra column of the GEMM they belong to.
+#include "fast.cuh"
+#include "kernels.cuh"
+
+namespace garb200 {
+
+// ---- pre-pass: batched inverse of E ------------------------------------------------------
+template <int N, int WPB>
+__global__ void __launch_bounds__(32 * WPB) einv_kernel(const DevParams p) {
+  extern __shared__ __align__(16) double sm[];
+  constexpr int LDW = 2 * N + 1;
+  constexpr int PER = N * LDW + ((N + 1) / 2 + 1);     // work array + pivots (ints)
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long total = (long long)p.batch * p.T;
+  const long long w = (long long)blockIdx.x * WPB + warp;
+  if (w >= total) return;
+  const int b = (int)(w / p.T), t = (int)(w % p.T);
+  double *W = sm + (size_t)warp * PER;
+  int *piv = reinterpret_cast<int *>(W + N * LDW);
+  const double *Eg = p.knots + ((size_t)b * (p.T + 1) + phys_t(p, t)) * p.KL.stride + p.KL.E;
+  double *Xg = p.einv + ((size_t)b * p.T + phys_t(p, t)) * (size_t)(N * N);
+  const bool ok = lu_inverse_warp<N>(lane, Eg, W, piv, Xg);
+  if (!ok && lane == 0) atomicOr(reinterpret_cast<int *>(p.flags) + b, GARB200_FLAG_LU_SINGULAR);
+}
+
+// ---- shared-memory plan of the sweep (doubles) ---------------------------------------------
+template <int NX, int NU, int NC> struct FastPlan {
+  static constexpr int n = NX, m = NU, c = NC, s = NU + NC;
+  static constexpr int r2(int x) { return (x + 1) & ~1; }
+  // packed knot record (same offsets as garb200_make_knot_layout(NX, NU, NC, 0))
+  static constexpr int oQ = 0, oS = r2(oQ + n * n), oR = r2(oS + n * m), oq = r2(oR + m * m),
+                       orr = r2(oq + n), oA = r2(orr + m), oB = r2(oA + n * n), oE = r2(oB + n * m),
+                       of = r2(oE + n * n), oC = r2(of + n), oD = r2(oC + c * n), od = r2(oD + c * m),
+                       kstride = r2(od + c);
+  static_assert(oS == oQ + n * n && oB == oA + n * n, "[Q|S] and [A|B] must be contiguous (even n*n)");
+  static constexpr int nrows = m + c + 2 * n;
+  static constexpr int gff = 0, gfb = r2(nrows), gstride = r2(gfb + nrows * n);
+  // smem
+  static constexpr int rec = 0;
+  static constexpr int X1 = r2(rec + kstride);          // n x (n+1)
+  static constexpr int P = r2(X1 + n * (n + 1));        // n x (n+1): [P | pvec] / [Vxx | vx] / [A_pre | tv]
+  static constexpr int BtV = r2(P + n * (n + 1));       // m x (n+1)
+  static constexpr int kkt = r2(BtV + m * (n + 1));     // s x s
+  static constexpr int ksub = r2(kkt + s * s);          // max(s, 2n) + 2
+  static constexpr int KS = (s > 2 * n ? s : 2 * n) + 2;
+  static constexpr int dinv = r2(ksub + KS);            // n
+  static constexpr int rhat = r2(dinv + n);             // s  (A^T vx, B^T vx scratch: n + m)
+  static constexpr int atvx = r2(rhat + s);             // n + m
+  static constexpr int G = r2(atvx + n + m);            // gains staging record
+  static constexpr int ints = r2(G + gstride);          // pivots: KS ints
+  static constexpr int bar = r2(ints + (KS + 1) / 2);
+  static constexpr int total = bar + 2;
+};
+
+template <int NX, int NU, int NC, int NW>
+__global__ void __launch_bounds__(32 * NW) sweep_kernel(const DevParams p) {
+  extern __shared__ __align__(16) double sm[];
+  using PL = FastPlan<NX, NU, NC>;
+  constexpr int n = NX, m = NU, c = NC, s = NU + NC, NT = 32 * NW;
+  constexpr int rK = 0, rZ = m, rL = m + c, rA = m + c + n;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.x;
+  const int T = p.T;
+  const double mudyn = p.mudyn, mueq = p.mueq;
+  double *rec = sm + PL::rec;
+  double *Q = rec + PL::oQ, *S = rec + PL::oS, *R = rec + PL::oR, *qv = rec + PL::oq, *rv = rec + PL::orr;
+  double *A = rec + PL::oA, *B = rec + PL::oB, *Einv = rec + PL::oE, *f = rec + PL::of;
+  double *C = rec + PL::oC, *D = rec + PL::oD, *d = rec + PL::od;
+  double *X1 = sm + PL::X1, *P = sm + PL::P, *BtV = sm + PL::BtV, *kkt = sm + PL::kkt;
+  double *ksub = sm + PL::ksub, *dinv = sm + PL::dinv, *atvx = sm + PL::atvx, *Gs = sm + PL::G;
+  double *pv = P + n * n;         // column n of the augmented P block
+  double *x1v = X1 + n * n;       // column n of the augmented X1 block
+  double *btvx = BtV + m * n;     // column n of BtV: B^T vx
+  double *ff = Gs + PL::gff, *fb = Gs + PL::gfb;
+  int *kpiv = reinterpret_cast<int *>(sm + PL::ints);
+  uint64_t *bar = reinterpret_cast<uint64_t *>(sm + PL::bar);
+  int flags = 0;
+
+  if (tid == 0) { mbar_init(bar, 1); fence_mbar_init(); }
+  for (int e = tid; e < PL::gstride; e += NT) Gs[e] = 0.0;
+  cta_sync<NT>();
+  uint32_t phase = 0;
+  const size_t pbase = (size_t)b * (T + 1);
+  auto issue_load = [&](int t) {      // thread 0 only
+    const int pt = phys_t(p, t);
+    const double *src = p.knots + (pbase + pt) * PL::kstride;
+    fence_proxy_async();
+    if (t == T) {
+      mbar_expect_tx(bar, (uint32_t)PL::kstride * 8u);
+      tma_load_1d(rec, src, (uint32_t)PL::kstride * 8u, bar);
+    } else {
+      mbar_expect_tx(bar, (uint32_t)PL::kstride * 8u);
+      tma_load_1d(rec, src, (uint32_t)PL::oE * 8u, bar);
+      tma_load_1d(Einv, p.einv + ((size_t)b * T + pt) * (size_t)(n * n), (uint32_t)(n * n) * 8u, bar);
+      tma_load_1d(rec + PL::of, src + PL::of, (uint32_t)(PL::kstride - PL::of) * 8u, bar);
+    }
+  };
+  auto store_gains = [&](int t) {     // all threads; Gs complete
+    fence_proxy_async();
+    cta_sync<NT>();
+    if (tid == 0) {
+      tma_store_1d(p.gains + (pbase + phys_t(p, t)) * p.GL.stride, Gs, (uint32_t)PL::gstride * 8u);
+      tma_store_commit();
+    }
+  };
+  auto store_value = [&](int t) {     // [P | pv] is the value function of knot t
+    const int slot = p.store_all_values ? t : (t == 0 ? 0 : -1);
+    if (slot < 0) return;
+    double *v = p.values + ((size_t)b * p.nslots + slot) * p.VL.stride;
+    for (int e = tid; e < n * n; e += NT) v[p.VL.Pmat + e] = P[e];
+    for (int i = tid; i < n; i += NT) v[p.VL.pvec + i] = pv[i];
+    if (t == 0 && p.store_all_values) {                       // proximal-riccati.hxx:39-42
+      for (int e = tid; e < n * n; e += NT) v[p.VL.Vxx + e] = P[e];
+      for (int i = tid; i < n; i += NT) v[p.VL.vx + i] = pv[i];
+    }
+  };
+
+  // ---- terminal knot (nu = nc = 0): Pmat = Q, pvec = q, empty gains  (riccati-kernel.hxx:90-150)
+  if (tid == 0) issue_load(T);
+  mbar_wait(bar, phase); phase ^= 1;
+  for (int e = tid; e < n * n; e += NT) P[e] = Q[e];
+  for (int i = tid; i < n; i += NT) pv[i] = qv[i];
+  store_gains(T);
+  store_value(T);
+  fence_proxy_async();
+  cta_sync<NT>();
+
+#pragma unroll 1
+  for (int t = T - 1; t >= 0; t--) {
+    if (tid == 0) { issue_load(t); tma_store_wait_read(); }
+    mbar_wait(bar, phase); phase ^= 1;
+    cta_sync<NT>();
+    // (1) [X1 | x1v] = Einv^T [P | pvec]          EinvP, -ptilde      (:175-178)
+    mma_gemm<n, n + 1, n, NW>(warp, lane,
+        [&](int i, int k) { return Einv[k + i * n]; },
+        [&](int k, int j) { return P[k + j * n]; },
+        [](int, int) { return 0.0; },
+        [&](int i, int j, double v) { X1[i + j * n] = v; });
+    cta_sync<NT>();
+    // (2) Ptilde = X1 * Einv (lower triangle kept, mirrored); vx <- ptilde = -x1v   (:179-180)
+    mma_gemm<n, n, n, NW>(warp, lane,
+        [&](int i, int k) { return X1[i + k * n]; },
+        [&](int k, int j) { return Einv[k + j * n]; },
+        [](int, int) { return 0.0; },
+        [&](int i, int j, double v) { if (i >= j) { P[i + j * n] = v; P[j + i * n] = v; } });
+    cta_sync<NT>();
+    // (3) w = ptilde + Ptilde f -> pv ; Lambda = I + mudyn Ptilde -> X1 (lower)      (:182-187)
+    gemv4<n, n, NT>(tid, [&](int i, int j) { return P[i + j * n]; }, [&](int j) { return f[j]; },
+                    [&](int i) { return -x1v[i]; }, [&](int i, double v) { pv[i] = v; });
+    for (int e = tid; e < n * n; e += NT) {
+      const int i = e % n, j = e / n;
+      if (i >= j) X1[e] = (i == j ? 1.0 : 0.0) + mudyn * P[e];
+    }
+    cta_sync<NT>();
+    // (4) [Vxx | vx] = Lambda^{-1} [Ptilde | w]                                      (:185-190)
+    if (!ldlt_solve<n, n + 1, NT>(tid, X1, P, dinv)) flags |= GARB200_FLAG_LLT_NOT_PD;
+    mirror_lower_ct<n, NT>(tid, P);
+    cta_sync<NT>();
+    if (p.store_all_values) {
+      double *v = p.values + ((size_t)b * p.nslots + (t + 1)) * p.VL.stride;
+      for (int e = tid; e < n * n; e += NT) v[p.VL.Vxx + e] = P[e];
+      for (int i = tid; i < n; i += NT) v[p.VL.vx + i] = pv[i];
+    }
+    // (5) [AtV ; BtV] = [A | B]^T [Vxx | vx]: rows < n -> X1 (+ A^T vx), rows >= n -> BtV (+ B^T vx)
+    mma_gemm<n + m, n + 1, n, NW>(warp, lane,
+        [&](int i, int k) { return A[k + i * n]; },           // [A | B] is one n x (n+m) col-major block
+        [&](int k, int j) { return P[k + j * n]; },
+        [](int, int) { return 0.0; },
+        [&](int i, int j, double v) {
+          if (i < n) { if (j < n) X1[i + j * n] = v; else atvx[i] = v; }
+          else BtV[(i - n) + j * m] = v;
+        });
+    cta_sync<NT>();
+    // (6) [Qhat | Shat] = [Q | S] + AtV [A | B] (in place) ; Rhat = R + BtV B -> kkt   (:195-199)
+    mma_gemm<n, n + m, n, NW>(warp, lane,
+        [&](int i, int k) { return X1[i + k * n]; },
+        [&](int k, int j) { return A[k + j * n]; },
+        [&](int i, int j) { return Q[i + j * n]; },           // [Q | S] contiguous as well
+        [&](int i, int j, double v) { Q[i + j * n] = v; });
+    mma_gemm<m, m, n, NW>(warp, lane,
+        [&](int i, int k) { return BtV[i + k * m]; },
+        [&](int k, int j) { return B[k + j * n]; },
+        [&](int i, int j) { return R[i + j * m]; },
+        [&](int i, int j, double v) { kkt[i + j * s] = v; });
+    // right-hand sides of the reduced KKT system, in the gains record          (:210-226)
+    for (int i = tid; i < m; i += NT) ff[rK + i] = -(rv[i] + btvx[i]);          // -rhat
+    for (int i = tid; i < c; i += NT) ff[rZ + i] = -d[i];
+    for (int e = tid; e < c * s; e += NT) {                                     // [D  -mueq I] rows
+      const int i = e % c, j = e / c;
+      kkt[(m + i) + j * s] = (j < m) ? D[i + j * c] : ((j - m == i) ? -mueq : 0.0);
+    }
+    for (int e = tid; e < c * n; e += NT) { const int i = e % c, j = e / c; fb[(rZ + i) * n + j] = -C[i + j * c]; }
+    for (int i = tid; i < n; i += NT) qv[i] += atvx[i];                         // qhat
+    cta_sync<NT>();
+    for (int e = tid; e < m * n; e += NT) { const int i = e / n, j = e % n; fb[(rK + i) * n + j] = -S[j + i * n]; }  // -Shat^T
+    // (7) Bunch-Kaufman of [Rhat D^T; D -mueq I] and the 1 + n solves                 (:202-228)
+    if (warp == 0) {
+      if (!bk_factor_warp(lane, s, kkt, s, kpiv, ksub)) flags |= GARB200_FLAG_BK_SINGULAR;
+    }
+    cta_sync<NT>();
+    for (int col = tid; col < n + 1; col += NT) {
+      if (col == 0) bk_solve_column(s, kkt, s, kpiv, ksub, ff, 1);
+      else bk_solve_column(s, kkt, s, kpiv, ksub, fb + (col - 1), n);
+    }
+    cta_sync<NT>();
+    // (8) lff = vx + BtV^T kff ; tv = f + B kff - mudyn lff -> pv slot                  (:231-236)
+    for (int i = tid; i < n; i += NT) {
+      double l = pv[i], tb = f[i];
+#pragma unroll
+      for (int k = 0; k < m; k++) { l = fma(BtV[k + i * m], ff[rK + k], l); tb = fma(B[i + k * n], ff[rK + k], tb); }
+      ff[rL + i] = l;
+      pv[i] = tb - mudyn * l;
+    }
+    // (9) L = AtV^T + BtV^T K  (Vxx A == AtV^T: Vxx is exactly symmetric) -> fb rows rL     (:238-239)
+    //     A_pre = A + B K - mudyn L -> P block                                            (:241-242)
+    {
+      constexpr int TM = (n + 7) / 8, TN = (n + 7) / 8, KSt = (m + 3) / 4;
+      const int g = lane >> 2, q = lane & 3;
+      for (int tt = warp; tt < TM * TN; tt += NW) {
+        const int ti = tt % TM, tj = tt / TM;
+        const int ic = ti * 8 + g, ia = min(ic, n - 1);
+        const int jc = tj * 8 + 2 * q, j0 = min(jc, n - 1), j1 = min(jc + 1, n - 1);
+        const int jbk = min(tj * 8 + g, n - 1);
+        double l0 = X1[j0 + ia * n], l1 = X1[j1 + ia * n];       // AtV^T
+        double a0 = A[ia + j0 * n], a1 = A[ia + j1 * n];
+#pragma unroll
+        for (int ks = 0; ks < KSt; ks++) {
+          const int k = ks * 4 + q;
+          const bool kv = (m % 4 == 0) || (k < m);
+          const int kc = min(k, m - 1);
+          const double bvK = kv ? fb[(rK + kc) * n + jbk] : 0.0;
+          const double aL = kv ? BtV[kc + ia * m] : 0.0;
+          const double aB = kv ? B[ia + kc * n] : 0.0;
+          dmma_884(l0, l1, aL, bvK);
+          dmma_884(a0, a1, aB, bvK);
+        }
+        if (ic < n) {
+          if (jc < n) { fb[(rL + ic) * n + jc] = l0; P[ic + jc * n] = a0 - mudyn * l0; }
+          if (jc + 1 < n) { fb[(rL + ic) * n + jc + 1] = l1; P[ic + (jc + 1) * n] = a1 - mudyn * l1; }
+        }
+      }
+    }
+    cta_sync<NT>();
+    // (10) [Afb | yff] = -Einv [A_pre | tv]                                              (:243-245)
+    mma_gemm<n, n + 1, n, NW>(warp, lane,
+        [&](int i, int k) { return -Einv[i + k * n]; },
+        [&](int k, int j) { return P[k + j * n]; },
+        [](int, int) { return 0.0; },
+        [&](int i, int j, double v) { if (j < n) fb[(rA + i) * n + j] = v; else ff[rA + i] = v; });
+    cta_sync<NT>();
+    // (11) [Pmat | pvec] = [Qhat | qhat] + Shat [K | kff] + C^T [Z | zff]                  (:249-250)
+    mma_gemm<n, n + 1, s, NW>(warp, lane,
+        [&](int i, int k) { return k < m ? S[i + k * n] : C[(k - m) + i * c]; },
+        [&](int k, int j) { return j < n ? fb[k * n + j] : ff[k]; },
+        [&](int i, int j) { return j < n ? Q[i + j * n] : qv[i]; },
+        [&](int i, int j, double v) { P[i + j * n] = v; });
+    store_gains(t);
+    store_value(t);
+    fence_proxy_async();
+    cta_sync<NT>();
+  }
+
+  // ---- initial stage: BK of [Pmat0 G0^T; G0 -mudyn I]        (proximal-riccati.hxx:44-62) ----
+  {
+    if (tid == 0) tma_store_wait_read();
+    cta_sync<NT>();
+    const int c0 = p.nc0, s0 = n + c0;
+    double *K0 = sm;                               // overlays rec | X1  (>= (2n)^2 doubles? checked on host)
+    double *ff0 = Gs;
+    const double *G0 = p.G0 + (size_t)b * c0 * n, *g0 = p.g0 + (size_t)b * c0;
+    for (int e = tid; e < s0 * s0; e += NT) {
+      const int i = e % s0, j = e / s0;
+      double v;
+      if (j < n) v = (i < n) ? P[i + j * n] : G0[(i - n) + j * c0];
+      else v = (i == j) ? -mudyn : 0.0;
+      K0[e] = v;
+    }
+    for (int i = tid; i < s0; i += NT) ff0[i] = (i < n) ? -pv[i] : -g0[i - n];
+    cta_sync<NT>();
+    if (warp == 0) {
+      if (!bk_factor_warp(lane, s0, K0, s0, kpiv, ksub)) flags |= GARB200_FLAG_BK_SINGULAR;
+    }
+    cta_sync<NT>();
+    if (tid == 0) bk_solve_column(s0, K0, s0, kpiv, ksub, ff0, 1);
+    cta_sync<NT>();
+    double *off = p.kkt0_ff + (size_t)b * s0;
+    for (int i = tid; i < s0; i += NT) off[i] = ff0[i];
+  }
+  for (int e = tid; e < n * n; e += NT)
+    if (!isfinite(P[e])) flags |= GARB200_FLAG_NONFINITE;
+  if (flags) atomicOr(reinterpret_cast<int *>(p.flags) + b, flags);
+  if (tid == 0) tma_store_wait_all();
+}
+
+// ---- host side -----------------------------------------------------------------------------
+template <int NX, int NU, int NC, int NW>
+static int launch_fast_t(const DevParams &p, cudaStream_t st) {
+  using PL = FastPlan<NX, NU, NC>;
+  static_assert(PL::kstride >= 0, "");
+  if (p.KL.stride != PL::kstride || p.GL.stride != PL::gstride || p.KL.E != PL::oE || p.KL.f != PL::of)
+    return -3;   // layout mismatch: never expected, fall back to the generic kernel
+  const int s0 = NX + p.nc0;
+  if ((size_t)s0 * s0 > (size_t)PL::P) return -3;            // K0 overlay must end before the P block
+  // pre-pass
+  constexpr int WPB = NX <= 16 ? 8 : 4;
+  constexpr int PER = NX * (2 * NX + 1) + ((NX + 1) / 2 + 1);
+  const size_t smem_e = (size_t)WPB * PER * sizeof(double);
+  auto ke = einv_kernel<NX, WPB>;
+  if (cudaFuncSetAttribute(ke, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_e) != cudaSuccess) return -2;
+  const long long total = (long long)p.batch * p.T;
+  int launched = 0;
+  if (total > 0) {
+    ke<<<(unsigned)((total + WPB - 1) / WPB), 32 * WPB, smem_e, st>>>(p);
+    if (cudaGetLastError() != cudaSuccess) return -2;
+    launched++;
+  }
+  const size_t smem = (size_t)PL::total * sizeof(double);
+  auto ks = sweep_kernel<NX, NU, NC, NW>;
+  if (cudaFuncSetAttribute(ks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -2;
+  ks<<<p.batch, 32 * NW, smem, st>>>(p);
+  if (cudaGetLastError() != cudaSuccess) return -2;
+  return launched + 1;
+}
+
+/// Returns the number of kernels launched, -3 if no specialisation matches (caller falls back
+/// to the generic kernel), < 0 otherwise on error.
+int launch_backward_fast(const DevParams &p, const int *h_nu_t, const int *h_nc_t, cudaStream_t st) {
+  if (p.num_legs >= 2 || p.nth != 0 || p.einv == nullptr || p.T < 1) return -3;
+  if (h_nu_t[p.T] != 0 || h_nc_t[p.T] != 0) return -3;
+  for (int t = 0; t < p.T; t++)
+    if (h_nu_t[t] != p.nu || h_nc_t[t] != p.nc) return -3;
+  if (p.nx == 12 && p.nu == 4 && p.nc == 0) return launch_fast_t<12, 4, 0, 1>(p, st);
+  if (p.nx == 36 && p.nu == 12 && p.nc == 0) return launch_fast_t<36, 12, 0, 4>(p, st);
+  return -3;
+}
+
+bool fast_path_available(int nx, int nu, int nc, int nth, int num_legs) {
+  if (num_legs >= 2 || nth != 0) return false;
+  return (nx == 12 && nu == 4 && nc == 0) || (nx == 36 && nu == 12 && nc == 0);
+}
+
+} // namespace garb200

@@ -52,6 +52,8 @@ extern "C" {
 #define GARB200_STORE_ALL_VALUES 1   /* keep StageFactor::vm of EVERY knot (default: knot 0 and
                                         leg heads only — what the algorithm itself consumes)  */
 
+#define GARB200_FORCE_GENERIC 2      /* never use the dimension-specialised kernels (testing)  */
+
 typedef struct garb200_solver garb200_solver; /* opaque */
 
 typedef struct garb200_config {
@@ -183,6 +185,8 @@ int garb200_upload_trajectory(garb200_solver *s, const double *xs, const double 
 int64_t garb200_kernel_launches(const garb200_solver *s);
 /* device-event time (ms) of the last backward and forward kernels sequences */
 int garb200_last_timings(garb200_solver *s, float *backward_ms, float *forward_ms);
+/* 1 if the last backward ran the dimension-specialised (DMMA) sweep, 0 for the generic kernel */
+int garb200_used_fast_path(const garb200_solver *s);
 /* Per-call device timing log (bench / roofline): after _start, every backward and forward
  * brackets its kernels with CUDA events on the solver stream (up to `capacity` of each);
  * _read synchronises, returns the per-call durations in ms and stops logging. */

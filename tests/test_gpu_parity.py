@@ -60,7 +60,7 @@ CASES = [
     (7, 5, 3, 2, 9, 4, 1e-6, "ref"),
     (17, 1, 0, 0, 12, 3, 1e-9, "ref"),
     (33, 9, 4, 3, 6, 2, 1e-10, "ref"),
-    (5, 0, 2, 0, 6, 2, 1e-9, "ref"),         # nu = 0 everywhere
+    (5, 0, 2, 0, 6, 2, 1e-6, "ref"),         # nu = 0 everywhere (Z = C / mueq, riccati-kernel.hxx:105-108)
     (48, 16, 0, 0, 8, 2, 1e-11, "ref"),
 ]
 
@@ -68,11 +68,27 @@ CASES = [
 @pytest.mark.parametrize("case", CASES, ids=lambda c: "nx%d_nu%d_nc%d_nth%d_T%d_B%d_%g_%s" % c)
 def test_prox_parity(capi, oracle, case):
     nx, nu, nc, nth, T, B, mu, dist = case
+    _prox_parity(capi, oracle, case, capi.STORE_ALL_VALUES)
+
+
+FAST_SHAPES = [c for c in CASES if (c[0], c[1], c[2], c[3]) in ((12, 4, 0, 0), (36, 12, 0, 0))]
+
+
+@pytest.mark.parametrize("case", FAST_SHAPES, ids=lambda c: "nx%d_nu%d_nc%d_nth%d_T%d_B%d_%g_%s" % c)
+def test_prox_parity_generic_kernel(capi, oracle, case):
+    """The shapes that have a dimension-specialised (DMMA) kernel, forced through the generic one."""
+    _prox_parity(capi, oracle, case, capi.STORE_ALL_VALUES | capi.FORCE_GENERIC)
+
+
+def _prox_parity(capi, oracle, case, flags):
+    nx, nu, nc, nth, T, B, mu, dist = case
     pp = generate_problems(B, T, nx, nu, nc, nth, seed=nx * 131 + T, dist=dist)
     theta = np.random.default_rng(1).standard_normal((B, nth)) if nth else None
-    s = capi.Solver.for_problems(pp, flags=capi.STORE_ALL_VALUES)
+    s = capi.Solver.for_problems(pp, flags=flags)
     s.upload(pp)
     s.backward(mu, mu)
+    fast_expected = (nx, nu, nc, nth) in ((12, 4, 0, 0), (36, 12, 0, 0)) and not (flags & capi.FORCE_GENERIC) and T >= 1
+    assert s.used_fast_path() == fast_expected
     xs, us, vs, lb = s.forward(theta)
     assert (s.get_flags() == 0).all()
     G = GainLayout(nx, nu, nc, nth)
@@ -103,9 +119,13 @@ def test_prox_parity(capi, oracle, case):
             assert relerr(thg, ref["thGrad"]) < RTOL_GAINS and relerr(thh, ref["thHess"]) < RTOL_GAINS
         # KKT residual kernel == oracle's lqrComputeKktError on the GPU trajectory
         ek = oracle.kkt_error(pp, xs[b], us[b], vs[b], lb[b], mu, mu, theta=th, b=b)
-        assert np.allclose(kkt_gpu[b], ek, rtol=1e-6, atol=1e-13), (kkt_gpu[b], ek)
+        # (residuals live at round-off level: summation order differs, so compare up to the
+        #  rounding scale |data| * |trajectory| * eps * terms, not bit for bit)
+        floor = 64 * np.finfo(float).eps * max(1.0, np.abs(pp.knots[b]).max()) * max(
+            1.0, np.abs(xs[b]).max(), np.abs(lb[b]).max(), np.abs(us[b]).max() if us[b].size else 0.0)
+        assert np.allclose(kkt_gpu[b], ek, rtol=1e-6, atol=floor), (kkt_gpu[b], ek, floor)
         # and it is as small as the oracle's own residual (same order of magnitude)
-        assert kkt_gpu[b].max() <= max(10 * ref["kkt"].max(), 1e-12)
+        assert kkt_gpu[b].max() <= max(10 * ref["kkt"].max(), 1e-12, 10 * floor)
     s.close()
 
 
@@ -153,7 +173,7 @@ def test_gar_mirror_api(capi, oracle):
     assert K.shape == (2 + 0 + 4, 2) and kff.shape == (6,)
     np.testing.assert_allclose(us[0], kff[:2] + K[:2] @ xs[0], rtol=1e-12, atol=1e-14)
     # the solver re-reads the problem on every backward (proximal-riccati.hxx:37)
-    prob.stages[0].q[:] = 5.0
+    prob.stages[1].q[:] = 5.0
     solver.backward(1e-14, 1e-14)
     xs2, us2, vs2, lb2 = gar.lqrInitializeSolution(prob)
     solver.forward(xs2, us2, vs2, lb2)
@@ -196,14 +216,15 @@ def test_device_generator_roundtrip(capi, oracle):
     xs, us, vs, lb = s.forward()
     assert (s.get_flags() == 0).all()
     kkt = s.kkt_error(mu, mu)
-    assert kkt.max() < 1e-7
-    idx = [0, 1, 149, 299]
+    assert kkt.max() < 1e-4      # E ~ 1000 N(0,1), f ~ N(0, 100^2): residual scale of the data itself
+    idx = [0, 1, 149, 299, int(kkt.max(axis=1).argmax())]
     for b in idx:
         knots, G0, g0 = s.download_packed(b, 1)
         pp = PackedProblems(KnotLayout(nx, nu, 0, 0), T, nx, s.nu_t, s.nc_t, knots, G0, g0)
         ref = oracle.prox_solve(pp, mu, mu)
         assert relerr(xs[b], ref["xs"]) < RTOL and relerr(us[b], ref["us"]) < RTOL
         assert relerr(lb[b], ref["lbdas"]) < RTOL
+        assert kkt[b].max() <= max(10 * ref["kkt"].max(), 1e-10)   # as small as the CPU solver's own
     # distribution sanity (test_util.cpp:31-35): E ~ 1000 N(0,1), B ~ U[-1,1]
     knots, _, _ = s.download_packed(0, 32)
     o = KnotLayout(nx, nu, 0, 0).offsets
@@ -229,7 +250,7 @@ def test_parallel_in_time_parity(capi, oracle, case):
     """ParallelRiccatiSolver on the GPU (legs = CTAs): serial == parallel <= 1e-10
     (tests/gar/parallel.cpp:243-260) and == the oracle's restated parallel solver."""
     nx, nu, nc, T, J, B, mu = case
-    pp = generate_problems(B, T, nx, nu, nc, 0, seed=nx + T + J, dist="explicit")
+    pp = generate_problems(B, T, nx, nu, nc, 0, seed=nx + T + J, dist="ref")
     s, xs, us, vs, lb = solve_gpu(capi, pp, mu, num_legs=J)
     assert (s.get_flags() == 0).all()
     kkt = s.kkt_error(mu, mu)
@@ -242,15 +263,29 @@ def test_parallel_in_time_parity(capi, oracle, case):
         assert np.abs(xs[b] - ser["xs"]).max() <= 1e-10 * scale_x
         assert np.abs(lb[b] - ser["lbdas"]).max() <= 1e-9 * scale_l
         assert relerr(xs[b], par["xs"]) < 1e-9 and relerr(us[b], par["us"]) < 1e-9
-    # collapseFeedback (parallel-solver.hpp:55-66)
-    g_before = s.get_gains(0, 0)[1].copy()
+    s.close()
+
+
+def test_collapse_feedback(capi, oracle):
+    """collapseFeedback (parallel-solver.hpp:55-66): K0 -= Kth0 * subdiagonal[1].  Explicit
+    dynamics and two-knot legs so that the correction is not vanishingly small."""
+    nx, nu, T, J, mu = 4, 2, 5, 3, 1e-8
+    pp = generate_problems(2, T, nx, nu, 0, 0, seed=11, dist="explicit")
+    s, xs, us, vs, lb = solve_gpu(capi, pp, mu, num_legs=J)
+    G = GainLayout(nx, nu, 0, nx)
+    for b in range(2):
+        g_before = s.get_gains(b, 0)[1].copy()
+        ref0 = oracle.parallel_solve(pp, mu, mu, J, collapse=False, b=b)
+        rfb0 = G.unpack(ref0["gains"][0], nu, 0)[1]
+        assert np.abs(g_before - rfb0).max() <= 1e-9 * max(np.abs(rfb0).max(), 1.0)
     s.collapse_feedback()
-    g_after = s.get_gains(0, 0)[1]
-    ref = oracle.parallel_solve(pp, mu, mu, J, collapse=True, b=0)
-    G = GainLayout(nx, nu, nc, nx)
-    rff, rfb, rfth = G.unpack(ref["gains"][0], pp.nu_t[0], pp.nc_t[0])
-    assert np.abs(g_after - rfb).max() <= 1e-8 * max(np.abs(rfb).max(), 1.0)
-    assert np.abs(g_after[:nu] - g_before[:nu]).max() > 0
+    for b in range(2):
+        g_after = s.get_gains(b, 0)[1]
+        ref = oracle.parallel_solve(pp, mu, mu, J, collapse=True, b=b)
+        rfb = G.unpack(ref["gains"][0], nu, 0)[1]
+        rfb0 = G.unpack(oracle.parallel_solve(pp, mu, mu, J, b=b)["gains"][0], nu, 0)[1]
+        assert np.abs(rfb[:nu] - rfb0[:nu]).max() > 1e-6          # the correction is visible
+        assert np.abs(g_after - rfb).max() <= 1e-9 * max(np.abs(rfb).max(), 1.0)
     s.close()
 
 
