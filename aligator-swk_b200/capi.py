@@ -53,7 +53,7 @@ SYMBOLS = [
     "garb200_get_refinement_steps", "garb200_collapse_feedback", "garb200_cycle_append",
     "garb200_kkt_error", "garb200_upload_trajectory", "garb200_kernel_launches", "garb200_last_timings",
     "garb200_fp64_peak", "garb200_timing_log_start", "garb200_timing_log_read",
-    "garb200_used_fast_path",
+    "garb200_used_fast_path", "garb200_phase_cycles",
 ]
 
 
@@ -98,6 +98,7 @@ def lib():
         L.garb200_last_timings.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.garb200_fp64_peak.argtypes = [C.c_int, C.c_int, C.c_void_p]
         L.garb200_used_fast_path.argtypes = [C.c_void_p]
+        L.garb200_phase_cycles.argtypes = [C.c_void_p, C.c_void_p]
         L.garb200_timing_log_start.argtypes = [C.c_void_p, C.c_int]
         L.garb200_timing_log_read.argtypes = [C.c_void_p] * 4
         L.garb200_create.argtypes = [C.c_void_p, C.c_void_p]
@@ -312,6 +313,11 @@ class Solver:
 
     def used_fast_path(self) -> bool:
         return bool(lib().garb200_used_fast_path(self._h))
+
+    def phase_cycles(self):
+        out = np.zeros(16, np.int64)
+        check(lib().garb200_phase_cycles(self._h, _ptr(out)))
+        return out
 
     def timing_log_start(self, capacity):
         check(lib().garb200_timing_log_start(self._h, int(capacity)))

@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <string>
 #include <vector>
 #include "kernels.cuh"
@@ -168,6 +169,8 @@ int garb200_create(const garb200_config *cfg, garb200_solver **out) {
   TRYB(dmalloc(s, &p.flags, B));
   TRYB(dmalloc(s, &p.refine_steps, B));
   TRYB(dmalloc(s, &s->d_kkt_out, B * 3));
+  p.phase_cycles = nullptr;
+  if (getenv("GARB200_PHASE_TIMERS")) { TRYB(dmalloc(s, &p.phase_cycles, 16)); cudaMemset(p.phase_cycles, 0, 16 * sizeof(long long)); }
   cudaMemset(p.flags, 0, B * sizeof(int32_t));
   cudaMemset(p.refine_steps, 0, B * sizeof(int32_t));
   cudaMemset(p.values, 0, B * p.nslots * p.VL.stride * sizeof(double));
@@ -622,6 +625,16 @@ int garb200_last_timings(garb200_solver *s, float *backward_ms, float *forward_m
 }
 
 int garb200_used_fast_path(const garb200_solver *s) { return s && s->used_fast ? 1 : 0; }
+
+int garb200_phase_cycles(garb200_solver *s, long long *out16) {
+  if (!s || !out16) return fail(GARB200_ERR_INVALID, "null argument");
+  if (!s->p.phase_cycles) return fail(GARB200_ERR_STATE, "create the solver with GARB200_PHASE_TIMERS=1 in the environment");
+  CK(cudaSetDevice(s->cfg.device));
+  CK(cudaStreamSynchronize(s->stream));
+  CK(cudaMemcpy(out16, s->p.phase_cycles, 16 * sizeof(long long), cudaMemcpyDeviceToHost));
+  CK(cudaMemset(s->p.phase_cycles, 0, 16 * sizeof(long long)));
+  return GARB200_OK;
+}
 
 int garb200_timing_log_start(garb200_solver *s, int capacity) {
   if (!s || capacity < 0) return fail(GARB200_ERR_INVALID, "bad argument");

@@ -165,6 +165,175 @@ __device__ __forceinline__ bool ldlt_solve(int tid, double *S, double *R, double
 }
 
 // ------------------------------------------------------------------------------------------
+// Runtime-extent DMMA update with ONE k-step (K = 4):  C(i,j) = cin(i,j) + sum_{k<4} a(i,k) b(k,j)
+// for i < M, j < N; `lower`: only the 8x8 tiles on or below the diagonal (M == N).
+// ------------------------------------------------------------------------------------------
+template <int NW, int TNMAX, class FA, class FB, class FC, class FS>
+__device__ __forceinline__ void mma_k4(int warp, int lane, int M, int N, bool lower, FA a, FB b, FC cin,
+                                       FS store) {
+  if (M <= 0 || N <= 0) return;
+  const int TM = (M + 7) >> 3, TN = (N + 7) >> 3;
+  const int g = lane >> 2, q = lane & 3;
+  // one warp per 8-row strip: the A fragment is loaded once, every operand of the strip is
+  // fetched before the first DMMA issues (loads, tensor ops and stores overlap across tiles)
+  for (int ti = warp; ti < TM; ti += NW) {
+    const int ic = ti * 8 + g, ia = min(ic, M - 1);
+    const double av = a(ia, q);
+    double c0[TNMAX], c1[TNMAX], bv[TNMAX];
+#pragma unroll
+    for (int u = 0; u < TNMAX; u++) {
+      const bool on = u < TN && (!lower || u <= ti);
+      if (on) {
+        const int jb = min(u * 8 + g, N - 1), jc = u * 8 + 2 * q;
+        bv[u] = b(q, jb);
+        c0[u] = cin(ia, min(jc, N - 1));
+        c1[u] = cin(ia, min(jc + 1, N - 1));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < TNMAX; u++) {
+      const bool on = u < TN && (!lower || u <= ti);
+      if (on) dmma_884(c0[u], c1[u], av, bv[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < TNMAX; u++) {
+      const bool on = u < TN && (!lower || u <= ti);
+      const int jc = u * 8 + 2 * q;
+      if (on && ic < M) {
+        if (jc < N) store(ic, jc, c0[u]);
+        if (jc + 1 < N) store(ic, jc + 1, c1[u]);
+      }
+    }
+  }
+}
+
+/// Right-hand-side accessors for ldlt_solve_blocked: element (i, j) of the N x NR block.
+template <int LD> struct RhsColMajor {
+  double *p;
+  __device__ __forceinline__ double get(int i, int j) const { return p[i + j * LD]; }
+  __device__ __forceinline__ void set(int i, int j, double v) const { p[i + j * LD] = v; }
+};
+/// The (1 + n) right-hand sides of the reduced KKT system where they sit in a gains record:
+/// column j < n is column j of the row-major fb rows, column n is ff (riccati-kernel.hpp:76-78).
+template <int NXc> struct RhsGains {
+  double *ff, *fb;
+  __device__ __forceinline__ double get(int i, int j) const { return j < NXc ? fb[i * NXc + j] : ff[i]; }
+  __device__ __forceinline__ void set(int i, int j, double v) const { if (j < NXc) fb[i * NXc + j] = v; else ff[i] = v; }
+};
+
+template <int N, int NR, int NT, int NPOS = N, class RH>
+__device__ __forceinline__ bool ldlt_solve_blocked(int tid, double *S, RH R, double *Wp, double *dinv) {
+  static_assert(N % 4 == 0, "blocked LDL^T needs N % 4 == 0");
+  constexpr int NW = NT / 32;
+  constexpr int CO_ = ((N - 4 + 31) / 32) * 32;
+  constexpr int CO = (CO_ + NR <= NT) ? CO_ : (N - 4 > 0 ? N - 4 : 0);
+  static_assert(CO + NR <= NT, "not enough threads for rows + rhs columns");
+  const int warp = tid >> 5, lane = tid & 31;
+  bool ok = true;
+#pragma unroll 1
+  for (int r0 = 0; r0 < N; r0 += 4) {
+    // ---- phase A
+    const double *Dg = S + r0 + r0 * N;
+    const double a00 = Dg[0], a10 = Dg[1], a20 = Dg[2], a30 = Dg[3];
+    const double a11 = Dg[1 + N], a21 = Dg[2 + N], a31 = Dg[3 + N];
+    const double a22 = Dg[2 + 2 * N], a32 = Dg[3 + 2 * N], a33 = Dg[3 + 3 * N];
+    const double i0 = __drcp_rn(a00);
+    const double l10 = a10 * i0, l20 = a20 * i0, l30 = a30 * i0;
+    const double d1 = fma(-l10, a10, a11);
+    const double w21 = fma(-l20, a10, a21), w31 = fma(-l30, a10, a31);     // unscaled
+    const double i1 = __drcp_rn(d1);
+    const double l21 = w21 * i1, l31 = w31 * i1;
+    const double d2 = fma(-l21, w21, fma(-l20, a20, a22));
+    const double w32 = fma(-l31, w21, fma(-l30, a20, a32));
+    const double i2 = __drcp_rn(d2);
+    const double l32 = w32 * i2;
+    const double d3 = fma(-l32, w32, fma(-l31, w31, fma(-l30, a30, a33)));
+    const double i3 = __drcp_rn(d3);
+    // inertia check: the first NPOS pivots must be > 0, the others < 0 (quasi-definite matrix)
+    {
+      const double s0 = (r0 + 0 < NPOS) ? a00 : -a00, s1 = (r0 + 1 < NPOS) ? d1 : -d1;
+      const double s2 = (r0 + 2 < NPOS) ? d2 : -d2, s3 = (r0 + 3 < NPOS) ? d3 : -d3;
+      if (!(s0 > 0.0) || !(s1 > 0.0) || !(s2 > 0.0) || !(s3 > 0.0)) ok = false;
+    }
+    const int nbelow = N - r0 - 4;
+    if (tid < nbelow) {
+      const int i = r0 + 4 + tid;
+      double *row = S + i + r0 * N;
+      const double w0 = row[0];
+      const double l0 = w0 * i0;
+      const double w1 = fma(-l0, a10, row[N]);
+      const double l1 = w1 * i1;
+      const double w2 = fma(-l1, w21, fma(-l0, a20, row[2 * N]));
+      const double l2 = w2 * i2;
+      const double w3 = fma(-l2, w32, fma(-l1, w31, fma(-l0, a30, row[3 * N])));
+      const double l3 = w3 * i3;
+      row[0] = l0; row[N] = l1; row[2 * N] = l2; row[3 * N] = l3;
+      double *wp = Wp + 4 * (i - r0 - 4);
+      wp[0] = w0; wp[1] = w1; wp[2] = w2; wp[3] = w3;
+    } else if (tid >= CO && tid < CO + NR) {
+      const int j = tid - CO;
+      const double y0 = R.get(r0, j);
+      const double y1 = fma(-l10, y0, R.get(r0 + 1, j));
+      const double y2 = fma(-l21, y1, fma(-l20, y0, R.get(r0 + 2, j)));
+      const double y3 = fma(-l32, y2, fma(-l31, y1, fma(-l30, y0, R.get(r0 + 3, j))));
+      R.set(r0 + 1, j, y1); R.set(r0 + 2, j, y2); R.set(r0 + 3, j, y3);
+    }
+    cta_sync<NT>();
+    if (tid == NT - 1) {   // after the barrier: every thread has read the unscaled diagonal block
+      double *Dw = S + r0 + r0 * N;
+      Dw[1] = l10; Dw[2] = l20; Dw[3] = l30; Dw[2 + N] = l21; Dw[3 + N] = l31; Dw[3 + 2 * N] = l32;
+      dinv[r0] = i0; dinv[r0 + 1] = i1; dinv[r0 + 2] = i2; dinv[r0 + 3] = i3;
+    }
+    // ---- phase B (rows/cols below the block, origin r1)
+    if (nbelow > 0) {
+      const int r1 = r0 + 4;
+      const double *Lp = S + r1 + r0 * N;          // L panel: (i, k) at Lp[i + k*N]
+      mma_k4<NW, (NR + 7) / 8>(warp, lane, nbelow, NR, false,
+                 [&](int i, int k) { return -Lp[i + k * N]; },
+                 [&](int k, int j) { return R.get(r0 + k, j); },
+                 [&](int i, int j) { return R.get(r1 + i, j); },
+                 [&](int i, int j, double v) { R.set(r1 + i, j, v); });
+      double *S1 = S + r1 + r1 * N;
+      mma_k4<NW, ((N + 3) / 8 < 1 ? 1 : (N + 3) / 8)>(warp, lane, nbelow, nbelow, true,
+                 [&](int i, int k) { return -Lp[i + k * N]; },
+                 [&](int k, int j) { return Wp[4 * j + k]; },
+                 [&](int i, int j) { return S1[i + j * N]; },
+                 [&](int i, int j, double v) { S1[i + j * N] = v; });
+      cta_sync<NT>();
+    }
+  }
+  cta_sync<NT>();
+  // z = D^{-1} y
+  for (int e = tid; e < N * NR; e += NT) { const int i = e % N, j = e / N; R.set(i, j, R.get(i, j) * dinv[i]); }
+  cta_sync<NT>();
+#pragma unroll 1
+  for (int r0 = N - 4; r0 >= 0; r0 -= 4) {
+    // ---- phase C: x rows r0..r0+3 of every column
+    if (tid < NR) {
+      const double *Dg = S + r0 + r0 * N;
+      const double l10 = Dg[1], l20 = Dg[2], l30 = Dg[3], l21 = Dg[2 + N], l31 = Dg[3 + N], l32 = Dg[3 + 2 * N];
+      const double x3 = R.get(r0 + 3, tid);
+      const double x2 = fma(-l32, x3, R.get(r0 + 2, tid));
+      const double x1 = fma(-l31, x3, fma(-l21, x2, R.get(r0 + 1, tid)));
+      const double x0 = fma(-l30, x3, fma(-l20, x2, fma(-l10, x1, R.get(r0, tid))));
+      R.set(r0 + 2, tid, x2); R.set(r0 + 1, tid, x1); R.set(r0, tid, x0);
+    }
+    if (r0 == 0) break;
+    cta_sync<NT>();
+    // ---- phase D: rows above: R(i, j) -= sum_k L(r0+k, i) x(r0+k, j)
+    const double *Lr = S + r0;                     // (r0+k, i) at Lr[k + i*N]
+    mma_k4<NW, (NR + 7) / 8>(warp, lane, r0, NR, false,
+               [&](int i, int k) { return -Lr[k + i * N]; },
+               [&](int k, int j) { return R.get(r0 + k, j); },
+               [&](int i, int j) { return R.get(i, j); },
+               [&](int i, int j, double v) { R.set(i, j, v); });
+    cta_sync<NT>();
+  }
+  cta_sync<NT>();
+  return ok;
+}
+
+// ------------------------------------------------------------------------------------------
 // X = E^{-1} by LU with row partial pivoting, executed by ONE warp on a row-major work
 // array W[N][LDW] (LDW = 2N+1, odd => lane-private rows are bank-conflict free).
 // Lanes own rows (lane, lane+32, ...); rows never move, `piv[k]` records the pivot row of
@@ -252,6 +421,110 @@ __device__ __forceinline__ bool lu_inverse_warp(int lane, const double *__restri
   // X(k, j) = W[piv[k]][N + j]  -> col-major global, consecutive lanes = consecutive k
   for (int j = 0; j < N; j++)
     for (int k = lane; k < N; k += 32) Xg[k + j * N] = W[piv[k] * LDW + N + j];
+  return ok;
+}
+
+// ------------------------------------------------------------------------------------------
+// X = E^{-1} entirely in REGISTERS: in-place Gauss-Jordan elimination with row partial
+// pivoting (same pivot rule as PartialPivLU: largest |entry| of the column among the rows not
+// yet used).  LPM lanes own one matrix (16 for N <= 16: two matrices per warp), lane `sub`
+// holds rows sub, sub + LPM, ...  All loops are unrolled so every register index is static;
+// per step the pivot row travels through N doubles of shared memory (`srow`) as a broadcast.
+// Rows never move: step k records its pivot row in spiv[k] and the row remembers its step,
+// and the final store un-permutes:  X(step(r), spiv[c]) = a_r[c].
+// Returns false on an exactly zero pivot.
+// ------------------------------------------------------------------------------------------
+template <int N> struct GjShape {
+  static constexpr int LPM = N <= 16 ? 16 : 32;
+  static constexpr int MPW = 32 / LPM;
+  static constexpr int RPL = (N + LPM - 1) / LPM;
+  static_assert(N <= 64, "register Gauss-Jordan: N <= 64");
+};
+
+template <int N>
+__device__ __forceinline__ bool gj_inverse_regs(int sub, unsigned mask, const double *__restrict__ Eg,
+                                                double *__restrict__ Xg, bool do_store, double *srow,
+                                                int *spiv) {
+  constexpr int LPM = GjShape<N>::LPM, RPL = GjShape<N>::RPL;
+  double a[RPL][N];
+  int sig[RPL];
+  bool act[RPL];
+#pragma unroll
+  for (int s = 0; s < RPL; s++) {
+    const int row = sub + LPM * s;
+    act[s] = row < N;
+    sig[s] = 0;
+#pragma unroll
+    for (int j = 0; j < N; j++) a[s][j] = act[s] ? Eg[row + j * N] : 0.0;
+  }
+  bool ok = true;
+#pragma unroll
+  for (int k = 0; k < N; k++) {
+    // pivot search: 64-bit key = bits(|a|) with the low 7 bits replaced by (127 - row)
+    unsigned long long best = 0ull;
+#pragma unroll
+    for (int s = 0; s < RPL; s++) {
+      const int row = sub + LPM * s;
+      unsigned long long key = (unsigned long long)__double_as_longlong(fabs(a[s][k]));
+      key = (key & ~0x7Full) | (unsigned long long)(127 - row);
+      if (act[s] && key > best) best = key;
+    }
+    const unsigned hi = (unsigned)(best >> 32), lo = (unsigned)best;
+    const unsigned mhi = __reduce_max_sync(mask, hi);
+    const unsigned mlo = __reduce_max_sync(mask, (best != 0ull && hi == mhi) ? lo : 0u);
+    const int r = 127 - (int)(mlo & 0x7Fu);
+    const int rl = r % LPM, rs = r / LPM;
+    double pcand = a[0][k];
+#pragma unroll
+    for (int s = 1; s < RPL; s++) if (rs == s) pcand = a[s][k];
+    const double pval = __shfl_sync(mask, pcand, rl, LPM);
+    if (pval == 0.0) ok = false;
+    const double pinv = __drcp_rn(pval);
+    if (sub == rl) {
+#pragma unroll
+      for (int s = 0; s < RPL; s++)
+        if (rs == s) {
+#pragma unroll
+          for (int j = 0; j < N; j++) srow[j] = a[s][j];
+        }
+    }
+    if (sub == 0) spiv[k] = r;
+    __syncwarp(mask);
+    double f[RPL];
+#pragma unroll
+    for (int s = 0; s < RPL; s++) {
+      const bool isp = (sub + LPM * s) == r;
+      f[s] = isp ? 0.0 : a[s][k] * pinv;
+    }
+#pragma unroll
+    for (int j = 0; j < N; j++) {
+      if (j == k) continue;
+      const double bj = srow[j];
+#pragma unroll
+      for (int s = 0; s < RPL; s++) a[s][j] = fma(-f[s], bj, a[s][j]);
+    }
+#pragma unroll
+    for (int s = 0; s < RPL; s++) {
+      const bool isp = (sub + LPM * s) == r;
+      a[s][k] = isp ? pinv : -f[s];
+      if (isp) {
+        act[s] = false;
+        sig[s] = k;
+#pragma unroll
+        for (int j = 0; j < N; j++) if (j != k) a[s][j] *= pinv;
+      }
+    }
+  }
+  __syncwarp(mask);
+  if (do_store) {
+#pragma unroll
+    for (int c = 0; c < N; c++) {
+      const int pc = spiv[c];
+#pragma unroll
+      for (int s = 0; s < RPL; s++)
+        if (sub + LPM * s < N) Xg[sig[s] + pc * N] = a[s][c];
+    }
+  }
   return ok;
 }
 

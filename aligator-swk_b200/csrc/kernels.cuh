@@ -34,6 +34,7 @@ struct DevParams {
   double *cdiagF, *csubF, *crhs, *csol, *cerr, *csubd;
   int *cpiv;
   int32_t *flags, *refine_steps;
+  long long *phase_cycles;        // [16] accumulated phase timers of the specialised sweep, or nullptr
   double mudyn, mueq;
   garb200_knot_layout KL;
   garb200_gain_layout GL;   // built with nth_eff = (leg mode ? nx : nth)

@@ -16,22 +16,26 @@
 namespace garb200 {
 
 // ---- pre-pass: batched inverse of E ------------------------------------------------------
+// One matrix per LPM lanes (two 12x12 matrices or one 36x36 matrix per warp), the whole matrix
+// in registers; E is read once from HBM and Einv written once (2 n^2 doubles of traffic).
 template <int N, int WPB>
 __global__ void __launch_bounds__(32 * WPB) einv_kernel(const DevParams p) {
-  extern __shared__ __align__(16) double sm[];
-  constexpr int LDW = 2 * N + 1;
-  constexpr int PER = N * LDW + ((N + 1) / 2 + 1);     // work array + pivots (ints)
+  using GS = GjShape<N>;
+  constexpr int MPW = GS::MPW, LPM = GS::LPM, NP = (N + 1) & ~1;
+  __shared__ __align__(16) double s_row[WPB * MPW][NP];
+  __shared__ int s_piv[WPB * MPW][NP];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int mi = lane / LPM, sub = lane % LPM;
+  const unsigned mask = (LPM == 32) ? 0xffffffffu : (0xffffu << (16 * mi));
   const long long total = (long long)p.batch * p.T;
-  const long long w = (long long)blockIdx.x * WPB + warp;
-  if (w >= total) return;
+  long long w = ((long long)blockIdx.x * WPB + warp) * MPW + mi;
+  const bool valid = w < total;
+  if (!valid) w = total - 1;      // keep the lane group busy on a duplicate, store nothing
   const int b = (int)(w / p.T), t = (int)(w % p.T);
-  double *W = sm + (size_t)warp * PER;
-  int *piv = reinterpret_cast<int *>(W + N * LDW);
   const double *Eg = p.knots + ((size_t)b * (p.T + 1) + phys_t(p, t)) * p.KL.stride + p.KL.E;
   double *Xg = p.einv + ((size_t)b * p.T + phys_t(p, t)) * (size_t)(N * N);
-  const bool ok = lu_inverse_warp<N>(lane, Eg, W, piv, Xg);
-  if (!ok && lane == 0) atomicOr(reinterpret_cast<int *>(p.flags) + b, GARB200_FLAG_LU_SINGULAR);
+  const bool ok = gj_inverse_regs<N>(sub, mask, Eg, Xg, valid, s_row[warp * MPW + mi], s_piv[warp * MPW + mi]);
+  if (!ok && sub == 0 && valid) atomicOr(reinterpret_cast<int *>(p.flags) + b, GARB200_FLAG_LU_SINGULAR);
 }
 
 // ---- shared-memory plan of the sweep (doubles) ---------------------------------------------
@@ -63,7 +67,7 @@ template <int NX, int NU, int NC> struct FastPlan {
   static constexpr int total = bar + 2;
 };
 
-template <int NX, int NU, int NC, int NW>
+template <int NX, int NU, int NC, int NW, bool PROF>
 __global__ void __launch_bounds__(32 * NW) sweep_kernel(const DevParams p) {
   extern __shared__ __align__(16) double sm[];
   using PL = FastPlan<NX, NU, NC>;
@@ -86,6 +90,18 @@ __global__ void __launch_bounds__(32 * NW) sweep_kernel(const DevParams p) {
   int *kpiv = reinterpret_cast<int *>(sm + PL::ints);
   uint64_t *bar = reinterpret_cast<uint64_t *>(sm + PL::bar);
   int flags = 0;
+  // optional phase timers (GARB200_PHASE_TIMERS=1): cycles of thread 0 between phase marks
+  long long ph_acc[16], ph_last = 0;
+  if constexpr (PROF) {
+#pragma unroll
+    for (int i = 0; i < 16; i++) ph_acc[i] = 0;
+    ph_last = clock64();
+  }
+  auto PH = [&](int i) {
+    if constexpr (PROF) {
+      if (tid == 0) { const long long now = clock64(); ph_acc[i] += now - ph_last; ph_last = now; }
+    }
+  };
 
   if (tid == 0) { mbar_init(bar, 1); fence_mbar_init(); }
   for (int e = tid; e < PL::gstride; e += NT) Gs[e] = 0.0;
@@ -141,6 +157,7 @@ __global__ void __launch_bounds__(32 * NW) sweep_kernel(const DevParams p) {
     if (tid == 0) { issue_load(t); tma_store_wait_read(); }
     mbar_wait(bar, phase); phase ^= 1;
     cta_sync<NT>();
+    PH(0);
     // (1) [X1 | x1v] = Einv^T [P | pvec]          EinvP, -ptilde      (:175-178)
     mma_gemm<n, n + 1, n, NW>(warp, lane,
         [&](int i, int k) { return Einv[k + i * n]; },
@@ -148,6 +165,7 @@ __global__ void __launch_bounds__(32 * NW) sweep_kernel(const DevParams p) {
         [](int, int) { return 0.0; },
         [&](int i, int j, double v) { X1[i + j * n] = v; });
     cta_sync<NT>();
+    PH(1);
     // (2) Ptilde = X1 * Einv (lower triangle kept, mirrored); vx <- ptilde = -x1v   (:179-180)
     mma_gemm<n, n, n, NW>(warp, lane,
         [&](int i, int k) { return X1[i + k * n]; },
@@ -155,6 +173,7 @@ __global__ void __launch_bounds__(32 * NW) sweep_kernel(const DevParams p) {
         [](int, int) { return 0.0; },
         [&](int i, int j, double v) { if (i >= j) { P[i + j * n] = v; P[j + i * n] = v; } });
     cta_sync<NT>();
+    PH(2);
     // (3) w = ptilde + Ptilde f -> pv ; Lambda = I + mudyn Ptilde -> X1 (lower)      (:182-187)
     gemv4<n, n, NT>(tid, [&](int i, int j) { return P[i + j * n]; }, [&](int j) { return f[j]; },
                     [&](int i) { return -x1v[i]; }, [&](int i, double v) { pv[i] = v; });
@@ -163,10 +182,13 @@ __global__ void __launch_bounds__(32 * NW) sweep_kernel(const DevParams p) {
       if (i >= j) X1[e] = (i == j ? 1.0 : 0.0) + mudyn * P[e];
     }
     cta_sync<NT>();
+    PH(3);
     // (4) [Vxx | vx] = Lambda^{-1} [Ptilde | w]                                      (:185-190)
-    if (!ldlt_solve<n, n + 1, NT>(tid, X1, P, dinv)) flags |= GARB200_FLAG_LLT_NOT_PD;
+    if (!ldlt_solve_blocked<n, n + 1, NT>(tid, X1, RhsColMajor<n>{P}, Gs, dinv)) flags |= GARB200_FLAG_LLT_NOT_PD;
+    PH(4);
     mirror_lower_ct<n, NT>(tid, P);
     cta_sync<NT>();
+    PH(5);
     if (p.store_all_values) {
       double *v = p.values + ((size_t)b * p.nslots + (t + 1)) * p.VL.stride;
       for (int e = tid; e < n * n; e += NT) v[p.VL.Vxx + e] = P[e];
@@ -182,38 +204,66 @@ __global__ void __launch_bounds__(32 * NW) sweep_kernel(const DevParams p) {
           else BtV[(i - n) + j * m] = v;
         });
     cta_sync<NT>();
+    PH(6);
     // (6) [Qhat | Shat] = [Q | S] + AtV [A | B] (in place) ; Rhat = R + BtV B -> kkt   (:195-199)
     mma_gemm<n, n + m, n, NW>(warp, lane,
         [&](int i, int k) { return X1[i + k * n]; },
         [&](int k, int j) { return A[k + j * n]; },
         [&](int i, int j) { return Q[i + j * n]; },           // [Q | S] contiguous as well
         [&](int i, int j, double v) { Q[i + j * n] = v; });
-    mma_gemm<m, m, n, NW>(warp, lane,
-        [&](int i, int k) { return BtV[i + k * m]; },
-        [&](int k, int j) { return B[k + j * n]; },
-        [&](int i, int j) { return R[i + j * m]; },
-        [&](int i, int j, double v) { kkt[i + j * s] = v; });
-    // right-hand sides of the reduced KKT system, in the gains record          (:210-226)
-    for (int i = tid; i < m; i += NT) ff[rK + i] = -(rv[i] + btvx[i]);          // -rhat
-    for (int i = tid; i < c; i += NT) ff[rZ + i] = -d[i];
-    for (int e = tid; e < c * s; e += NT) {                                     // [D  -mueq I] rows
-      const int i = e % c, j = e / c;
-      kkt[(m + i) + j * s] = (j < m) ? D[i + j * c] : ((j - m == i) ? -mueq : 0.0);
-    }
-    for (int e = tid; e < c * n; e += NT) { const int i = e % c, j = e / c; fb[(rZ + i) * n + j] = -C[i + j * c]; }
-    for (int i = tid; i < n; i += NT) qv[i] += atvx[i];                         // qhat
+    // Rhat = R + BtV B -> kkt, the constraint rows [D  -mueq I], and the right-hand sides
+    // [-rhat | -Shat^T ; -d | -C] in the gains record                              (:202-226)
+    auto build_kkt = [&]() {
+      mma_gemm<m, m, n, NW>(warp, lane,
+          [&](int i, int k) { return BtV[i + k * m]; },
+          [&](int k, int j) { return B[k + j * n]; },
+          [&](int i, int j) { return R[i + j * m]; },
+          [&](int i, int j, double v) { kkt[i + j * s] = v; });
+      for (int i = tid; i < m; i += NT) ff[rK + i] = -(rv[i] + btvx[i]);          // -rhat
+      if constexpr (c > 0) {
+        constexpr int cc = c > 0 ? c : 1;
+        for (int i = tid; i < c; i += NT) ff[rZ + i] = -d[i];
+        for (int e = tid; e < c * s; e += NT) {
+          const int i = e % cc, j = e / cc;
+          kkt[(m + i) + j * s] = (j < m) ? D[i + j * c] : ((j - m == i) ? -mueq : 0.0);
+        }
+        for (int e = tid; e < c * n; e += NT) { const int i = e % cc, j = e / cc; fb[(rZ + i) * n + j] = -C[i + j * c]; }
+      }
+    };
+    auto build_rhs_K = [&]() {   // needs Shat complete
+      for (int e = tid; e < m * n; e += NT) { const int i = e / n, j = e % n; fb[(rK + i) * n + j] = -S[j + i * n]; }
+    };
+    build_kkt();
+    for (int i = tid; i < n; i += NT) qv[i] += atvx[i];                           // qhat
     cta_sync<NT>();
-    for (int e = tid; e < m * n; e += NT) { const int i = e / n, j = e % n; fb[(rK + i) * n + j] = -S[j + i * n]; }  // -Shat^T
-    // (7) Bunch-Kaufman of [Rhat D^T; D -mueq I] and the 1 + n solves                 (:202-228)
-    if (warp == 0) {
-      if (!bk_factor_warp(lane, s, kkt, s, kpiv, ksub)) flags |= GARB200_FLAG_BK_SINGULAR;
-    }
+    build_rhs_K();
+    // (7) reduced KKT system [Rhat D^T; D -mueq I] [K kff; Z zff] = rhs                  (:202-228)
+    // The matrix is quasi-definite whenever Rhat > 0 (any convex stage): LDL^T in the natural
+    // order exists and its pivots are (+)^m (-)^c.  That inertia is verified pivot by pivot; a
+    // knot that fails the check is rebuilt and factorised with the reference's Bunch-Kaufman
+    // pivoting instead (bunchkaufman.hpp:20-167, 447-516).
+    PH(7);
     cta_sync<NT>();
-    for (int col = tid; col < n + 1; col += NT) {
-      if (col == 0) bk_solve_column(s, kkt, s, kpiv, ksub, ff, 1);
-      else bk_solve_column(s, kkt, s, kpiv, ksub, fb + (col - 1), n);
+    PH(8);
+    {
+      static_assert(s % 4 == 0, "specialised sweep needs (nu + nc) % 4 == 0");
+      const bool okk = ldlt_solve_blocked<s, n + 1, NT, m>(tid, kkt, RhsGains<n>{ff, fb}, P, P + 4 * s);
+      if (!okk) {                     // uniform: every thread computed the same pivots
+        build_kkt();
+        build_rhs_K();
+        cta_sync<NT>();
+        if (warp == 0) {
+          if (!bk_factor_warp(lane, s, kkt, s, kpiv, ksub)) flags |= GARB200_FLAG_BK_SINGULAR;
+        }
+        cta_sync<NT>();
+        for (int col = tid; col < n + 1; col += NT) {
+          if (col == 0) bk_solve_column(s, kkt, s, kpiv, ksub, ff, 1);
+          else bk_solve_column(s, kkt, s, kpiv, ksub, fb + (col - 1), n);
+        }
+        cta_sync<NT>();
+      }
     }
-    cta_sync<NT>();
+    PH(9);
     // (8) lff = vx + BtV^T kff ; tv = f + B kff - mudyn lff -> pv slot                  (:231-236)
     for (int i = tid; i < n; i += NT) {
       double l = pv[i], tb = f[i];
@@ -252,6 +302,7 @@ __global__ void __launch_bounds__(32 * NW) sweep_kernel(const DevParams p) {
       }
     }
     cta_sync<NT>();
+    PH(10);
     // (10) [Afb | yff] = -Einv [A_pre | tv]                                              (:243-245)
     mma_gemm<n, n + 1, n, NW>(warp, lane,
         [&](int i, int k) { return -Einv[i + k * n]; },
@@ -259,17 +310,21 @@ __global__ void __launch_bounds__(32 * NW) sweep_kernel(const DevParams p) {
         [](int, int) { return 0.0; },
         [&](int i, int j, double v) { if (j < n) fb[(rA + i) * n + j] = v; else ff[rA + i] = v; });
     cta_sync<NT>();
+    PH(11);
     // (11) [Pmat | pvec] = [Qhat | qhat] + Shat [K | kff] + C^T [Z | zff]                  (:249-250)
     mma_gemm<n, n + 1, s, NW>(warp, lane,
         [&](int i, int k) { return k < m ? S[i + k * n] : C[(k - m) + i * c]; },
         [&](int k, int j) { return j < n ? fb[k * n + j] : ff[k]; },
         [&](int i, int j) { return j < n ? Q[i + j * n] : qv[i]; },
         [&](int i, int j, double v) { P[i + j * n] = v; });
+    PH(12);
     store_gains(t);
     store_value(t);
     fence_proxy_async();
     cta_sync<NT>();
+    PH(13);
   }
+  PH(14);
 
   // ---- initial stage: BK of [Pmat0 G0^T; G0 -mudyn I]        (proximal-riccati.hxx:44-62) ----
   {
@@ -301,6 +356,12 @@ __global__ void __launch_bounds__(32 * NW) sweep_kernel(const DevParams p) {
     if (!isfinite(P[e])) flags |= GARB200_FLAG_NONFINITE;
   if (flags) atomicOr(reinterpret_cast<int *>(p.flags) + b, flags);
   if (tid == 0) tma_store_wait_all();
+  PH(15);
+  if constexpr (PROF) {
+    if (tid == 0 && p.phase_cycles)
+#pragma unroll
+      for (int i = 0; i < 16; i++) atomicAdd(reinterpret_cast<unsigned long long *>(p.phase_cycles) + i, (unsigned long long)ph_acc[i]);
+  }
 }
 
 // ---- host side -----------------------------------------------------------------------------
@@ -313,20 +374,18 @@ static int launch_fast_t(const DevParams &p, cudaStream_t st) {
   const int s0 = NX + p.nc0;
   if ((size_t)s0 * s0 > (size_t)PL::P) return -3;            // K0 overlay must end before the P block
   // pre-pass
-  constexpr int WPB = NX <= 16 ? 8 : 4;
-  constexpr int PER = NX * (2 * NX + 1) + ((NX + 1) / 2 + 1);
-  const size_t smem_e = (size_t)WPB * PER * sizeof(double);
+  constexpr int WPB = 4;
+  constexpr int MPB = WPB * GjShape<NX>::MPW;
   auto ke = einv_kernel<NX, WPB>;
-  if (cudaFuncSetAttribute(ke, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_e) != cudaSuccess) return -2;
   const long long total = (long long)p.batch * p.T;
   int launched = 0;
   if (total > 0) {
-    ke<<<(unsigned)((total + WPB - 1) / WPB), 32 * WPB, smem_e, st>>>(p);
+    ke<<<(unsigned)((total + MPB - 1) / MPB), 32 * WPB, 0, st>>>(p);
     if (cudaGetLastError() != cudaSuccess) return -2;
     launched++;
   }
   const size_t smem = (size_t)PL::total * sizeof(double);
-  auto ks = sweep_kernel<NX, NU, NC, NW>;
+  auto ks = p.phase_cycles ? sweep_kernel<NX, NU, NC, NW, true> : sweep_kernel<NX, NU, NC, NW, false>;
   if (cudaFuncSetAttribute(ks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -2;
   ks<<<p.batch, 32 * NW, smem, st>>>(p);
   if (cudaGetLastError() != cudaSuccess) return -2;

@@ -187,6 +187,9 @@ int64_t garb200_kernel_launches(const garb200_solver *s);
 int garb200_last_timings(garb200_solver *s, float *backward_ms, float *forward_ms);
 /* 1 if the last backward ran the dimension-specialised (DMMA) sweep, 0 for the generic kernel */
 int garb200_used_fast_path(const garb200_solver *s);
+/* Diagnostic: accumulated clock64() cycles of thread 0 of every CTA per phase of the specialised
+ * sweep since the last call (solver created with GARB200_PHASE_TIMERS=1 in the environment). */
+int garb200_phase_cycles(garb200_solver *s, long long *out16);
 /* Per-call device timing log (bench / roofline): after _start, every backward and forward
  * brackets its kernels with CUDA events on the solver stream (up to `capacity` of each);
  * _read synchronises, returns the per-call durations in ms and stops logging. */

@@ -330,3 +330,20 @@ def test_cycle_append(capi, oracle):
     xs, us, vs, lb = s.forward()
     compare_traj(oracle, pp, mu, xs, us, vs, lb)
     s.close()
+
+
+@pytest.mark.parametrize("shape", [(12, 4, 20), (36, 12, 12)])
+def test_fast_path_indefinite_kkt_falls_back_to_bunch_kaufman(capi, oracle, shape):
+    """The specialised sweep factors the reduced KKT matrix without pivoting after checking its
+    inertia; a knot with an indefinite Rhat must be re-factorised with Bunch-Kaufman pivoting and
+    still match the oracle.  Problems 0 and 2 are untouched, problem 1 has R_t = -R_t at t = 3."""
+    nx, nu, T = shape
+    mu = 1e-10
+    pp = generate_problems(3, T, nx, nu, seed=77)
+    o = pp.layout.offsets
+    pp.knots[1, 3, o["R"]: o["R"] + nu * nu] *= -1.0
+    s, xs, us, vs, lb = solve_gpu(capi, pp, mu)
+    assert s.used_fast_path()
+    assert (s.get_flags() == 0).all()
+    compare_traj(oracle, pp, mu, xs, us, vs, lb, rtol=1e-9)
+    s.close()

@@ -1,0 +1,22 @@
+"""Per-phase cycle breakdown of the specialised sweep (diagnostic; run on the GPU box):
+   GARB200_PHASE_TIMERS=1 python tools/phase_timers.py c1b 296"""
+import os, sys
+os.environ["GARB200_PHASE_TIMERS"] = "1"
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import bench, garb200_pkg
+garb200_pkg.load()
+from aligator_swk_b200 import capi
+w = dict(bench.WORKLOADS[sys.argv[1]]); B = int(sys.argv[2]) if len(sys.argv) > 2 else w["batch"]
+s = capi.Solver(w["nx"], w["nu"], w["nc"], w["nth"], horizon=w["T"], batch=B)
+s.generate(42, 0)
+for _ in range(2):
+    s.backward(bench.MU, bench.MU)
+s.synchronize_stream_only(); s.phase_cycles()
+s.backward(bench.MU, bench.MU); s.synchronize_stream_only()
+c = s.phase_cycles().astype(float) / (B * w["T"])
+names = ["load", "g1 EinvT P", "g2 Ptilde", "gemv+Lambda", "ldlt", "mirror", "g5 AtV/BtV", "g6 Qhat/Rhat+rhs", "bk factor",
+         "bk solve", "L/Apre", "g10 Afb", "g11 Pmat", "store", "init-pre", "initial"]
+tot = c[:14].sum()
+for n, v in zip(names, c):
+    print(f"{n:18s} {v:10.0f} cycles/knot  {100*v/tot:5.1f}%")
+print("total per knot", tot, "cycles; initial stage per problem", c[15] * w["T"])
