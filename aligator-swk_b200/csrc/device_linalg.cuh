@@ -398,6 +398,216 @@ __device__ __forceinline__ bool bk_factor_warp(int lane, int n, double *a, int l
   return true;
 }
 
+// ------------------------------------------------------------------------------------------
+// Bunch-Kaufman LDL^T with the trailing update spread over a whole group of NT threads
+// (the initial-stage KKT matrix is (nx + nc0)^2: 72 x 72 for nx = 36).  Same pivoting rules and
+// output format as bk_factor_warp.  Per pivot: warp 0 searches, decides, interchanges and
+// snapshots the pivot column(s) into wk; one barrier; every thread updates its share of the
+// trailing lower triangle; one barrier.   wk: 2n + 4 doubles, ctl: 4 ints of scratch.
+// ------------------------------------------------------------------------------------------
+template <int NT>
+__device__ __forceinline__ bool bk_factor_cta(int tid, int n, double *a, int ld, int *piv, double *sub,
+                                              double *wk, int *ctl) {
+  const double alpha = 0.6403882032022076;   // (1 + sqrt(17)) / 8
+  const int lane = tid & 31, warp = tid >> 5;
+  constexpr int TY = NT / 32;
+  auto gsync = [&]() { if constexpr (NT == 32) __syncwarp(); else __syncthreads(); };
+  if (n == 0) return true;
+  int k = 0;
+  bool ok = true;
+  while (k < n) {
+    if (warp == 0) {
+      int kstep = 1, kp = k, fail = 0;
+      const double abs_akk = fabs(a[k + k * ld]);
+      double cv = -1.0; int ci = k + 1, ckey;
+      for (int i = k + 1 + lane; i < n; i += 32) {
+        const double v = fabs(a[i + k * ld]);
+        if (v > cv) { cv = v; ci = i; }
+      }
+      ckey = ci;
+      warp_argmax(cv, ckey, ci);
+      const double colmax = cv < 0.0 ? 0.0 : cv;
+      const int imax = cv < 0.0 ? k + 1 : ci;
+      if (fmax(abs_akk, colmax) == 0.0) fail = 1;
+      else if (k + 1 >= n || abs_akk >= colmax * alpha) kp = k;
+      else {
+        double rm = 0.0;
+        for (int j = k + lane; j < imax; j += 32) rm = fmax(rm, fabs(a[imax + j * ld]));
+        for (int i = imax + 1 + lane; i < n; i += 32) rm = fmax(rm, fabs(a[i + imax * ld]));
+        const double rowmax = warp_max(rm);
+        if (abs_akk >= (alpha * colmax) * (colmax / rowmax)) kp = k;
+        else if (fabs(a[imax + imax * ld]) >= alpha * rowmax) kp = imax;
+        else { kp = imax; kstep = 2; }
+      }
+      const int kk = k + kstep - 1;
+      __syncwarp();
+      if (!fail && kp != kk) {
+        for (int i = kp + 1 + lane; i < n; i += 32) {
+          const double t = a[i + kk * ld]; a[i + kk * ld] = a[i + kp * ld]; a[i + kp * ld] = t;
+        }
+        for (int j = kk + 1 + lane; j < kp; j += 32) {
+          const double t = a[j + kk * ld]; a[j + kk * ld] = a[kp + j * ld]; a[kp + j * ld] = t;
+        }
+        if (lane == 0) {
+          double t = a[kk + kk * ld]; a[kk + kk * ld] = a[kp + kp * ld]; a[kp + kp * ld] = t;
+          if (kstep == 2) { t = a[k + 1 + k * ld]; a[k + 1 + k * ld] = a[kp + k * ld]; a[kp + k * ld] = t; }
+        }
+        __syncwarp();
+      }
+      if (!fail) {
+        if (kstep == 1) {
+          for (int i = k + 1 + lane; i < n; i += 32) wk[i] = a[i + k * ld];
+          if (lane == 0) {
+            const double d11 = 1.0 / a[k + k * ld];
+            wk[2 * n] = d11; a[k + k * ld] = d11; piv[k] = kp;
+          }
+        } else {
+          for (int i = k + 2 + lane; i < n; i += 32) { wk[i] = a[i + k * ld]; wk[n + i] = a[i + (k + 1) * ld]; }
+          if (lane == 0) {
+            const double a21 = a[k + 1 + k * ld];
+            const double d21_abs = fabs(a21);
+            const double d21_inv = 1.0 / d21_abs;
+            const double d11 = d21_inv * a[k + 1 + (k + 1) * ld];
+            const double d22 = d21_inv * a[k + k * ld];
+            const double t = 1.0 / ((d11 * d22) - 1.0);
+            const double d = t * d21_inv;
+            const double d21 = a21 * d21_inv;
+            wk[2 * n] = d11; wk[2 * n + 1] = d22; wk[2 * n + 2] = d21; wk[2 * n + 3] = d;
+            a[k + k * ld] = d11 * d; a[k + 1 + k * ld] = -d21 * d; a[k + 1 + (k + 1) * ld] = d22 * d;
+            piv[k] = -1 - kp; piv[k + 1] = -1 - kp;
+          }
+        }
+      }
+      if (lane == 0) { ctl[0] = kstep; ctl[1] = fail; }
+    }
+    gsync();
+    const int kstep = ctl[0];
+    if (ctl[1]) { ok = false; break; }
+    const int tx = lane, ty = warp;
+    if (kstep == 1) {
+      const double d11 = wk[2 * n];
+      for (int j = k + 1 + ty; j < n; j += TY) {
+        const double d11xj = wk[j] * d11;
+        for (int i = j + tx; i < n; i += 32) a[i + j * ld] -= d11xj * wk[i];
+      }
+      for (int i = k + 1 + tid; i < n; i += NT) a[i + k * ld] = wk[i] * d11;
+    } else {
+      const double d11 = wk[2 * n], d22 = wk[2 * n + 1], d21 = wk[2 * n + 2], d = wk[2 * n + 3];
+      for (int j = k + 2 + ty; j < n; j += TY) {
+        const double ajk = wk[j], ajk1 = wk[n + j];
+        const double w0 = ((ajk * d11) - (ajk1 * d21)) * d;
+        const double w1 = ((ajk1 * d22) - (ajk * d21)) * d;
+        for (int i = j + tx; i < n; i += 32) a[i + j * ld] -= wk[i] * w0 + wk[n + i] * w1;
+      }
+      for (int j = k + 2 + tid; j < n; j += NT) {
+        const double ajk = wk[j], ajk1 = wk[n + j];
+        a[j + k * ld] = ((ajk * d11) - (ajk1 * d21)) * d;
+        a[j + (k + 1) * ld] = ((ajk1 * d22) - (ajk * d21)) * d;
+      }
+    }
+    gsync();
+    k += kstep;
+  }
+  if (!ok) return false;
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int q = 0; q < n;) {
+        if (piv[q] < 0) { sub[q] = a[q + 1 + q * ld]; sub[q + 1] = 0.0; a[q + 1 + q * ld] = 0.0; q += 2; }
+        else { sub[q] = 0.0; q += 1; }
+      }
+    }
+    __syncwarp();
+    for (int q = 0; q < n;) {
+      int pp = piv[q];
+      int row, step;
+      if (pp < 0) { pp = -1 - pp; row = q + 1; step = 2; } else { row = q; step = 1; }
+      if (pp != row)
+        for (int j = lane; j < q; j += 32) {
+          const double t = a[row + j * ld]; a[row + j * ld] = a[pp + j * ld]; a[pp + j * ld] = t;
+        }
+      __syncwarp();
+      q += step;
+    }
+  }
+  gsync();
+  return true;
+}
+
+// ------------------------------------------------------------------------------------------
+// Bunch-Kaufman solve of ONE right-hand side by one warp (bunchkaufman.hpp:447-516).
+// x lives in shared memory on entry/exit; in between every lane keeps its entries
+// (lane, lane+32, ...; n <= 32*MAXS) in registers and the pivot element travels by shuffle,
+// so a triangular sweep costs one shuffle + one fused multiply-add per step instead of a
+// shared-memory round trip.  `a` should have an odd leading dimension (row AND column
+// accesses are then bank-conflict free).  role: n ints of scratch.
+// ------------------------------------------------------------------------------------------
+template <int MAXS>
+__device__ __forceinline__ void bk_solve_vec_warp(int lane, int n, const double *a, int ld,
+                                                  const int *piv, const double *sub, double *x,
+                                                  int *role) {
+  if (lane == 0) {
+    for (int k = 0; k < n;) {       // P x, and the role of every index inside the block diagonal
+      int p = piv[k];
+      if (p < 0) {
+        p = -1 - p;
+        role[k] = 1; role[k + 1] = 2;
+        if (p != k + 1) { const double t = x[k + 1]; x[k + 1] = x[p]; x[p] = t; }
+        k += 2;
+      } else {
+        role[k] = 0;
+        if (p != k) { const double t = x[k]; x[k] = x[p]; x[p] = t; }
+        k += 1;
+      }
+    }
+  }
+  __syncwarp();
+  double xr[MAXS];
+#pragma unroll
+  for (int s = 0; s < MAXS; s++) { const int i = lane + 32 * s; xr[s] = i < n ? x[i] : 0.0; }
+  auto bcast = [&](int k) {
+    double v = xr[0];
+#pragma unroll
+    for (int s = 1; s < MAXS; s++) if ((k >> 5) == s) v = xr[s];
+    return __shfl_sync(0xffffffffu, v, k & 31);
+  };
+  for (int k = 0; k < n; k++) {            // unit lower
+    const double xk = bcast(k);
+#pragma unroll
+    for (int s = 0; s < MAXS; s++) { const int i = lane + 32 * s; if (i > k && i < n) xr[s] = fma(-a[i + k * ld], xk, xr[s]); }
+  }
+#pragma unroll
+  for (int s = 0; s < MAXS; s++) { const int i = lane + 32 * s; if (i < n) x[i] = xr[s]; }
+  __syncwarp();
+#pragma unroll
+  for (int s = 0; s < MAXS; s++) {         // block diagonal (stored inverted)
+    const int i = lane + 32 * s;
+    if (i < n) {
+      const int r = role[i];
+      if (r == 0) xr[s] = x[i] * a[i + i * ld];
+      else if (r == 1) xr[s] = x[i] * a[i + i * ld] + x[i + 1] * sub[i];
+      else xr[s] = x[i] * a[i + i * ld] + x[i - 1] * sub[i - 1];
+    }
+  }
+  for (int k = n - 1; k >= 0; k--) {       // unit upper (L^T), column oriented: row k of L
+    const double xk = bcast(k);
+#pragma unroll
+    for (int s = 0; s < MAXS; s++) { const int j = lane + 32 * s; if (j < k) xr[s] = fma(-a[k + j * ld], xk, xr[s]); }
+  }
+  __syncwarp();
+#pragma unroll
+  for (int s = 0; s < MAXS; s++) { const int i = lane + 32 * s; if (i < n) x[i] = xr[s]; }
+  __syncwarp();
+  if (lane == 0) {
+    for (int k = n; k > 0;) {              // undo the interchanges
+      k -= 1;
+      int p = piv[k];
+      if (p < 0) { p = -1 - p; if (p != k) { const double t = x[k]; x[k] = x[p]; x[p] = t; } k -= 1; }
+      else if (p != k) { const double t = x[k]; x[k] = x[p]; x[p] = t; }
+    }
+  }
+  __syncwarp();
+}
+
 // One thread solves one right-hand-side column in place: x(i) = xp[i*xs].
 // Restates bunch_kaufman_solve_in_place, core/bunchkaufman.hpp:447-516.
 __device__ __forceinline__ void bk_solve_column(int n, const double *__restrict__ a, int ld,

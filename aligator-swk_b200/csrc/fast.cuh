@@ -40,43 +40,44 @@ template <int RS, int CS> struct MV {
 template <int M, int N, int K, int NW, int TB = 1, class FA, class FB, class FC, class FS>
 __device__ __forceinline__ void mma_gemm(int warp, int lane, FA a, FB b, FC cin, FS store) {
   if constexpr (M <= 0 || N <= 0) return;
-  constexpr int TM = (M + 7) / 8, TN = (N + 7) / 8, TNB = (TN + TB - 1) / TB;
-  constexpr int KS = (K + 3) / 4;
+  constexpr int TM = (M + 7) / 8, TN = (N + 7) / 8, NTILE = TM * TN;
+  constexpr int NSLOT = (NTILE + NW - 1) / NW;      // tiles per warp, ALL kept in flight:
+  constexpr int KS = (K + 3) / 4;                   // NSLOT independent DMMA accumulation chains
   const int g = lane >> 2, q = lane & 3;
-  for (int t = warp; t < TM * TNB; t += NW) {
-    const int ti = t % TM, tjb = t / TM;
-    const int ia = min(ti * 8 + g, M - 1);      // A row of this lane
-    const int ic = ti * 8 + g;                  // C row
-    double acc[TB][2];
-    int jb[TB];
+  double acc[NSLOT][2];
+  int ia[NSLOT], jb[NSLOT];
 #pragma unroll
-    for (int u = 0; u < TB; u++) {
-      const int tj = tjb * TB + u;
-      jb[u] = min(tj * 8 + g, N - 1);           // B column of this lane
-      const int jc = tj * 8 + 2 * q;            // C columns jc, jc+1
-      acc[u][0] = cin(min(ic, M - 1), min(jc, N - 1));
-      acc[u][1] = cin(min(ic, M - 1), min(jc + 1, N - 1));
-    }
+  for (int u = 0; u < NSLOT; u++) {
+    const int t = min(warp + NW * u, NTILE - 1);
+    const int ti = t % TM, tj = t / TM;
+    ia[u] = min(ti * 8 + g, M - 1);
+    jb[u] = min(tj * 8 + g, N - 1);
+    const int jc = tj * 8 + 2 * q;
+    acc[u][0] = cin(ia[u], min(jc, N - 1));
+    acc[u][1] = cin(ia[u], min(jc + 1, N - 1));
+  }
 #pragma unroll
-    for (int ks = 0; ks < KS; ks++) {
-      const int k = ks * 4 + q;
-      double av;
-      if constexpr (K % 4 == 0) av = a(ia, k);
-      else av = (k < K) ? a(ia, min(k, K - 1)) : 0.0;
+  for (int ks = 0; ks < KS; ks++) {
+    const int k = ks * 4 + q;
+    double av[NSLOT], bv[NSLOT];
 #pragma unroll
-      for (int u = 0; u < TB; u++) {
-        if (TB > 1 && (tjb * TB + u) >= TN) continue;
-        double bv;
-        if constexpr (K % 4 == 0) bv = b(k, jb[u]);
-        else bv = (k < K) ? b(min(k, K - 1), jb[u]) : 0.0;
-        dmma_884(acc[u][0], acc[u][1], av, bv);
+    for (int u = 0; u < NSLOT; u++) {
+      if constexpr (K % 4 == 0) { av[u] = a(ia[u], k); bv[u] = b(k, jb[u]); }
+      else {
+        av[u] = (k < K) ? a(ia[u], min(k, K - 1)) : 0.0;
+        bv[u] = (k < K) ? b(min(k, K - 1), jb[u]) : 0.0;
       }
     }
 #pragma unroll
-    for (int u = 0; u < TB; u++) {
-      const int tj = tjb * TB + u;
-      const int jc = tj * 8 + 2 * q;
-      if (tj < TN && ic < M) {
+    for (int u = 0; u < NSLOT; u++) dmma_884(acc[u][0], acc[u][1], av[u], bv[u]);
+  }
+#pragma unroll
+  for (int u = 0; u < NSLOT; u++) {
+    const int t = warp + NW * u;
+    if (t < NTILE) {
+      const int ti = t % TM, tj = t / TM;
+      const int ic = ti * 8 + g, jc = tj * 8 + 2 * q;
+      if (ic < M) {
         if (jc < N) store(ic, jc, acc[u][0]);
         if (jc + 1 < N) store(ic, jc + 1, acc[u][1]);
       }

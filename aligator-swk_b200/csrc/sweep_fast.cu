@@ -59,8 +59,8 @@ template <int NX, int NU, int NC> struct FastPlan {
   static constexpr int ksub = r2(kkt + s * s);          // max(s, 2n) + 2
   static constexpr int KS = (s > 2 * n ? s : 2 * n) + 2;
   static constexpr int dinv = r2(ksub + KS);            // n
-  static constexpr int rhat = r2(dinv + n);             // s  (A^T vx, B^T vx scratch: n + m)
-  static constexpr int atvx = r2(rhat + s);             // n + m
+  static constexpr int rhat = r2(dinv + n);             // 16 doubles of reduction scratch
+  static constexpr int atvx = r2(rhat + 16);            // n + m
   static constexpr int G = r2(atvx + n + m);            // gains staging record
   static constexpr int ints = r2(G + gstride);          // pivots: KS ints
   static constexpr int bar = r2(ints + (KS + 1) / 2);
@@ -88,6 +88,7 @@ __global__ void __launch_bounds__(32 * NW) sweep_kernel(const DevParams p) {
   double *btvx = BtV + m * n;     // column n of BtV: B^T vx
   double *ff = Gs + PL::gff, *fb = Gs + PL::gfb;
   int *kpiv = reinterpret_cast<int *>(sm + PL::ints);
+  double *red = sm + PL::rhat;    // NW doubles: cross-warp reduction scratch
   uint64_t *bar = reinterpret_cast<uint64_t *>(sm + PL::bar);
   int flags = 0;
   // optional phase timers (GARB200_PHASE_TIMERS=1): cycles of thread 0 between phase marks
@@ -166,27 +167,57 @@ __global__ void __launch_bounds__(32 * NW) sweep_kernel(const DevParams p) {
         [&](int i, int j, double v) { X1[i + j * n] = v; });
     cta_sync<NT>();
     PH(1);
-    // (2) Ptilde = X1 * Einv (lower triangle kept, mirrored); vx <- ptilde = -x1v   (:179-180)
+    // (2) Ptilde = X1 * Einv (lower triangle kept, mirrored); ||Ptilde||_F^2 on the fly  (:179-180)
+    double fro = 0.0;
     mma_gemm<n, n, n, NW>(warp, lane,
         [&](int i, int k) { return X1[i + k * n]; },
         [&](int k, int j) { return Einv[k + j * n]; },
         [](int, int) { return 0.0; },
-        [&](int i, int j, double v) { if (i >= j) { P[i + j * n] = v; P[j + i * n] = v; } });
+        [&](int i, int j, double v) {
+          if (i >= j) { P[i + j * n] = v; P[j + i * n] = v; fro = fma(i == j ? v : 2.0 * v, v, fro); }
+        });
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) fro += __shfl_xor_sync(0xffffffffu, fro, o);
+    if (lane == 0) red[warp] = fro;
     cta_sync<NT>();
     PH(2);
-    // (3) w = ptilde + Ptilde f -> pv ; Lambda = I + mudyn Ptilde -> X1 (lower)      (:182-187)
+    fro = 0.0;
+#pragma unroll
+    for (int w = 0; w < NW; w++) fro += red[w];
+    // Lambda = I + mudyn Ptilde.  When mudyn ||Ptilde||_F <= 1e-9 the first-order Neumann form
+    //   Lambda^{-1} X = X - mudyn Ptilde X        (truncation <= (mudyn ||Ptilde||)^2 <= 1e-18 relative,
+    // below the rounding error of the LLT solve it replaces) is ONE product on the tensor pipe;
+    // otherwise the blocked LDL^T solve runs.  Uniform over the CTA (same `fro` in every thread).
+    const bool neumann = mudyn * sqrt(fro) <= 1e-9;
+    // (3) w = ptilde + Ptilde f -> pv                                                   (:182-187)
     gemv4<n, n, NT>(tid, [&](int i, int j) { return P[i + j * n]; }, [&](int j) { return f[j]; },
                     [&](int i) { return -x1v[i]; }, [&](int i, double v) { pv[i] = v; });
-    for (int e = tid; e < n * n; e += NT) {
-      const int i = e % n, j = e / n;
-      if (i >= j) X1[e] = (i == j ? 1.0 : 0.0) + mudyn * P[e];
+    if (!neumann) {
+      for (int e = tid; e < n * n; e += NT) {
+        const int i = e % n, j = e / n;
+        if (i >= j) X1[e] = (i == j ? 1.0 : 0.0) + mudyn * P[e];
+      }
     }
     cta_sync<NT>();
     PH(3);
     // (4) [Vxx | vx] = Lambda^{-1} [Ptilde | w]                                      (:185-190)
-    if (!ldlt_solve_blocked<n, n + 1, NT>(tid, X1, RhsColMajor<n>{P}, Gs, dinv)) flags |= GARB200_FLAG_LLT_NOT_PD;
-    PH(4);
-    mirror_lower_ct<n, NT>(tid, P);
+    if (neumann) {
+      mma_gemm<n, n + 1, n, NW>(warp, lane,
+          [&](int i, int k) { return -mudyn * P[i + k * n]; },
+          [&](int k, int j) { return P[k + j * n]; },
+          [&](int i, int j) { return P[i + j * n]; },
+          [&](int i, int j, double v) { X1[i + j * n] = v; });
+      cta_sync<NT>();
+      PH(4);
+      for (int e = tid; e < n * (n + 1); e += NT) {           // back into P, mirrored from the lower triangle
+        const int i = e % n, j = e / n;
+        P[e] = (j < n && i < j) ? X1[j + i * n] : X1[e];
+      }
+    } else {
+      if (!ldlt_solve_blocked<n, n + 1, NT>(tid, X1, RhsColMajor<n>{P}, Gs, dinv)) flags |= GARB200_FLAG_LLT_NOT_PD;
+      PH(4);
+      mirror_lower_ct<n, NT>(tid, P);
+    }
     cta_sync<NT>();
     PH(5);
     if (p.store_all_values) {
@@ -330,24 +361,22 @@ __global__ void __launch_bounds__(32 * NW) sweep_kernel(const DevParams p) {
   {
     if (tid == 0) tma_store_wait_read();
     cta_sync<NT>();
-    const int c0 = p.nc0, s0 = n + c0;
-    double *K0 = sm;                               // overlays rec | X1  (>= (2n)^2 doubles? checked on host)
+    const int c0 = p.nc0, s0 = n + c0, ld0 = s0 | 1;   // odd leading dimension: conflict-free rows and columns
+    double *K0 = sm;                               // overlays rec | X1 (size checked on the host)
     double *ff0 = Gs;
+    double *wk0 = Gs + ((s0 + 1) & ~1);
     const double *G0 = p.G0 + (size_t)b * c0 * n, *g0 = p.g0 + (size_t)b * c0;
     for (int e = tid; e < s0 * s0; e += NT) {
       const int i = e % s0, j = e / s0;
       double v;
       if (j < n) v = (i < n) ? P[i + j * n] : G0[(i - n) + j * c0];
       else v = (i == j) ? -mudyn : 0.0;
-      K0[e] = v;
+      K0[i + j * ld0] = v;
     }
     for (int i = tid; i < s0; i += NT) ff0[i] = (i < n) ? -pv[i] : -g0[i - n];
     cta_sync<NT>();
-    if (warp == 0) {
-      if (!bk_factor_warp(lane, s0, K0, s0, kpiv, ksub)) flags |= GARB200_FLAG_BK_SINGULAR;
-    }
-    cta_sync<NT>();
-    if (tid == 0) bk_solve_column(s0, K0, s0, kpiv, ksub, ff0, 1);
+    if (!bk_factor_cta<NT>(tid, s0, K0, ld0, kpiv, ksub, wk0, kpiv + s0)) flags |= GARB200_FLAG_BK_SINGULAR;
+    if (warp == 0) bk_solve_vec_warp<(2 * n + 31) / 32>(lane, s0, K0, ld0, kpiv, ksub, ff0, reinterpret_cast<int *>(wk0));
     cta_sync<NT>();
     double *off = p.kkt0_ff + (size_t)b * s0;
     for (int i = tid; i < s0; i += NT) off[i] = ff0[i];
@@ -372,7 +401,7 @@ static int launch_fast_t(const DevParams &p, cudaStream_t st) {
   if (p.KL.stride != PL::kstride || p.GL.stride != PL::gstride || p.KL.E != PL::oE || p.KL.f != PL::of)
     return -3;   // layout mismatch: never expected, fall back to the generic kernel
   const int s0 = NX + p.nc0;
-  if ((size_t)s0 * s0 > (size_t)PL::P) return -3;            // K0 overlay must end before the P block
+  if ((size_t)s0 * (s0 | 1) > (size_t)PL::P) return -3;      // K0 overlay must end before the P block
   // pre-pass
   constexpr int WPB = 4;
   constexpr int MPB = WPB * GjShape<NX>::MPW;

@@ -62,6 +62,9 @@ CASES = [
     (33, 9, 4, 3, 6, 2, 1e-10, "ref"),
     (5, 0, 2, 0, 6, 2, 1e-6, "ref"),         # nu = 0 everywhere (Z = C / mueq, riccati-kernel.hxx:105-108)
     (48, 16, 0, 0, 8, 2, 1e-11, "ref"),
+    (12, 4, 0, 0, 30, 4, 1e-3, "explicit"),  # mudyn |Ptilde| large: LDL^T path of the specialised sweep
+    (36, 12, 0, 0, 20, 2, 1e-2, "explicit"),
+    (12, 4, 0, 0, 30, 3, 1e-7, "explicit"),
 ]
 
 
