@@ -222,6 +222,20 @@ template <int NXc> struct RhsGains {
   __device__ __forceinline__ void set(int i, int j, double v) const { if (j < NXc) fb[i * NXc + j] = v; else ff[i] = v; }
 };
 
+/// A window of NRW columns starting at col0 of the same block; columns past n read 0 and drop writes.
+template <int NXc> struct RhsGainsPart {
+  double *ff, *fb;
+  int col0;
+  __device__ __forceinline__ double get(int i, int j) const {
+    const int jj = col0 + j;
+    return jj < NXc ? fb[i * NXc + jj] : (jj == NXc ? ff[i] : 0.0);
+  }
+  __device__ __forceinline__ void set(int i, int j, double v) const {
+    const int jj = col0 + j;
+    if (jj < NXc) fb[i * NXc + jj] = v; else if (jj == NXc) ff[i] = v;
+  }
+};
+
 template <int N, int NR, int NT, int NPOS = N, class RH>
 __device__ __forceinline__ bool ldlt_solve_blocked(int tid, double *S, RH R, double *Wp, double *dinv) {
   static_assert(N % 4 == 0, "blocked LDL^T needs N % 4 == 0");
@@ -422,6 +436,82 @@ __device__ __forceinline__ bool lu_inverse_warp(int lane, const double *__restri
   // X(k, j) = W[piv[k]][N + j]  -> col-major global, consecutive lanes = consecutive k
   for (int j = 0; j < N; j++)
     for (int k = lane; k < N; k += 32) Xg[k + j * N] = W[piv[k] * LDW + N + j];
+  return ok;
+}
+
+// ------------------------------------------------------------------------------------------
+// Reduced stage KKT system (s = nu + nc <= 32 unknowns, 1 + n right-hand sides sitting in a
+// gains record).  The matrix [Rhat D^T; D -mueq I] is quasi-definite for a convex stage, so
+// elimination in the natural order needs no pivoting and its pivots carry the inertia
+// (+)^NPOS (-)^(S-NPOS), which is verified.  Every warp inverts the matrix redundantly in
+// REGISTERS (lane i owns row i, Gauss-Jordan, pivot row broadcast by shuffles: no shared-memory
+// round trip, no CTA barrier), parks the inverse in its private scratch and multiplies it into
+// the column blocks it owns on the tensor pipe.  Returns false if the inertia check fails
+// (caller falls back to Bunch-Kaufman); the right-hand sides are then garbage.
+// ------------------------------------------------------------------------------------------
+template <int S, int NPOS, int NXc, int NW>
+__device__ __forceinline__ bool kkt_solve_inverse(int warp, int lane, const double *K, double *inv,
+                                                  double *ff, double *fb) {
+  static_assert(S <= 32, "reduced KKT: nu + nc <= 32");
+  double a[S];
+  const int row = min(lane, S - 1);
+#pragma unroll
+  for (int j = 0; j < S; j++) a[j] = (j <= row) ? K[row + j * S] : K[j + row * S];   // symmetric from lower
+  bool ok = true;
+#pragma unroll
+  for (int k = 0; k < S; k++) {
+    const double pv = __shfl_sync(0xffffffffu, a[k], k);
+    if (!((k < NPOS ? pv : -pv) > 0.0)) ok = false;
+    const double pinv = __drcp_rn(pv);
+    const bool isp = lane == k;
+    const double f = isp ? 0.0 : a[k] * pinv;
+#pragma unroll
+    for (int j = 0; j < S; j++) {
+      if (j == k) continue;
+      const double bj = __shfl_sync(0xffffffffu, a[j], k);
+      a[j] = fma(-f, bj, a[j]);
+    }
+    a[k] = isp ? pinv : -f;
+    if (isp) {
+#pragma unroll
+      for (int j = 0; j < S; j++) if (j != k) a[j] *= pinv;
+    }
+  }
+  if (lane < S) {
+#pragma unroll
+    for (int j = 0; j < S; j++) inv[lane + j * S] = a[j];
+  }
+  __syncwarp();
+  // X = inv * RHS, column blocks tj = warp, warp + NW, ...
+  constexpr int NR = NXc + 1, TM = (S + 7) / 8, TN = (NR + 7) / 8, KS = (S + 3) / 4;
+  const RhsGains<NXc> R{ff, fb};
+  const int g = lane >> 2, q = lane & 3;
+  for (int tj = warp; tj < TN; tj += NW) {
+    const int jb = min(tj * 8 + g, NR - 1);
+    double bv[KS], c0[TM], c1[TM];
+#pragma unroll
+    for (int ks = 0; ks < KS; ks++) { const int k = ks * 4 + q; bv[ks] = k < S ? R.get(k, jb) : 0.0; }
+#pragma unroll
+    for (int ti = 0; ti < TM; ti++) {
+      c0[ti] = 0.0; c1[ti] = 0.0;
+      const int ia = min(ti * 8 + g, S - 1);
+#pragma unroll
+      for (int ks = 0; ks < KS; ks++) {
+        const int k = ks * 4 + q;
+        const double av = k < S ? inv[ia + k * S] : 0.0;
+        dmma_884(c0[ti], c1[ti], av, bv[ks]);
+      }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int ti = 0; ti < TM; ti++) {
+      const int ic = ti * 8 + g, jc = tj * 8 + 2 * q;
+      if (ic < S) {
+        if (jc < NR) R.set(ic, jc, c0[ti]);
+        if (jc + 1 < NR) R.set(ic, jc + 1, c1[ti]);
+      }
+    }
+  }
   return ok;
 }
 

@@ -155,7 +155,15 @@ __global__ void __launch_bounds__(32 * NW) sweep_kernel(const DevParams p) {
 
 #pragma unroll 1
   for (int t = T - 1; t >= 0; t--) {
-    if (tid == 0) { issue_load(t); tma_store_wait_read(); }
+    if (tid == 0) {
+      issue_load(t);
+      if (t > 0) {          // next knot's record and E^{-1} towards L2 while this one is solved
+        const int pn = phys_t(p, t - 1);
+        l2_prefetch(p.knots + (pbase + pn) * PL::kstride, (uint32_t)PL::kstride * 8u);
+        l2_prefetch(p.einv + ((size_t)b * T + pn) * (size_t)(n * n), (uint32_t)(n * n) * 8u);
+      }
+      tma_store_wait_read();
+    }
     mbar_wait(bar, phase); phase ^= 1;
     cta_sync<NT>();
     PH(0);
@@ -278,6 +286,8 @@ __global__ void __launch_bounds__(32 * NW) sweep_kernel(const DevParams p) {
     PH(8);
     {
       static_assert(s % 4 == 0, "specialised sweep needs (nu + nc) % 4 == 0");
+      // blocked LDL^T solve (backward stable; an explicit inverse of Rhat was measurably less
+      // accurate on the ill-conditioned knots of the reference distribution)
       const bool okk = ldlt_solve_blocked<s, n + 1, NT, m>(tid, kkt, RhsGains<n>{ff, fb}, P, P + 4 * s);
       if (!okk) {                     // uniform: every thread computed the same pivots
         build_kkt();
@@ -306,29 +316,49 @@ __global__ void __launch_bounds__(32 * NW) sweep_kernel(const DevParams p) {
     // (9) L = AtV^T + BtV^T K  (Vxx A == AtV^T: Vxx is exactly symmetric) -> fb rows rL     (:238-239)
     //     A_pre = A + B K - mudyn L -> P block                                            (:241-242)
     {
-      constexpr int TM = (n + 7) / 8, TN = (n + 7) / 8, KSt = (m + 3) / 4;
+      constexpr int TM = (n + 7) / 8, TN = (n + 7) / 8, KSt = (m + 3) / 4, NTILE = TM * TN;
+      constexpr int NSLOT = (NTILE + NW - 1) / NW;
       const int g = lane >> 2, q = lane & 3;
-      for (int tt = warp; tt < TM * TN; tt += NW) {
-        const int ti = tt % TM, tj = tt / TM;
-        const int ic = ti * 8 + g, ia = min(ic, n - 1);
-        const int jc = tj * 8 + 2 * q, j0 = min(jc, n - 1), j1 = min(jc + 1, n - 1);
-        const int jbk = min(tj * 8 + g, n - 1);
-        double l0 = X1[j0 + ia * n], l1 = X1[j1 + ia * n];       // AtV^T
-        double a0 = A[ia + j0 * n], a1 = A[ia + j1 * n];
+      double l0[NSLOT], l1[NSLOT], a0[NSLOT], a1[NSLOT];
+      int ia[NSLOT], jbk[NSLOT];
 #pragma unroll
-        for (int ks = 0; ks < KSt; ks++) {
-          const int k = ks * 4 + q;
-          const bool kv = (m % 4 == 0) || (k < m);
-          const int kc = min(k, m - 1);
-          const double bvK = kv ? fb[(rK + kc) * n + jbk] : 0.0;
-          const double aL = kv ? BtV[kc + ia * m] : 0.0;
-          const double aB = kv ? B[ia + kc * n] : 0.0;
-          dmma_884(l0, l1, aL, bvK);
-          dmma_884(a0, a1, aB, bvK);
+      for (int u = 0; u < NSLOT; u++) {
+        const int tt = min(warp + NW * u, NTILE - 1);
+        const int ti = tt % TM, tj = tt / TM;
+        ia[u] = min(ti * 8 + g, n - 1);
+        jbk[u] = min(tj * 8 + g, n - 1);
+        const int jc = tj * 8 + 2 * q, j0 = min(jc, n - 1), j1 = min(jc + 1, n - 1);
+        l0[u] = X1[j0 + ia[u] * n]; l1[u] = X1[j1 + ia[u] * n];       // AtV^T
+        a0[u] = A[ia[u] + j0 * n];  a1[u] = A[ia[u] + j1 * n];
+      }
+#pragma unroll
+      for (int ks = 0; ks < KSt; ks++) {
+        const int k = ks * 4 + q;
+        const bool kv = (m % 4 == 0) || (k < m);
+        const int kc = min(k, m - 1);
+        double bvK[NSLOT], aL[NSLOT], aB[NSLOT];
+#pragma unroll
+        for (int u = 0; u < NSLOT; u++) {
+          bvK[u] = kv ? fb[(rK + kc) * n + jbk[u]] : 0.0;
+          aL[u] = kv ? BtV[kc + ia[u] * m] : 0.0;
+          aB[u] = kv ? B[ia[u] + kc * n] : 0.0;
         }
-        if (ic < n) {
-          if (jc < n) { fb[(rL + ic) * n + jc] = l0; P[ic + jc * n] = a0 - mudyn * l0; }
-          if (jc + 1 < n) { fb[(rL + ic) * n + jc + 1] = l1; P[ic + (jc + 1) * n] = a1 - mudyn * l1; }
+#pragma unroll
+        for (int u = 0; u < NSLOT; u++) {
+          dmma_884(l0[u], l1[u], aL[u], bvK[u]);
+          dmma_884(a0[u], a1[u], aB[u], bvK[u]);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < NSLOT; u++) {
+        const int tt = warp + NW * u;
+        if (tt < NTILE) {
+          const int ti = tt % TM, tj = tt / TM;
+          const int ic = ti * 8 + g, jc = tj * 8 + 2 * q;
+          if (ic < n) {
+            if (jc < n) { fb[(rL + ic) * n + jc] = l0[u]; P[ic + jc * n] = a0[u] - mudyn * l0[u]; }
+            if (jc + 1 < n) { fb[(rL + ic) * n + jc + 1] = l1[u]; P[ic + (jc + 1) * n] = a1[u] - mudyn * l1[u]; }
+          }
         }
       }
     }
@@ -361,25 +391,66 @@ __global__ void __launch_bounds__(32 * NW) sweep_kernel(const DevParams p) {
   {
     if (tid == 0) tma_store_wait_read();
     cta_sync<NT>();
-    const int c0 = p.nc0, s0 = n + c0, ld0 = s0 | 1;   // odd leading dimension: conflict-free rows and columns
-    double *K0 = sm;                               // overlays rec | X1 (size checked on the host)
-    double *ff0 = Gs;
-    double *wk0 = Gs + ((s0 + 1) & ~1);
+    const int c0 = p.nc0, s0 = n + c0;
     const double *G0 = p.G0 + (size_t)b * c0 * n, *g0 = p.g0 + (size_t)b * c0;
-    for (int e = tid; e < s0 * s0; e += NT) {
-      const int i = e % s0, j = e / s0;
-      double v;
-      if (j < n) v = (i < n) ? P[i + j * n] : G0[(i - n) + j * c0];
-      else v = (i == j) ? -mudyn : 0.0;
-      K0[i + j * ld0] = v;
-    }
-    for (int i = tid; i < s0; i += NT) ff0[i] = (i < n) ? -pv[i] : -g0[i - n];
-    cta_sync<NT>();
-    if (!bk_factor_cta<NT>(tid, s0, K0, ld0, kpiv, ksub, wk0, kpiv + s0)) flags |= GARB200_FLAG_BK_SINGULAR;
-    if (warp == 0) bk_solve_vec_warp<(2 * n + 31) / 32>(lane, s0, K0, ld0, kpiv, ksub, ff0, reinterpret_cast<int *>(wk0));
-    cta_sync<NT>();
     double *off = p.kkt0_ff + (size_t)b * s0;
-    for (int i = tid; i < s0; i += NT) off[i] = ff0[i];
+    // G0 == I exactly (the initial-state constraint x0 = xhat of every MPC / DDP problem,
+    // tests/gar/test_util.cpp:62-64)?  Then the second block row gives x0 = -g0 + mudyn lbd0 and
+    // the first one collapses to (I + mudyn P0) lbd0 = P0 g0 - p0: an n x n SPD-type system of
+    // the same form as Lambda above instead of the indefinite (2n)^2 Bunch-Kaufman problem.
+    int isI = (c0 == n);
+    if (isI)
+      for (int e = tid; e < n * n; e += NT) {
+        const int i = e % n, j = e / n;
+        if (G0[e] != (i == j ? 1.0 : 0.0)) isI = 0;
+      }
+    if constexpr (NT == 32) isI = __all_sync(0xffffffffu, isI); else isI = __syncthreads_and(isI);
+    if (isI) {
+      double fro = 0.0;
+      for (int e = tid; e < n * n; e += NT) fro = fma(P[e], P[e], fro);
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) fro += __shfl_xor_sync(0xffffffffu, fro, o);
+      if (lane == 0) red[warp] = fro;
+      gemv4<n, n, NT>(tid, [&](int i, int j) { return P[i + j * n]; }, [&](int j) { return g0[j]; },
+                      [&](int i) { return -pv[i]; }, [&](int i, double v) { x1v[i] = v; });
+      cta_sync<NT>();
+      fro = 0.0;
+#pragma unroll
+      for (int w = 0; w < NW; w++) fro += red[w];
+      const double *lam = x1v;
+      if (mudyn * sqrt(fro) <= 1e-9) {
+        gemv4<n, n, NT>(tid, [&](int i, int j) { return -mudyn * P[i + j * n]; }, [&](int j) { return x1v[j]; },
+                        [&](int i) { return x1v[i]; }, [&](int i, double v) { dinv[i] = v; });
+        lam = dinv;
+      } else {
+        for (int e = tid; e < n * n; e += NT) {
+          const int i = e % n, j = e / n;
+          if (i >= j) X1[e] = (i == j ? 1.0 : 0.0) + mudyn * P[e];
+        }
+        cta_sync<NT>();
+        if (!ldlt_solve_blocked<n, 1, NT>(tid, X1, RhsColMajor<n>{x1v}, Gs, dinv)) flags |= GARB200_FLAG_LLT_NOT_PD;
+      }
+      cta_sync<NT>();
+      for (int i = tid; i < n; i += NT) { off[i] = fma(mudyn, lam[i], -g0[i]); off[n + i] = lam[i]; }
+    } else {
+      const int ld0 = s0 | 1;                        // odd leading dimension: conflict-free rows and columns
+      double *K0 = sm;                               // overlays rec | X1 (size checked on the host)
+      double *ff0 = Gs;
+      double *wk0 = Gs + ((s0 + 1) & ~1);
+      for (int e = tid; e < s0 * s0; e += NT) {
+        const int i = e % s0, j = e / s0;
+        double v;
+        if (j < n) v = (i < n) ? P[i + j * n] : G0[(i - n) + j * c0];
+        else v = (i == j) ? -mudyn : 0.0;
+        K0[i + j * ld0] = v;
+      }
+      for (int i = tid; i < s0; i += NT) ff0[i] = (i < n) ? -pv[i] : -g0[i - n];
+      cta_sync<NT>();
+      if (!bk_factor_cta<NT>(tid, s0, K0, ld0, kpiv, ksub, wk0, kpiv + s0)) flags |= GARB200_FLAG_BK_SINGULAR;
+      if (warp == 0) bk_solve_vec_warp<(2 * n + 31) / 32>(lane, s0, K0, ld0, kpiv, ksub, ff0, reinterpret_cast<int *>(wk0));
+      cta_sync<NT>();
+      for (int i = tid; i < s0; i += NT) off[i] = ff0[i];
+    }
   }
   for (int e = tid; e < n * n; e += NT)
     if (!isfinite(P[e])) flags |= GARB200_FLAG_NONFINITE;

@@ -77,7 +77,7 @@ def generate_problems(batch, horizon, nx, nu, nc=0, nth=0, *, seed=42, dist="ref
         f = {}
         qsr = _wishart(rng, lead, nx + m, nx + m + 1)
         Q = qsr[..., :nx, :nx].copy()
-        if singular:
+        if singular and dist != "explicit_psd":   # "explicit_psd": convex stage costs (value function stays PSD)
             h = nx // 2
             Q[..., :h, :h] = 0.0
         f["Q"], f["S"], f["R"] = Q, qsr[..., :nx, nx:], qsr[..., nx:, nx:]
@@ -86,7 +86,7 @@ def generate_problems(batch, horizon, nx, nu, nc=0, nth=0, *, seed=42, dist="ref
         if dist == "ref":
             f["A"] = rng.standard_normal(lead + (nx, nx))
             f["E"] = 1000.0 * rng.standard_normal(lead + (nx, nx))
-        elif dist == "explicit":
+        elif dist in ("explicit", "explicit_psd"):
             # what ProxDDP feeds: explicit dynamics, E = -I (explicit-dynamics.hxx:32)
             f["A"] = 0.9 * np.eye(nx) + (0.1 / np.sqrt(nx)) * rng.standard_normal(lead + (nx, nx))
             f["E"] = np.broadcast_to(-np.eye(nx), lead + (nx, nx)).copy()

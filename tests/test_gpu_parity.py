@@ -62,9 +62,9 @@ CASES = [
     (33, 9, 4, 3, 6, 2, 1e-10, "ref"),
     (5, 0, 2, 0, 6, 2, 1e-6, "ref"),         # nu = 0 everywhere (Z = C / mueq, riccati-kernel.hxx:105-108)
     (48, 16, 0, 0, 8, 2, 1e-11, "ref"),
-    (12, 4, 0, 0, 30, 4, 1e-3, "explicit"),  # mudyn |Ptilde| large: LDL^T path of the specialised sweep
-    (36, 12, 0, 0, 20, 2, 1e-2, "explicit"),
-    (12, 4, 0, 0, 30, 3, 1e-7, "explicit"),
+    (12, 4, 0, 0, 30, 4, 1e-3, "explicit_psd"),  # mudyn |Ptilde| large: LDL^T path of the specialised sweep
+    (36, 12, 0, 0, 20, 2, 1e-2, "explicit_psd"),
+    (12, 4, 0, 0, 30, 3, 1e-7, "explicit_psd"),
 ]
 
 
@@ -349,4 +349,24 @@ def test_fast_path_indefinite_kkt_falls_back_to_bunch_kaufman(capi, oracle, shap
     assert s.used_fast_path()
     assert (s.get_flags() == 0).all()
     compare_traj(oracle, pp, mu, xs, us, vs, lb, rtol=1e-9)
+    s.close()
+
+
+@pytest.mark.parametrize("shape", [(12, 4, 15), (36, 12, 10)])
+def test_fast_path_general_initial_constraint(capi, oracle, shape):
+    """The specialised sweep solves the initial stage in reduced form when G0 == I exactly and
+    with Bunch-Kaufman on [P0 G0^T; G0 -mu I] otherwise (proximal-riccati.hxx:44-62): a dense
+    random G0 must take the second route and still match the oracle."""
+    nx, nu, T = shape
+    mu = 1e-9
+    pp = generate_problems(3, T, nx, nu, seed=5)
+    rng = np.random.default_rng(9)
+    pp.G0[1] = (np.eye(nx) + 0.3 * rng.standard_normal((nx, nx))).reshape(-1, order="F")
+    pp.G0[2] = rng.standard_normal((nx, nx)).reshape(-1, order="F")
+    s, xs, us, vs, lb = solve_gpu(capi, pp, mu)
+    assert s.used_fast_path() and (s.get_flags() == 0).all()
+    compare_traj(oracle, pp, mu, xs, us, vs, lb, rtol=1e-9)
+    for b in range(3):
+        ref = oracle.prox_solve(pp, mu, mu, b=b)
+        assert relerr(s.get_initial(b)[0], ref["kkt0_ff"]) < 1e-9
     s.close()
