@@ -549,14 +549,20 @@ __device__ __forceinline__ bool gj_inverse_regs(int sub, unsigned mask, const do
     for (int j = 0; j < N; j++) a[s][j] = act[s] ? Eg[row + j * N] : 0.0;
   }
   bool ok = true;
-#pragma unroll
+  static_assert(N % 2 == 0, "register Gauss-Jordan: even N (128-bit shared-memory accesses)");
+  double2 *srow2 = reinterpret_cast<double2 *>(srow);
+  // The register file is ROTATED by one column per step (the column being eliminated always
+  // sits at index 0, the finished inverse column is appended at index N-1), so the loop body
+  // has static register indices without unrolling over k: the whole kernel stays a few hundred
+  // instructions and lives in the instruction cache.  After N steps the order is restored.
+#pragma unroll 1
   for (int k = 0; k < N; k++) {
     // pivot search: 64-bit key = bits(|a|) with the low 7 bits replaced by (127 - row)
     unsigned long long best = 0ull;
 #pragma unroll
     for (int s = 0; s < RPL; s++) {
       const int row = sub + LPM * s;
-      unsigned long long key = (unsigned long long)__double_as_longlong(fabs(a[s][k]));
+      unsigned long long key = (unsigned long long)__double_as_longlong(fabs(a[s][0]));
       key = (key & ~0x7Full) | (unsigned long long)(127 - row);
       if (act[s] && key > best) best = key;
     }
@@ -565,9 +571,9 @@ __device__ __forceinline__ bool gj_inverse_regs(int sub, unsigned mask, const do
     const unsigned mlo = __reduce_max_sync(mask, (best != 0ull && hi == mhi) ? lo : 0u);
     const int r = 127 - (int)(mlo & 0x7Fu);
     const int rl = r % LPM, rs = r / LPM;
-    double pcand = a[0][k];
+    double pcand = a[0][0];
 #pragma unroll
-    for (int s = 1; s < RPL; s++) if (rs == s) pcand = a[s][k];
+    for (int s = 1; s < RPL; s++) if (rs == s) pcand = a[s][0];
     const double pval = __shfl_sync(mask, pcand, rl, LPM);
     if (pval == 0.0) ok = false;
     const double pinv = __drcp_rn(pval);
@@ -576,35 +582,38 @@ __device__ __forceinline__ bool gj_inverse_regs(int sub, unsigned mask, const do
       for (int s = 0; s < RPL; s++)
         if (rs == s) {
 #pragma unroll
-          for (int j = 0; j < N; j++) srow[j] = a[s][j];
+          for (int j = 0; j < N; j += 2) srow2[j / 2] = make_double2(a[s][j], a[s][j + 1]);
         }
     }
     if (sub == 0) spiv[k] = r;
     __syncwarp(mask);
     double f[RPL];
+    bool isp[RPL];
 #pragma unroll
     for (int s = 0; s < RPL; s++) {
-      const bool isp = (sub + LPM * s) == r;
-      f[s] = isp ? 0.0 : a[s][k] * pinv;
+      isp[s] = (sub + LPM * s) == r;
+      f[s] = isp[s] ? 0.0 : a[s][0] * pinv;
     }
 #pragma unroll
-    for (int j = 0; j < N; j++) {
-      if (j == k) continue;
-      const double bj = srow[j];
+    for (int j = 0; j < N; j += 2) {
+      const double2 bj = srow2[j / 2];
 #pragma unroll
-      for (int s = 0; s < RPL; s++) a[s][j] = fma(-f[s], bj, a[s][j]);
+      for (int s = 0; s < RPL; s++) {
+        if (j > 0) a[s][j - 1] = fma(-f[s], bj.x, a[s][j]);
+        a[s][j] = fma(-f[s], bj.y, a[s][j + 1]);
+      }
     }
 #pragma unroll
     for (int s = 0; s < RPL; s++) {
-      const bool isp = (sub + LPM * s) == r;
-      a[s][k] = isp ? pinv : -f[s];
-      if (isp) {
+      a[s][N - 1] = isp[s] ? pinv : -f[s];
+      if (isp[s]) {
         act[s] = false;
         sig[s] = k;
 #pragma unroll
-        for (int j = 0; j < N; j++) if (j != k) a[s][j] *= pinv;
+        for (int j = 0; j < N - 1; j++) a[s][j] *= pinv;
       }
     }
+    __syncwarp(mask);
   }
   __syncwarp(mask);
   if (do_store) {

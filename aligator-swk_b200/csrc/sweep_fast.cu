@@ -10,6 +10,7 @@
 //                  (NW warps) per problem, knot record + Einv staged by 1-D TMA bulk copies,
 //                  all n^3 contractions on the FP64 tensor pipe (DMMA), GEMVs riding along
 //                  as an extra column of the GEMM they belong to.
+#include <cstdlib>
 #include "fast.cuh"
 #include "kernels.cuh"
 
@@ -68,7 +69,7 @@ template <int NX, int NU, int NC> struct FastPlan {
 };
 
 template <int NX, int NU, int NC, int NW, bool PROF>
-__global__ void __launch_bounds__(32 * NW) sweep_kernel(const DevParams p) {
+__global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : 1)) sweep_kernel(const DevParams p) {
   extern __shared__ __align__(16) double sm[];
   using PL = FastPlan<NX, NU, NC>;
   constexpr int n = NX, m = NU, c = NC, s = NU + NC, NT = 32 * NW;
@@ -500,7 +501,10 @@ int launch_backward_fast(const DevParams &p, const int *h_nu_t, const int *h_nc_
   for (int t = 0; t < p.T; t++)
     if (h_nu_t[t] != p.nu || h_nc_t[t] != p.nc) return -3;
   if (p.nx == 12 && p.nu == 4 && p.nc == 0) return launch_fast_t<12, 4, 0, 1>(p, st);
-  if (p.nx == 36 && p.nu == 12 && p.nc == 0) return launch_fast_t<36, 12, 0, 4>(p, st);
+  if (p.nx == 36 && p.nu == 12 && p.nc == 0) {
+    static const int nw = getenv("GARB200_NW36") ? atoi(getenv("GARB200_NW36")) : 4;   // tuning knob
+    return nw == 8 ? launch_fast_t<36, 12, 0, 8>(p, st) : launch_fast_t<36, 12, 0, 4>(p, st);
+  }
   return -3;
 }
 
