@@ -182,7 +182,7 @@ def gpu_arm(args, w, rank, world, local_rank):
     import torch
     import garb200_pkg
     garb200_pkg.load()
-    from aligator_swk_b200 import capi
+    from aligator_swk_b200 import capi, sharding
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — the product path has no CPU fallback")
@@ -214,13 +214,11 @@ def gpu_arm(args, w, rank, world, local_rank):
     send = recv = None
     out_ptrs = {}
     if dist is not None:
-        sizes = [B * (T + 1) * nx, B * (T + 1) * nu, B * (T + 1) * nc, B * (nx + T * nx)]
+        sizes = sharding.trajectory_sizes(B, T, nx, nu, nc)
         send = torch.empty(sum(sizes), dtype=torch.float64, device="cuda")
         recv = [torch.empty_like(send) for _ in range(world)] if rank == 0 else None
-        off = 0
-        for name, sz in zip(("d_xs", "d_us", "d_vs", "d_lbdas"), sizes):
-            out_ptrs[name] = send.data_ptr() + 8 * off
-            off += sz
+        for name, view in zip(("d_xs", "d_us", "d_vs", "d_lbdas"), sharding.carve(send, sizes)):
+            out_ptrs[name] = view.data_ptr()
 
     def step_device():
         s.backward(MU, MU)
@@ -228,7 +226,7 @@ def gpu_arm(args, w, rank, world, local_rank):
 
     def gather():
         if dist is not None:
-            dist.gather(send, recv, dst=0)
+            sharding.gather_to_root(dist, send, rank, world, recv)
 
     # ---- value: device-resident inputs -> device-resident outputs -----------------------
     for _ in range(W):
@@ -285,7 +283,8 @@ def gpu_arm(args, w, rank, world, local_rank):
     ach_gbs = B * (b_in + b_gain) / bwd / 1e9
     ach_tf = B * f_bwd / bwd / 1e12
     hbm_bound = (ach_gbs / hbm_peak) >= (ach_tf / fp64_peak)
-    roof = {"kernel": "backward_kernel", "bound": "hbm" if hbm_bound else "fp64",
+    roof = {"kernel": "backward_kernel", "bound": "hbm" if hbm_bound else "tensor",
+            "bound_detail": "HBM bytes" if hbm_bound else "FP64 on the tensor pipe (DMMA m8n8k4; no tcgen05 kind for f64)",
             "achieved": ach_gbs if hbm_bound else ach_tf, "peak": hbm_peak if hbm_bound else fp64_peak,
             "unit": "GB/s" if hbm_bound else "TFLOP/s",
             "frac": (ach_gbs / hbm_peak) if hbm_bound else (ach_tf / fp64_peak), "traffic": None,
