@@ -44,6 +44,58 @@ __device__ __forceinline__ void mma_gemm(int warp, int lane, FA a, FB b, FC cin,
   constexpr int NSLOT = (NTILE + NW - 1) / NW;      // tiles per warp, ALL kept in flight:
   constexpr int KS = (K + 3) / 4;                   // NSLOT independent DMMA accumulation chains
   const int g = lane >> 2, q = lane & 3;
+  // Strip mode: when the row tiles (or else the column tiles) divide evenly over the warps,
+  // a warp owns whole 8-row strips (8-column strips) of C, so one A (B) fragment feeds every
+  // tile of the strip: (SR + SC) shared-memory loads per SR * SC DMMAs instead of 2 per DMMA.
+  constexpr bool ROWS = (TM % NW == 0);
+  constexpr bool COLS = !ROWS && (TN % NW == 0);
+  if constexpr (ROWS || COLS) {
+    constexpr int SR = ROWS ? TM / NW : TM, SC = ROWS ? TN : TN / NW;
+    double acc[SR][SC][2];
+    int ia[SR], jb[SC];
+#pragma unroll
+    for (int r = 0; r < SR; r++) ia[r] = min((ROWS ? warp + NW * r : r) * 8 + g, M - 1);
+#pragma unroll
+    for (int u = 0; u < SC; u++) jb[u] = min((ROWS ? u : warp + NW * u) * 8 + g, N - 1);
+#pragma unroll
+    for (int r = 0; r < SR; r++)
+#pragma unroll
+      for (int u = 0; u < SC; u++) {
+        const int jc = (ROWS ? u : warp + NW * u) * 8 + 2 * q;
+        acc[r][u][0] = cin(ia[r], min(jc, N - 1));
+        acc[r][u][1] = cin(ia[r], min(jc + 1, N - 1));
+      }
+#pragma unroll
+    for (int ks = 0; ks < KS; ks++) {
+      const int k = ks * 4 + q;
+      double av[SR], bv[SC];
+#pragma unroll
+      for (int r = 0; r < SR; r++) {
+        if constexpr (K % 4 == 0) av[r] = a(ia[r], k);
+        else av[r] = (k < K) ? a(ia[r], min(k, K - 1)) : 0.0;
+      }
+#pragma unroll
+      for (int u = 0; u < SC; u++) {
+        if constexpr (K % 4 == 0) bv[u] = b(k, jb[u]);
+        else bv[u] = (k < K) ? b(min(k, K - 1), jb[u]) : 0.0;
+      }
+#pragma unroll
+      for (int r = 0; r < SR; r++)
+#pragma unroll
+        for (int u = 0; u < SC; u++) dmma_884(acc[r][u][0], acc[r][u][1], av[r], bv[u]);
+    }
+#pragma unroll
+    for (int r = 0; r < SR; r++)
+#pragma unroll
+      for (int u = 0; u < SC; u++) {
+        const int ic = (ROWS ? warp + NW * r : r) * 8 + g, jc = (ROWS ? u : warp + NW * u) * 8 + 2 * q;
+        if (ic < M) {
+          if (jc < N) store(ic, jc, acc[r][u][0]);
+          if (jc + 1 < N) store(ic, jc + 1, acc[r][u][1]);
+        }
+      }
+    return;
+  }
   double acc[NSLOT][2];
   int ia[NSLOT], jb[NSLOT];
 #pragma unroll
@@ -540,11 +592,13 @@ __device__ __forceinline__ bool gj_inverse_regs(int sub, unsigned mask, const do
   double a[RPL][N];
   int sig[RPL];
   bool act[RPL];
+  double rscale[RPL];
 #pragma unroll
   for (int s = 0; s < RPL; s++) {
     const int row = sub + LPM * s;
     act[s] = row < N;
     sig[s] = 0;
+    rscale[s] = 1.0;
 #pragma unroll
     for (int j = 0; j < N; j++) a[s][j] = act[s] ? Eg[row + j * N] : 0.0;
   }
@@ -603,14 +657,16 @@ __device__ __forceinline__ bool gj_inverse_regs(int sub, unsigned mask, const do
         a[s][j] = fma(-f[s], bj.y, a[s][j + 1]);
       }
     }
+    // A pivot row is NOT scaled by 1/pivot here: it keeps its raw values (new column entry 1)
+    // and later steps treat it like any other row, which commutes with the row scaling; the
+    // scale factor is applied once in the final store.
 #pragma unroll
     for (int s = 0; s < RPL; s++) {
-      a[s][N - 1] = isp[s] ? pinv : -f[s];
+      a[s][N - 1] = isp[s] ? 1.0 : -f[s];
       if (isp[s]) {
         act[s] = false;
         sig[s] = k;
-#pragma unroll
-        for (int j = 0; j < N - 1; j++) a[s][j] *= pinv;
+        rscale[s] = pinv;
       }
     }
     __syncwarp(mask);
@@ -622,7 +678,175 @@ __device__ __forceinline__ bool gj_inverse_regs(int sub, unsigned mask, const do
       const int pc = spiv[c];
 #pragma unroll
       for (int s = 0; s < RPL; s++)
-        if (sub + LPM * s < N) Xg[sig[s] + pc * N] = a[s][c];
+        if (sub + LPM * s < N) Xg[sig[s] + pc * N] = a[s][c] * rscale[s];
+    }
+  }
+  return ok;
+}
+
+// ------------------------------------------------------------------------------------------
+// Block Gauss-Jordan inverse on the FP64 tensor pipe: one warp per N x N matrix (N % 4 == 0),
+// the whole (padded) matrix lives in registers as m8n8k4 accumulator tiles for all N/4 block
+// steps.  Block step kb (columns c0 = 4 kb .. c0 + 3):
+//   1. the 4-column panel leaves the tiles through shared memory and is reduced row-per-lane by
+//      an ordinary in-place Gauss-Jordan with partial pivoting over ALL not-yet-pivoted rows
+//      (so the pivot order is the one of unblocked partial pivoting on this panel); afterwards
+//      panel row i holds -A[i,panel] B^{-1} (other rows) or the rows of B^{-1} (pivot rows),
+//      B = A[pivot rows, panel].
+//   2. the 4 raw pivot rows leave the tiles (their tile rows are zeroed), with the panel
+//      columns replaced by I_4.
+//   3. one rank-4 update  C += panel' * pivot_rows  = 1 DMMA per tile.
+// Rows never move: X(step(r), piv[c]) = C(r, c) un-permutes in the final store like
+// gj_inverse_regs.  Shared memory per warp: GjDmma<N>::SMEM doubles + GjDmma<N>::SINTS ints.
+// ------------------------------------------------------------------------------------------
+template <int N> struct GjDmma {
+  static_assert(N % 4 == 0 && N <= 64, "block Gauss-Jordan: N % 4 == 0, N <= 64");
+  static constexpr int NTL = (N + 7) / 8, NP = NTL * 8, NB = N / 4;
+  static constexpr int PLD = (NP % 16 == 8) ? NP + 4 : NP + 12;   // == 12 (mod 16): conflict-free B fragments
+  static constexpr int RPL = (NP + 31) / 32;
+  static constexpr int PAN = 0, PROW = NP * 4, SMEM = PROW + 4 * PLD;
+  static constexpr int SINTS = 2 * NP;     // piv[c] | step[r]
+};
+
+template <int N>
+__device__ __forceinline__ bool gj_inverse_dmma(int lane, const double *__restrict__ Eg,
+                                                double *__restrict__ Xg, bool do_store,
+                                                double *sw, int *si) {
+  using G = GjDmma<N>;
+  constexpr int NTL = G::NTL, NP = G::NP, NB = G::NB, PLD = G::PLD, RPL = G::RPL;
+  double *pan = sw + G::PAN, *prow = sw + G::PROW;
+  int *spiv = si, *sstep = si + NP;
+  const int g = lane >> 2, q = lane & 3;
+  double c[NTL][NTL][2];
+#pragma unroll
+  for (int mt = 0; mt < NTL; mt++)
+#pragma unroll
+    for (int nt = 0; nt < NTL; nt++) {
+      const int row = g + 8 * mt, col = 8 * nt + 2 * q;
+      c[mt][nt][0] = (row < N && col < N) ? Eg[row + col * N] : 0.0;
+      c[mt][nt][1] = (row < N && col + 1 < N) ? Eg[row + (col + 1) * N] : 0.0;
+    }
+  bool act[RPL];
+#pragma unroll
+  for (int s = 0; s < RPL; s++) act[s] = lane + 32 * s < N;
+  bool ok = true;
+#pragma unroll
+  for (int kb = 0; kb < NB; kb++) {
+    constexpr int dummy = 0; (void)dummy;
+    const int ntp = kb >> 1, h = kb & 1, c0 = 4 * kb;
+    // 1. panel out of the tiles (and zero it there)
+    if ((q >> 1) == h) {
+#pragma unroll
+      for (int mt = 0; mt < NTL; mt++) {
+        *reinterpret_cast<double2 *>(pan + (g + 8 * mt) * 4 + 2 * (q & 1)) = make_double2(c[mt][ntp][0], c[mt][ntp][1]);
+        c[mt][ntp][0] = 0.0; c[mt][ntp][1] = 0.0;
+      }
+    }
+    __syncwarp();
+    double a[RPL][4];
+#pragma unroll
+    for (int s = 0; s < RPL; s++) {
+      const int row = lane + 32 * s;
+      if (row < NP) {
+        const double2 lo = *reinterpret_cast<const double2 *>(pan + row * 4), hi = *reinterpret_cast<const double2 *>(pan + row * 4 + 2);
+        a[s][0] = lo.x; a[s][1] = lo.y; a[s][2] = hi.x; a[s][3] = hi.y;
+      } else {
+        a[s][0] = a[s][1] = a[s][2] = a[s][3] = 0.0;
+      }
+    }
+    int rsel[4];
+#pragma unroll
+    for (int ss = 0; ss < 4; ss++) {
+      unsigned long long best = 0ull;
+#pragma unroll
+      for (int s = 0; s < RPL; s++) {
+        unsigned long long key = (unsigned long long)__double_as_longlong(fabs(a[s][ss]));
+        key = (key & ~0x7Full) | (unsigned long long)(127 - (lane + 32 * s));
+        if (act[s] && key > best) best = key;
+      }
+      const unsigned hi32 = (unsigned)(best >> 32), lo32 = (unsigned)best;
+      const unsigned mhi = __reduce_max_sync(0xffffffffu, hi32);
+      const unsigned mlo = __reduce_max_sync(0xffffffffu, (best != 0ull && hi32 == mhi) ? lo32 : 0u);
+      const int r = 127 - (int)(mlo & 0x7Fu);
+      const int rl = r & 31, rs = r >> 5;
+      rsel[ss] = r;
+      double pr[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        double v = a[0][j];
+#pragma unroll
+        for (int s = 1; s < RPL; s++) if (rs == s) v = a[s][j];
+        pr[j] = __shfl_sync(0xffffffffu, v, rl);
+      }
+      if (pr[ss] == 0.0) ok = false;
+      const double pinv = __drcp_rn(pr[ss]);
+#pragma unroll
+      for (int j = 0; j < 4; j++) pr[j] *= pinv;        // scaled pivot row
+#pragma unroll
+      for (int s = 0; s < RPL; s++) {
+        const bool isp = (lane + 32 * s) == r;
+        const double m = a[s][ss];
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+          if (j != ss) a[s][j] = isp ? pr[j] : fma(-m, pr[j], a[s][j]);
+        a[s][ss] = isp ? pinv : -m * pinv;
+        if (isp) { act[s] = false; sstep[r] = c0 + ss; }
+      }
+      if (lane == 0) spiv[c0 + ss] = r;
+    }
+    // transformed panel back (A operand of the update)
+#pragma unroll
+    for (int s = 0; s < RPL; s++) {
+      const int row = lane + 32 * s;
+      if (row < NP) {
+        *reinterpret_cast<double2 *>(pan + row * 4) = make_double2(a[s][0], a[s][1]);
+        *reinterpret_cast<double2 *>(pan + row * 4 + 2) = make_double2(a[s][2], a[s][3]);
+      }
+    }
+    // 2. raw pivot rows out of the tiles, zeroed there
+#pragma unroll
+    for (int mt = 0; mt < NTL; mt++) {
+      const int row = g + 8 * mt;
+      const int sidx = row == rsel[0] ? 0 : row == rsel[1] ? 1 : row == rsel[2] ? 2 : row == rsel[3] ? 3 : -1;
+      if (sidx >= 0) {
+#pragma unroll
+        for (int nt = 0; nt < NTL; nt++) {
+          *reinterpret_cast<double2 *>(prow + sidx * PLD + 8 * nt + 2 * q) = make_double2(c[mt][nt][0], c[mt][nt][1]);
+          c[mt][nt][0] = 0.0; c[mt][nt][1] = 0.0;
+        }
+      }
+    }
+    __syncwarp();
+    if (lane < 16) prow[(lane >> 2) * PLD + c0 + (lane & 3)] = ((lane >> 2) == (lane & 3)) ? 1.0 : 0.0;
+    __syncwarp();
+    // 3. rank-4 update, one DMMA per tile
+    double af[NTL], bf[NTL];
+#pragma unroll
+    for (int mt = 0; mt < NTL; mt++) af[mt] = pan[(g + 8 * mt) * 4 + q];
+#pragma unroll
+    for (int nt = 0; nt < NTL; nt++) bf[nt] = prow[q * PLD + g + 8 * nt];
+#pragma unroll
+    for (int mt = 0; mt < NTL; mt++)
+#pragma unroll
+      for (int nt = 0; nt < NTL; nt++) dmma_884(c[mt][nt][0], c[mt][nt][1], af[mt], bf[nt]);
+    __syncwarp();
+  }
+  if (do_store) {
+    int sg[NTL];
+#pragma unroll
+    for (int mt = 0; mt < NTL; mt++) sg[mt] = (g + 8 * mt < N) ? sstep[g + 8 * mt] : 0;
+#pragma unroll
+    for (int nt = 0; nt < NTL; nt++) {
+      const int col = 8 * nt + 2 * q;
+      if (col < N) {
+        const int p0 = spiv[col], p1 = spiv[col + 1];
+#pragma unroll
+        for (int mt = 0; mt < NTL; mt++)
+          if (g + 8 * mt < N) {
+            Xg[sg[mt] + p0 * N] = c[mt][nt][0];
+            Xg[sg[mt] + p1 * N] = c[mt][nt][1];
+          }
+      }
     }
   }
   return ok;

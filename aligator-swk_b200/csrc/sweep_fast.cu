@@ -39,6 +39,24 @@ __global__ void __launch_bounds__(32 * WPB) einv_kernel(const DevParams p) {
   if (!ok && sub == 0 && valid) atomicOr(reinterpret_cast<int *>(p.flags) + b, GARB200_FLAG_LU_SINGULAR);
 }
 
+// Same pre-pass on the tensor pipe (block Gauss-Jordan, fast.cuh): one warp per matrix.
+template <int N, int WPB>
+__global__ void __launch_bounds__(32 * WPB, 3) einv_dmma_kernel(const DevParams p) {
+  using G = GjDmma<N>;
+  __shared__ __align__(16) double s_w[WPB][G::SMEM];
+  __shared__ int s_i[WPB][G::SINTS];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long total = (long long)p.batch * p.T;
+  long long w = (long long)blockIdx.x * WPB + warp;
+  const bool valid = w < total;
+  if (!valid) w = total - 1;
+  const int b = (int)(w / p.T), t = (int)(w % p.T);
+  const double *Eg = p.knots + ((size_t)b * (p.T + 1) + phys_t(p, t)) * p.KL.stride + p.KL.E;
+  double *Xg = p.einv + ((size_t)b * p.T + phys_t(p, t)) * (size_t)(N * N);
+  const bool ok = gj_inverse_dmma<N>(lane, Eg, Xg, valid, s_w[warp], s_i[warp]);
+  if (!ok && lane == 0 && valid) atomicOr(reinterpret_cast<int *>(p.flags) + b, GARB200_FLAG_LU_SINGULAR);
+}
+
 // ---- shared-memory plan of the sweep (doubles) ---------------------------------------------
 template <int NX, int NU, int NC> struct FastPlan {
   static constexpr int n = NX, m = NU, c = NC, s = NU + NC;
@@ -51,6 +69,10 @@ template <int NX, int NU, int NC> struct FastPlan {
   static_assert(oS == oQ + n * n && oB == oA + n * n, "[Q|S] and [A|B] must be contiguous (even n*n)");
   static constexpr int nrows = m + c + 2 * n;
   static constexpr int gff = 0, gfb = r2(nrows), gstride = r2(gfb + nrows * n);
+  // only ff and the K / Z rows of fb are staged in shared memory (they are operands of later
+  // steps); the L and A rows go from the accumulators straight to the gains record in HBM
+  static constexpr int gpart = r2(gfb + s * n);
+  static_assert(n % 2 == 0, "row-major fb rows are written as 16-byte pairs");
   // smem
   static constexpr int rec = 0;
   static constexpr int X1 = r2(rec + kstride);          // n x (n+1)
@@ -63,13 +85,13 @@ template <int NX, int NU, int NC> struct FastPlan {
   static constexpr int rhat = r2(dinv + n);             // 16 doubles of reduction scratch
   static constexpr int atvx = r2(rhat + 16);            // n + m
   static constexpr int G = r2(atvx + n + m);            // gains staging record
-  static constexpr int ints = r2(G + gstride);          // pivots: KS ints
+  static constexpr int ints = r2(G + gpart);            // pivots: KS ints
   static constexpr int bar = r2(ints + (KS + 1) / 2);
   static constexpr int total = bar + 2;
 };
 
 template <int NX, int NU, int NC, int NW, bool PROF>
-__global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : 1)) sweep_kernel(const DevParams p) {
+__global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : NW == 5 ? 3 : 1)) sweep_kernel(const DevParams p) {
   extern __shared__ __align__(16) double sm[];
   using PL = FastPlan<NX, NU, NC>;
   constexpr int n = NX, m = NU, c = NC, s = NU + NC, NT = 32 * NW;
@@ -106,7 +128,7 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : 1)) sweep_kernel(const
   };
 
   if (tid == 0) { mbar_init(bar, 1); fence_mbar_init(); }
-  for (int e = tid; e < PL::gstride; e += NT) Gs[e] = 0.0;
+  for (int e = tid; e < PL::gpart; e += NT) Gs[e] = 0.0;
   cta_sync<NT>();
   uint32_t phase = 0;
   const size_t pbase = (size_t)b * (T + 1);
@@ -128,7 +150,7 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : 1)) sweep_kernel(const
     fence_proxy_async();
     cta_sync<NT>();
     if (tid == 0) {
-      tma_store_1d(p.gains + (pbase + phys_t(p, t)) * p.GL.stride, Gs, (uint32_t)PL::gstride * 8u);
+      tma_store_1d(p.gains + (pbase + phys_t(p, t)) * p.GL.stride, Gs, (uint32_t)PL::gpart * 8u);
       tma_store_commit();
     }
   };
@@ -150,6 +172,10 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : 1)) sweep_kernel(const
   for (int e = tid; e < n * n; e += NT) P[e] = Q[e];
   for (int i = tid; i < n; i += NT) pv[i] = qv[i];
   store_gains(T);
+  {
+    double *gT = p.gains + (pbase + phys_t(p, T)) * p.GL.stride;
+    for (int e = PL::gpart + tid; e < PL::gstride; e += NT) gT[e] = 0.0;
+  }
   store_value(T);
   fence_proxy_async();
   cta_sync<NT>();
@@ -316,10 +342,48 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : 1)) sweep_kernel(const
     }
     // (9) L = AtV^T + BtV^T K  (Vxx A == AtV^T: Vxx is exactly symmetric) -> fb rows rL     (:238-239)
     //     A_pre = A + B K - mudyn L -> P block                                            (:241-242)
+    double *gfbg = p.gains + (pbase + phys_t(p, t)) * p.GL.stride + PL::gfb;   // fb rows of this knot in HBM
     {
       constexpr int TM = (n + 7) / 8, TN = (n + 7) / 8, KSt = (m + 3) / 4, NTILE = TM * TN;
-      constexpr int NSLOT = (NTILE + NW - 1) / NW;
       const int g = lane >> 2, q = lane & 3;
+      if constexpr (TM % NW == 0) {        // row strips: one A-side fragment pair feeds the whole strip
+        constexpr int SR = TM / NW;
+#pragma unroll
+        for (int r = 0; r < SR; r++) {
+          const int ic = (warp + NW * r) * 8 + g, ia = min(ic, n - 1);
+          double l0[TN], l1[TN], a0[TN], a1[TN];
+          int jbk[TN];
+#pragma unroll
+          for (int u = 0; u < TN; u++) {
+            jbk[u] = min(u * 8 + g, n - 1);
+            const int jc = u * 8 + 2 * q, j0 = min(jc, n - 1), j1 = min(jc + 1, n - 1);
+            l0[u] = X1[j0 + ia * n]; l1[u] = X1[j1 + ia * n];
+            a0[u] = A[ia + j0 * n];  a1[u] = A[ia + j1 * n];
+          }
+#pragma unroll
+          for (int ks = 0; ks < KSt; ks++) {
+            const int k = ks * 4 + q;
+            const bool kv = (m % 4 == 0) || (k < m);
+            const int kc = min(k, m - 1);
+            const double aL = kv ? BtV[kc + ia * m] : 0.0, aB = kv ? B[ia + kc * n] : 0.0;
+            double bvK[TN];
+#pragma unroll
+            for (int u = 0; u < TN; u++) bvK[u] = kv ? fb[(rK + kc) * n + jbk[u]] : 0.0;
+#pragma unroll
+            for (int u = 0; u < TN; u++) { dmma_884(l0[u], l1[u], aL, bvK[u]); dmma_884(a0[u], a1[u], aB, bvK[u]); }
+          }
+#pragma unroll
+          for (int u = 0; u < TN; u++) {
+            const int jc = u * 8 + 2 * q;
+            if (ic < n && jc < n) {
+              *reinterpret_cast<double2 *>(gfbg + (rL + ic) * n + jc) = make_double2(l0[u], l1[u]);
+              P[ic + jc * n] = a0[u] - mudyn * l0[u];
+              P[ic + (jc + 1) * n] = a1[u] - mudyn * l1[u];
+            }
+          }
+        }
+      } else {
+      constexpr int NSLOT = (NTILE + NW - 1) / NW;
       double l0[NSLOT], l1[NSLOT], a0[NSLOT], a1[NSLOT];
       int ia[NSLOT], jbk[NSLOT];
 #pragma unroll
@@ -356,11 +420,13 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : 1)) sweep_kernel(const
         if (tt < NTILE) {
           const int ti = tt % TM, tj = tt / TM;
           const int ic = ti * 8 + g, jc = tj * 8 + 2 * q;
-          if (ic < n) {
-            if (jc < n) { fb[(rL + ic) * n + jc] = l0[u]; P[ic + jc * n] = a0[u] - mudyn * l0[u]; }
-            if (jc + 1 < n) { fb[(rL + ic) * n + jc + 1] = l1[u]; P[ic + (jc + 1) * n] = a1[u] - mudyn * l1[u]; }
+          if (ic < n && jc < n) {
+            *reinterpret_cast<double2 *>(gfbg + (rL + ic) * n + jc) = make_double2(l0[u], l1[u]);
+            P[ic + jc * n] = a0[u] - mudyn * l0[u];
+            P[ic + (jc + 1) * n] = a1[u] - mudyn * l1[u];
           }
         }
+      }
       }
     }
     cta_sync<NT>();
@@ -370,7 +436,7 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : 1)) sweep_kernel(const
         [&](int i, int k) { return -Einv[i + k * n]; },
         [&](int k, int j) { return P[k + j * n]; },
         [](int, int) { return 0.0; },
-        [&](int i, int j, double v) { if (j < n) fb[(rA + i) * n + j] = v; else ff[rA + i] = v; });
+        [&](int i, int j, double v) { if (j < n) gfbg[(rA + i) * n + j] = v; else ff[rA + i] = v; });
     cta_sync<NT>();
     PH(11);
     // (11) [Pmat | pvec] = [Qhat | qhat] + Shat [K | kff] + C^T [Z | zff]                  (:249-250)
@@ -477,11 +543,16 @@ static int launch_fast_t(const DevParams &p, cudaStream_t st) {
   // pre-pass
   constexpr int WPB = 4;
   constexpr int MPB = WPB * GjShape<NX>::MPW;
-  auto ke = einv_kernel<NX, WPB>;
   const long long total = (long long)p.batch * p.T;
   int launched = 0;
   if (total > 0) {
-    ke<<<(unsigned)((total + MPB - 1) / MPB), 32 * WPB, 0, st>>>(p);
+    static const bool force_regs = [] { const char *e = getenv("GARB200_EINV"); return e && e[0] == 'r'; }();
+    if constexpr (NX % 4 == 0 && NX > 16) {
+      if (!force_regs) einv_dmma_kernel<NX, WPB><<<(unsigned)((total + WPB - 1) / WPB), 32 * WPB, 0, st>>>(p);
+      else einv_kernel<NX, WPB><<<(unsigned)((total + MPB - 1) / MPB), 32 * WPB, 0, st>>>(p);
+    } else {
+      einv_kernel<NX, WPB><<<(unsigned)((total + MPB - 1) / MPB), 32 * WPB, 0, st>>>(p);
+    }
     if (cudaGetLastError() != cudaSuccess) return -2;
     launched++;
   }
@@ -502,8 +573,9 @@ int launch_backward_fast(const DevParams &p, const int *h_nu_t, const int *h_nc_
     if (h_nu_t[t] != p.nu || h_nc_t[t] != p.nc) return -3;
   if (p.nx == 12 && p.nu == 4 && p.nc == 0) return launch_fast_t<12, 4, 0, 1>(p, st);
   if (p.nx == 36 && p.nu == 12 && p.nc == 0) {
-    static const int nw = getenv("GARB200_NW36") ? atoi(getenv("GARB200_NW36")) : 4;   // tuning knob
-    return nw == 8 ? launch_fast_t<36, 12, 0, 8>(p, st) : launch_fast_t<36, 12, 0, 4>(p, st);
+    static const int nw = getenv("GARB200_NW36") ? atoi(getenv("GARB200_NW36")) : 5;   // tuning knob
+    return nw == 8 ? launch_fast_t<36, 12, 0, 8>(p, st) : nw == 5 ? launch_fast_t<36, 12, 0, 5>(p, st)
+                                                         : launch_fast_t<36, 12, 0, 4>(p, st);
   }
   return -3;
 }
