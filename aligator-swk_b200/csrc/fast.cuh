@@ -304,18 +304,25 @@ __device__ __forceinline__ bool ldlt_solve_blocked(int tid, double *S, RH R, dou
     const double a00 = Dg[0], a10 = Dg[1], a20 = Dg[2], a30 = Dg[3];
     const double a11 = Dg[1 + N], a21 = Dg[2 + N], a31 = Dg[3 + N];
     const double a22 = Dg[2 + 2 * N], a32 = Dg[3 + 2 * N], a33 = Dg[3 + 3 * N];
+    // The reciprocal pivots come in PAIRS (2x2 leading minors): 1/d1 = a00 / (a00 a11 - a10^2)
+    // does not wait for 1/d0, which shortens the dependent FP64 chain of the block from ~30 to
+    // ~20 operations.  Dependent FP64 latency is what this phase costs: the other CTAs of the SM
+    // keep the FP64 pipe full of DMMAs, so every dependent DFMA waits ~100 cycles (measured).
     const double i0 = __drcp_rn(a00);
+    const double det01 = fma(a00, a11, -a10 * a10);
+    const double i1 = a00 * __drcp_rn(det01);
     const double l10 = a10 * i0, l20 = a20 * i0, l30 = a30 * i0;
-    const double d1 = fma(-l10, a10, a11);
+    const double d1 = det01 * i0;
     const double w21 = fma(-l20, a10, a21), w31 = fma(-l30, a10, a31);     // unscaled
-    const double i1 = __drcp_rn(d1);
     const double l21 = w21 * i1, l31 = w31 * i1;
     const double d2 = fma(-l21, w21, fma(-l20, a20, a22));
     const double w32 = fma(-l31, w21, fma(-l30, a20, a32));
+    const double s33 = fma(-l31, w31, fma(-l30, a30, a33));
     const double i2 = __drcp_rn(d2);
+    const double det23 = fma(d2, s33, -w32 * w32);
+    const double i3 = d2 * __drcp_rn(det23);
     const double l32 = w32 * i2;
-    const double d3 = fma(-l32, w32, fma(-l31, w31, fma(-l30, a30, a33)));
-    const double i3 = __drcp_rn(d3);
+    const double d3 = det23 * i2;
     // inertia check: the first NPOS pivots must be > 0, the others < 0 (quasi-definite matrix)
     {
       const double s0 = (r0 + 0 < NPOS) ? a00 : -a00, s1 = (r0 + 1 < NPOS) ? d1 : -d1;
@@ -689,22 +696,26 @@ __device__ __forceinline__ bool gj_inverse_regs(int sub, unsigned mask, const do
 // the whole (padded) matrix lives in registers as m8n8k4 accumulator tiles for all N/4 block
 // steps.  Block step kb (columns c0 = 4 kb .. c0 + 3):
 //   1. the 4-column panel leaves the tiles through shared memory and is reduced row-per-lane by
-//      an ordinary in-place Gauss-Jordan with partial pivoting over ALL not-yet-pivoted rows
-//      (so the pivot order is the one of unblocked partial pivoting on this panel); afterwards
-//      panel row i holds -A[i,panel] B^{-1} (other rows) or the rows of B^{-1} (pivot rows),
-//      B = A[pivot rows, panel].
-//   2. the 4 raw pivot rows leave the tiles (their tile rows are zeroed), with the panel
-//      columns replaced by I_4.
-//   3. one rank-4 update  C += panel' * pivot_rows  = 1 DMMA per tile.
-// Rows never move: X(step(r), piv[c]) = C(r, c) un-permutes in the final store like
-// gj_inverse_regs.  Shared memory per warp: GjDmma<N>::SMEM doubles + GjDmma<N>::SINTS ints.
+//      an ordinary in-place Gauss-Jordan with partial pivoting over ALL not-yet-pivoted rows;
+//      afterwards panel row i holds W_i = -A[i,panel] B^{-1} (other rows) or the rows of B^{-1}
+//      (the 4 pivot rows R), B = A[R, panel].
+//   2. the 4 raw pivot rows are copied out of the tiles, panel columns replaced by I_4.
+//   3. one rank-4 update  C += W * pivot_rows  = 1 DMMA per tile, with W = 0 for the pivot rows.
+// The pivot rows themselves are NOT transformed at their block step: they stay raw (panel
+// columns e_s) and keep being updated like any other row, which commutes with the pending
+// left-multiplication by B^{-1}; all N/4 block transforms are applied at the end as one
+// block-diagonal DMMA product on the rows sorted by pivot step, which is also where the row
+// permutation is undone.  The column permutation is undone by the final store:
+//   X(step(r), piv[c]) = (B_kb^{-1} C[R_kb, :])(r, c).
+// Shared memory per warp: GjDmma<N>::SMEM doubles + GjDmma<N>::SINTS ints.
 // ------------------------------------------------------------------------------------------
 template <int N> struct GjDmma {
   static_assert(N % 4 == 0 && N <= 64, "block Gauss-Jordan: N % 4 == 0, N <= 64");
   static constexpr int NTL = (N + 7) / 8, NP = NTL * 8, NB = N / 4;
   static constexpr int PLD = (NP % 16 == 8) ? NP + 4 : NP + 12;   // == 12 (mod 16): conflict-free B fragments
   static constexpr int RPL = (NP + 31) / 32;
-  static constexpr int PAN = 0, PROW = NP * 4, SMEM = PROW + 4 * PLD;
+  static constexpr int PAN = 0, PROW = NP * 4, BINV = PROW + 4 * PLD, YS = BINV + 16 * (2 * NTL);
+  static constexpr int SMEM = YS + N * PLD;     // Y: the N rows sorted by pivot step
   static constexpr int SINTS = 2 * NP;     // piv[c] | step[r]
 };
 
@@ -714,7 +725,7 @@ __device__ __forceinline__ bool gj_inverse_dmma(int lane, const double *__restri
                                                 double *sw, int *si) {
   using G = GjDmma<N>;
   constexpr int NTL = G::NTL, NP = G::NP, NB = G::NB, PLD = G::PLD, RPL = G::RPL;
-  double *pan = sw + G::PAN, *prow = sw + G::PROW;
+  double *pan = sw + G::PAN, *prow = sw + G::PROW, *sbinv = sw + G::BINV, *Y = sw + G::YS;
   int *spiv = si, *sstep = si + NP;
   const int g = lane >> 2, q = lane & 3;
   double c[NTL][NTL][2];
@@ -726,13 +737,14 @@ __device__ __forceinline__ bool gj_inverse_dmma(int lane, const double *__restri
       c[mt][nt][0] = (row < N && col < N) ? Eg[row + col * N] : 0.0;
       c[mt][nt][1] = (row < N && col + 1 < N) ? Eg[row + (col + 1) * N] : 0.0;
     }
+  // block-inverse slots past the last block (padding of the final product) are zero
+  for (int e = lane; e < 16 * (2 * NTL - NB); e += 32) sbinv[16 * NB + e] = 0.0;
   bool act[RPL];
 #pragma unroll
   for (int s = 0; s < RPL; s++) act[s] = lane + 32 * s < N;
   bool ok = true;
 #pragma unroll
   for (int kb = 0; kb < NB; kb++) {
-    constexpr int dummy = 0; (void)dummy;
     const int ntp = kb >> 1, h = kb & 1, c0 = 4 * kb;
     // 1. panel out of the tiles (and zero it there)
     if ((q >> 1) == h) {
@@ -757,17 +769,17 @@ __device__ __forceinline__ bool gj_inverse_dmma(int lane, const double *__restri
     int rsel[4];
 #pragma unroll
     for (int ss = 0; ss < 4; ss++) {
-      unsigned long long best = 0ull;
+      // pivot search on a 32-bit key: top 25 bits of |a| (exponent + 13 mantissa bits), row in
+      // the low 7 bits; candidates closer than 2^-13 relative are interchangeable as pivots
+      unsigned best = 0u;
 #pragma unroll
       for (int s = 0; s < RPL; s++) {
-        unsigned long long key = (unsigned long long)__double_as_longlong(fabs(a[s][ss]));
-        key = (key & ~0x7Full) | (unsigned long long)(127 - (lane + 32 * s));
+        const unsigned hi32 = (unsigned)__double2hiint(a[s][ss]) & 0x7fffffffu;
+        const unsigned key = (hi32 & ~0x7Fu) | (unsigned)(127 - (lane + 32 * s));
         if (act[s] && key > best) best = key;
       }
-      const unsigned hi32 = (unsigned)(best >> 32), lo32 = (unsigned)best;
-      const unsigned mhi = __reduce_max_sync(0xffffffffu, hi32);
-      const unsigned mlo = __reduce_max_sync(0xffffffffu, (best != 0ull && hi32 == mhi) ? lo32 : 0u);
-      const int r = 127 - (int)(mlo & 0x7Fu);
+      const unsigned mx = __reduce_max_sync(0xffffffffu, best);
+      const int r = 127 - (int)(mx & 0x7Fu);
       const int rl = r & 31, rs = r >> 5;
       rsel[ss] = r;
       double pr[4];
@@ -778,7 +790,7 @@ __device__ __forceinline__ bool gj_inverse_dmma(int lane, const double *__restri
         for (int s = 1; s < RPL; s++) if (rs == s) v = a[s][j];
         pr[j] = __shfl_sync(0xffffffffu, v, rl);
       }
-      if (pr[ss] == 0.0) ok = false;
+      if (mx == 0u || pr[ss] == 0.0) ok = false;
       const double pinv = __drcp_rn(pr[ss]);
 #pragma unroll
       for (int j = 0; j < 4; j++) pr[j] *= pinv;        // scaled pivot row
@@ -790,11 +802,10 @@ __device__ __forceinline__ bool gj_inverse_dmma(int lane, const double *__restri
         for (int j = 0; j < 4; j++)
           if (j != ss) a[s][j] = isp ? pr[j] : fma(-m, pr[j], a[s][j]);
         a[s][ss] = isp ? pinv : -m * pinv;
-        if (isp) { act[s] = false; sstep[r] = c0 + ss; }
+        if (isp) act[s] = false;
       }
-      if (lane == 0) spiv[c0 + ss] = r;
     }
-    // transformed panel back (A operand of the update)
+    // transformed panel back: W (A operand of the update); the pivot rows hold B^{-1}
 #pragma unroll
     for (int s = 0; s < RPL; s++) {
       const int row = lane + 32 * s;
@@ -803,21 +814,34 @@ __device__ __forceinline__ bool gj_inverse_dmma(int lane, const double *__restri
         *reinterpret_cast<double2 *>(pan + row * 4 + 2) = make_double2(a[s][2], a[s][3]);
       }
     }
-    // 2. raw pivot rows out of the tiles, zeroed there
+    if (lane < 4) {
+      const int r = lane == 0 ? rsel[0] : lane == 1 ? rsel[1] : lane == 2 ? rsel[2] : rsel[3];
+      spiv[c0 + lane] = r;
+      sstep[r] = c0 + lane;
+    }
+    // 2. raw pivot rows out of the tiles; the pivot rows' own panel entries become e_s
 #pragma unroll
     for (int mt = 0; mt < NTL; mt++) {
       const int row = g + 8 * mt;
       const int sidx = row == rsel[0] ? 0 : row == rsel[1] ? 1 : row == rsel[2] ? 2 : row == rsel[3] ? 3 : -1;
       if (sidx >= 0) {
 #pragma unroll
-        for (int nt = 0; nt < NTL; nt++) {
+        for (int nt = 0; nt < NTL; nt++)
           *reinterpret_cast<double2 *>(prow + sidx * PLD + 8 * nt + 2 * q) = make_double2(c[mt][nt][0], c[mt][nt][1]);
-          c[mt][nt][0] = 0.0; c[mt][nt][1] = 0.0;
-        }
+      }
+      if ((q >> 1) == h) {
+        if (sidx == 2 * (q & 1)) c[mt][ntp][0] = 1.0;
+        if (sidx == 2 * (q & 1) + 1) c[mt][ntp][1] = 1.0;
       }
     }
     __syncwarp();
-    if (lane < 16) prow[(lane >> 2) * PLD + c0 + (lane & 3)] = ((lane >> 2) == (lane & 3)) ? 1.0 : 0.0;
+    if (lane < 16) {
+      const int sr = lane >> 2, sc = lane & 3;
+      const int r = sr == 0 ? rsel[0] : sr == 1 ? rsel[1] : sr == 2 ? rsel[2] : rsel[3];
+      prow[sr * PLD + c0 + sc] = (sr == sc) ? 1.0 : 0.0;
+      sbinv[16 * kb + lane] = pan[r * 4 + sc];       // B^{-1}(sr, sc)
+      pan[r * 4 + sc] = 0.0;                         // W = 0 for the pivot rows
+    }
     __syncwarp();
     // 3. rank-4 update, one DMMA per tile
     double af[NTL], bf[NTL];
@@ -831,21 +855,49 @@ __device__ __forceinline__ bool gj_inverse_dmma(int lane, const double *__restri
       for (int nt = 0; nt < NTL; nt++) dmma_884(c[mt][nt][0], c[mt][nt][1], af[mt], bf[nt]);
     __syncwarp();
   }
-  if (do_store) {
-    int sg[NTL];
+  // rows sorted by pivot step -> Y, then X rows = blockdiag(B_kb^{-1}) Y
 #pragma unroll
-    for (int mt = 0; mt < NTL; mt++) sg[mt] = (g + 8 * mt < N) ? sstep[g + 8 * mt] : 0;
+  for (int mt = 0; mt < NTL; mt++) {
+    const int row = g + 8 * mt;
+    if (row < N) {
+      const int sg = sstep[row];
 #pragma unroll
-    for (int nt = 0; nt < NTL; nt++) {
-      const int col = 8 * nt + 2 * q;
-      if (col < N) {
-        const int p0 = spiv[col], p1 = spiv[col + 1];
+      for (int nt = 0; nt < NTL; nt++)
+        *reinterpret_cast<double2 *>(Y + sg * PLD + 8 * nt + 2 * q) = make_double2(c[mt][nt][0], c[mt][nt][1]);
+    }
+  }
+  __syncwarp();
+  int pc[NTL][2];
 #pragma unroll
-        for (int mt = 0; mt < NTL; mt++)
-          if (g + 8 * mt < N) {
-            Xg[sg[mt] + p0 * N] = c[mt][nt][0];
-            Xg[sg[mt] + p1 * N] = c[mt][nt][1];
-          }
+  for (int nt = 0; nt < NTL; nt++) {
+    const int col = 8 * nt + 2 * q;
+    pc[nt][0] = col < N ? spiv[col] : 0;
+    pc[nt][1] = col + 1 < N ? spiv[col + 1] : 0;
+  }
+#pragma unroll
+  for (int mt = 0; mt < NTL; mt++) {
+    double x[NTL][2];
+#pragma unroll
+    for (int nt = 0; nt < NTL; nt++) x[nt][0] = x[nt][1] = 0.0;
+#pragma unroll
+    for (int j = 0; j < 2; j++) {
+      if (2 * mt + j < NB) {
+        // A(row g, k q) = B_{2mt+j}^{-1}(g - 4j, q) on rows 4j..4j+3, zero elsewhere
+        const double av = ((g >> 2) == j) ? sbinv[16 * (2 * mt + j) + 4 * (g & 3) + q] : 0.0;
+#pragma unroll
+        for (int nt = 0; nt < NTL; nt++) {
+          const double bv = Y[(8 * mt + 4 * j + q) * PLD + g + 8 * nt];
+          dmma_884(x[nt][0], x[nt][1], av, bv);
+        }
+      }
+    }
+    const int row = g + 8 * mt;
+    if (do_store && row < N) {
+#pragma unroll
+      for (int nt = 0; nt < NTL; nt++) {
+        const int col = 8 * nt + 2 * q;
+        if (col < N) Xg[row + pc[nt][0] * N] = x[nt][0];
+        if (col + 1 < N) Xg[row + pc[nt][1] * N] = x[nt][1];
       }
     }
   }

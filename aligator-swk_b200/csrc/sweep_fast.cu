@@ -43,8 +43,9 @@ __global__ void __launch_bounds__(32 * WPB) einv_kernel(const DevParams p) {
 template <int N, int WPB>
 __global__ void __launch_bounds__(32 * WPB, 3) einv_dmma_kernel(const DevParams p) {
   using G = GjDmma<N>;
-  __shared__ __align__(16) double s_w[WPB][G::SMEM];
-  __shared__ int s_i[WPB][G::SINTS];
+  extern __shared__ __align__(16) double s_dyn[];
+  double *s_w = s_dyn + (threadIdx.x >> 5) * G::SMEM;
+  int *s_i = reinterpret_cast<int *>(s_dyn + WPB * G::SMEM) + (threadIdx.x >> 5) * G::SINTS;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long total = (long long)p.batch * p.T;
   long long w = (long long)blockIdx.x * WPB + warp;
@@ -53,7 +54,7 @@ __global__ void __launch_bounds__(32 * WPB, 3) einv_dmma_kernel(const DevParams 
   const int b = (int)(w / p.T), t = (int)(w % p.T);
   const double *Eg = p.knots + ((size_t)b * (p.T + 1) + phys_t(p, t)) * p.KL.stride + p.KL.E;
   double *Xg = p.einv + ((size_t)b * p.T + phys_t(p, t)) * (size_t)(N * N);
-  const bool ok = gj_inverse_dmma<N>(lane, Eg, Xg, valid, s_w[warp], s_i[warp]);
+  const bool ok = gj_inverse_dmma<N>(lane, Eg, Xg, valid, s_w, s_i);
   if (!ok && lane == 0 && valid) atomicOr(reinterpret_cast<int *>(p.flags) + b, GARB200_FLAG_LU_SINGULAR);
 }
 
@@ -548,7 +549,11 @@ static int launch_fast_t(const DevParams &p, cudaStream_t st) {
   if (total > 0) {
     static const bool force_regs = [] { const char *e = getenv("GARB200_EINV"); return e && e[0] == 'r'; }();
     if constexpr (NX % 4 == 0 && NX > 16) {
-      if (!force_regs) einv_dmma_kernel<NX, WPB><<<(unsigned)((total + WPB - 1) / WPB), 32 * WPB, 0, st>>>(p);
+      if (!force_regs) {
+        constexpr size_t esm = (size_t)WPB * (GjDmma<NX>::SMEM * sizeof(double) + GjDmma<NX>::SINTS * sizeof(int));
+        if (cudaFuncSetAttribute(einv_dmma_kernel<NX, WPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)esm) != cudaSuccess) return -2;
+        einv_dmma_kernel<NX, WPB><<<(unsigned)((total + WPB - 1) / WPB), 32 * WPB, esm, st>>>(p);
+      }
       else einv_kernel<NX, WPB><<<(unsigned)((total + MPB - 1) / MPB), 32 * WPB, 0, st>>>(p);
     } else {
       einv_kernel<NX, WPB><<<(unsigned)((total + MPB - 1) / MPB), 32 * WPB, 0, st>>>(p);
