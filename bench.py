@@ -118,14 +118,18 @@ def cpu_port_throughput(w, budget_s=12.0):
     from aligator_swk_b200.synth import generate_problems
     import pyoracle as po
     po.build()
-    cores = os.cpu_count() or 1
+    # all host cores this process may use — NOT OMP_NUM_THREADS, which torchrun pins to 1
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except AttributeError:
+        cores = os.cpu_count() or 1
     nx, nu, nc, nth, T, legs = w["nx"], w["nu"], w["nc"], w["nth"], w["T"], w["legs"]
     rng = np.random.default_rng(3)
 
     def run(nprob, reps):
         pp = generate_problems(nprob, T, nx, nu, nc, nth, seed=42)
         theta = rng.standard_normal(nth) if nth else None
-        secs, used = po.bench(pp, MU, MU, theta=theta, num_legs=legs, reps=reps, nthreads=0)
+        secs, used = po.bench(pp, MU, MU, theta=theta, num_legs=legs, reps=reps, nthreads=cores)
         return secs, used
 
     if legs >= 2 or w["batch"] == 1:
@@ -220,17 +224,30 @@ def gpu_arm(args, w, rank, world, local_rank):
         for name, view in zip(("d_xs", "d_us", "d_vs", "d_lbdas"), sharding.carve(send, sizes)):
             out_ptrs[name] = view.data_ptr()
 
+    # The gather of step i runs on a side stream and overlaps the backward sweep of step i+1;
+    # the next forward (which overwrites the send buffer) waits for it.
+    side = torch.cuda.Stream() if dist is not None else None
+
     def step_device():
         s.backward(MU, MU)
+        if side is not None:
+            torch.cuda.current_stream().wait_stream(side)
         s.forward_device(d_theta=theta_d, **out_ptrs)
 
     def gather():
         if dist is not None:
-            sharding.gather_to_root(dist, send, rank, world, recv)
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                sharding.gather_to_root(dist, send, rank, world, recv)
+
+    def drain():
+        if side is not None:
+            torch.cuda.current_stream().wait_stream(side)
 
     # ---- value: device-resident inputs -> device-resident outputs -----------------------
     for _ in range(W):
         step_device(); gather()
+    drain()
     barrier()
     l0 = s.kernel_launches()
     s.timing_log_start(K)
@@ -241,6 +258,7 @@ def gpu_arm(args, w, rank, world, local_rank):
     e0.record()
     for _ in range(K):
         step_device(); gather()
+    drain()                              # the last gather is inside the timed region
     e1.record()
     barrier()
     clocks = sampler.stop() if sampler else None
@@ -283,7 +301,7 @@ def gpu_arm(args, w, rank, world, local_rank):
     ach_gbs = B * (b_in + b_gain) / bwd / 1e9
     ach_tf = B * f_bwd / bwd / 1e12
     hbm_bound = (ach_gbs / hbm_peak) >= (ach_tf / fp64_peak)
-    roof = {"kernel": "backward_kernel", "bound": "hbm" if hbm_bound else "tensor",
+    roof = {"kernel": "backward pass = E^-1 pre-pass + sweep kernel (2 launches per step; generic shapes: 1)", "bound": "hbm" if hbm_bound else "tensor",
             "bound_detail": "HBM bytes" if hbm_bound else "FP64 on the tensor pipe (DMMA m8n8k4; no tcgen05 kind for f64)",
             "achieved": ach_gbs if hbm_bound else ach_tf, "peak": hbm_peak if hbm_bound else fp64_peak,
             "unit": "GB/s" if hbm_bound else "TFLOP/s",
@@ -296,6 +314,18 @@ def gpu_arm(args, w, rank, world, local_rank):
             "forward_gbs": B * (b_gain + b_out) / fwd / 1e9,
             "algorithmic_bytes_per_launch": B * (b_in + b_gain), "algorithmic_flops_per_launch": B * f_bwd,
             "kernel_share_of_step": (bwd * 1e3) / ms_step}
+    # DRAM traffic of the backward pass from the committed `ncu --set full` capture of this same
+    # workload at this same batch (profiles/rNN_ncu_digest.json, written by tools/make_profiles.py)
+    try:
+        import glob
+        digests = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_digest.json")))
+        full = (json.load(open(digests[-1])).get(args.workload) or {}).get("full") or {}
+        parts = {k: v["dram_bytes"] for k, v in full.items() if k.startswith("einv") or k.startswith("sweep")}
+        if parts and any(k.startswith("sweep") for k in parts) and B == WORKLOADS[args.workload]["batch"]:
+            roof["traffic"] = float(sum(parts.values()))
+            roof["traffic_source"] = os.path.basename(digests[-1]) + ": dram__bytes_read.sum + dram__bytes_write.sum of " + " + ".join(sorted(parts))
+    except Exception:
+        pass
     cpu_v, cores, sample = cpu_port_throughput(w, budget_s=args.cpu_budget)
     line = {
         "metric": "batched LQ solves/sec (bwd+fwd)", "value": value, "unit": "solves/s", "n_gpus": world,
@@ -307,7 +337,7 @@ def gpu_arm(args, w, rank, world, local_rank):
         "roofline": roof,
         "cpu_baseline": {"value": cpu_v, "unit": "solves/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
-        "collective": None if world == 1 else "one NCCL gather of (xs,us,vs,lbdas) to rank 0 per step",
+        "collective": None if world == 1 else "one NCCL gather of (xs,us,vs,lbdas) to rank 0 per step, on a side stream (overlaps the next backward sweep)",
     }
     print(json.dumps(line), flush=True)
     if dist is not None:

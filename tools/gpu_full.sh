@@ -15,7 +15,7 @@ if [ "$1" == "ncu" ]; then
     timeout 300 python bench.py --workload $wl --steps 2 --warmup 3 --no-e2e --cpu-budget 1 > gpurun_out/plain_$wl.log 2>&1 && \
     timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_$wl.csv \
       python bench.py --workload $wl --steps 2 --warmup 3 --no-e2e --cpu-budget 1 > gpurun_out/ncu_launch_$wl.log 2>&1; echo "launch list $wl rc=$?"
-    timeout 900 ncu --set full --clock-control none --import-source on -k regex:"sweep_kernel|einv_kernel|forward_kernel" -s 3 -c 3 -f -o gpurun_out/full_$wl \
+    timeout 900 ncu --set full --clock-control none --import-source on -k regex:"sweep_kernel|einv_|forward_kernel" -s 3 -c 3 -f -o gpurun_out/full_$wl \
       python bench.py --workload $wl --steps 1 --warmup 1 --no-e2e --cpu-budget 1 > gpurun_out/ncu_full_$wl.log 2>&1; echo "set full $wl rc=$?"
   done
 fi
