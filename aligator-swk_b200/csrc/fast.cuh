@@ -274,6 +274,20 @@ template <int NXc> struct RhsGains {
   __device__ __forceinline__ void set(int i, int j, double v) const { if (j < NXc) fb[i * NXc + j] = v; else ff[i] = v; }
 };
 
+/// The same with the theta block and padding: column j > n is column j - n - 1 of the row-major
+/// fth rows; rows >= S (padding of the blocked factorisation) read 0 and drop writes.
+template <int NXc, int H, int S> struct RhsGainsTh {
+  double *ff, *fb, *fth;
+  __device__ __forceinline__ double get(int i, int j) const {
+    if (i >= S) return 0.0;
+    return j < NXc ? fb[i * NXc + j] : (j == NXc ? ff[i] : fth[i * H + (j - NXc - 1)]);
+  }
+  __device__ __forceinline__ void set(int i, int j, double v) const {
+    if (i >= S) return;
+    if (j < NXc) fb[i * NXc + j] = v; else if (j == NXc) ff[i] = v; else fth[i * H + (j - NXc - 1)] = v;
+  }
+};
+
 /// A window of NRW columns starting at col0 of the same block; columns past n read 0 and drop writes.
 template <int NXc> struct RhsGainsPart {
   double *ff, *fb;

@@ -59,43 +59,55 @@ __global__ void __launch_bounds__(32 * WPB, 3) einv_dmma_kernel(const DevParams 
 }
 
 // ---- shared-memory plan of the sweep (doubles) ---------------------------------------------
-template <int NX, int NU, int NC> struct FastPlan {
-  static constexpr int n = NX, m = NU, c = NC, s = NU + NC;
+template <int NX, int NU, int NC, int NTH = 0> struct FastPlan {
+  static constexpr int n = NX, m = NU, c = NC, s = NU + NC, h = NTH;
+  static constexpr int NA = 1 + h;                      // augmented columns: the vector + the theta block
+  static constexpr int na = n + NA;
+  static constexpr int sp = (s + 3) & ~3;               // KKT block padded to a multiple of 4 (blocked LDL^T)
   static constexpr int r2(int x) { return (x + 1) & ~1; }
-  // packed knot record (same offsets as garb200_make_knot_layout(NX, NU, NC, 0))
+  // packed knot record (same offsets as garb200_make_knot_layout(NX, NU, NC, NTH))
   static constexpr int oQ = 0, oS = r2(oQ + n * n), oR = r2(oS + n * m), oq = r2(oR + m * m),
                        orr = r2(oq + n), oA = r2(orr + m), oB = r2(oA + n * n), oE = r2(oB + n * m),
                        of = r2(oE + n * n), oC = r2(of + n), oD = r2(oC + c * n), od = r2(oD + c * m),
-                       kstride = r2(od + c);
+                       oGth = r2(od + c), oGx = r2(oGth + h * h), oGu = r2(oGx + n * h),
+                       ogam = r2(oGu + m * h), kstride = r2(ogam + h);
   static_assert(oS == oQ + n * n && oB == oA + n * n, "[Q|S] and [A|B] must be contiguous (even n*n)");
   static constexpr int nrows = m + c + 2 * n;
-  static constexpr int gff = 0, gfb = r2(nrows), gstride = r2(gfb + nrows * n);
-  // only ff and the K / Z rows of fb are staged in shared memory (they are operands of later
-  // steps); the L and A rows go from the accumulators straight to the gains record in HBM
+  static constexpr int gff = 0, gfb = r2(nrows), gfth = r2(gfb + nrows * n), gstride = r2(gfth + nrows * h);
+  // only ff, the K / Z rows of fb (operands of later steps) and fth are staged in shared memory;
+  // the L and A rows of fb go from the accumulators straight to the gains record in HBM
   static constexpr int gpart = r2(gfb + s * n);
+  static constexpr int gthsz = r2(nrows * h);
   static_assert(n % 2 == 0, "row-major fb rows are written as 16-byte pairs");
   // smem
   static constexpr int rec = 0;
-  static constexpr int X1 = r2(rec + kstride);          // n x (n+1)
-  static constexpr int P = r2(X1 + n * (n + 1));        // n x (n+1): [P | pvec] / [Vxx | vx] / [A_pre | tv]
-  static constexpr int BtV = r2(P + n * (n + 1));       // m x (n+1)
-  static constexpr int kkt = r2(BtV + m * (n + 1));     // s x s
-  static constexpr int ksub = r2(kkt + s * s);          // max(s, 2n) + 2
-  static constexpr int KS = (s > 2 * n ? s : 2 * n) + 2;
+  static constexpr int X1 = r2(rec + kstride);          // n x na
+  static constexpr int P = r2(X1 + n * na);             // n x na: [P | pvec | Vxt] / [Vxx | vx | Lth0] / [A_pre | tv | Yth_pre]
+  static constexpr int BtV = r2(P + n * na);            // m x na
+  static constexpr int kkt = r2(BtV + m * na);          // sp x sp
+  static constexpr int ksub = r2(kkt + sp * sp);        // max(s, 2n) + 2
+  static constexpr int KS = (sp > 2 * n ? sp : 2 * n) + 2;
   static constexpr int dinv = r2(ksub + KS);            // n
   static constexpr int rhat = r2(dinv + n);             // 16 doubles of reduction scratch
   static constexpr int atvx = r2(rhat + 16);            // n + m
-  static constexpr int G = r2(atvx + n + m);            // gains staging record
-  static constexpr int ints = r2(G + gpart);            // pivots: KS ints
+  static constexpr int G = r2(atvx + n + m);            // gains staging: [ff | fb rows K,Z] then fth
+  static constexpr int Gth_s = r2(G + gpart);           // fth staging (nrows x h)
+  static constexpr int Pxt = r2(Gth_s + gthsz);         // Pxttilde = -Einv^T Vxt (n x h)
+  static constexpr int Vxn = r2(Pxt + n * h);           // Vxt^T Afb (h x n, transposed: n x h col-major)
+  static constexpr int Vtt = r2(Vxn + n * h);           // h x h | vt h | parts h*h + h
+  static constexpr int ints = r2(Vtt + 2 * (h * h + h)); // pivots: KS ints
   static constexpr int bar = r2(ints + (KS + 1) / 2);
   static constexpr int total = bar + 2;
 };
 
-template <int NX, int NU, int NC, int NW, bool PROF>
-__global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : NW == 5 ? 3 : 1)) sweep_kernel(const DevParams p) {
+template <int NX, int NU, int NC, int NTH, int NW, bool PROF>
+__global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : (NW == 5 && NC == 0 && NTH == 0) ? 3 : NW == 5 ? 2 : 1))
+sweep_kernel(const DevParams p) {
   extern __shared__ __align__(16) double sm[];
-  using PL = FastPlan<NX, NU, NC>;
-  constexpr int n = NX, m = NU, c = NC, s = NU + NC, NT = 32 * NW;
+  using PL = FastPlan<NX, NU, NC, NTH>;
+  constexpr int n = NX, m = NU, c = NC, s = NU + NC, h = NTH, NT = 32 * NW;
+  constexpr int NA = PL::NA, na = PL::na, sp = PL::sp;
+  constexpr int hh = h > 0 ? h : 1;        // divisor-safe
   constexpr int rK = 0, rZ = m, rL = m + c, rA = m + c + n;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int b = blockIdx.x;
@@ -105,11 +117,17 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : NW == 5 ? 3 : 1)) swee
   double *Q = rec + PL::oQ, *S = rec + PL::oS, *R = rec + PL::oR, *qv = rec + PL::oq, *rv = rec + PL::orr;
   double *A = rec + PL::oA, *B = rec + PL::oB, *Einv = rec + PL::oE, *f = rec + PL::of;
   double *C = rec + PL::oC, *D = rec + PL::oD, *d = rec + PL::od;
+  double *Gth = rec + PL::oGth, *Gx = rec + PL::oGx, *Gu = rec + PL::oGu, *gam = rec + PL::ogam;
+  double *fth = sm + PL::Gth_s;          // fth staging, nrows x h row-major
+  double *Pxt = sm + PL::Pxt, *Vxn = sm + PL::Vxn;
+  double *Vtt = sm + PL::Vtt, *vt = Vtt + h * h, *Vttp = vt + h, *vtp = Vttp + h * h;
   double *X1 = sm + PL::X1, *P = sm + PL::P, *BtV = sm + PL::BtV, *kkt = sm + PL::kkt;
   double *ksub = sm + PL::ksub, *dinv = sm + PL::dinv, *atvx = sm + PL::atvx, *Gs = sm + PL::G;
   double *pv = P + n * n;         // column n of the augmented P block
   double *x1v = X1 + n * n;       // column n of the augmented X1 block
   double *btvx = BtV + m * n;     // column n of BtV: B^T vx
+  double *Pth = P + n * (n + 1);  // theta columns of the P block: Vxt / Lth0 / Yth_pre
+  double *BtVth = BtV + m * (n + 1);
   double *ff = Gs + PL::gff, *fb = Gs + PL::gfb;
   int *kpiv = reinterpret_cast<int *>(sm + PL::ints);
   double *red = sm + PL::rhat;    // NW doubles: cross-warp reduction scratch
@@ -130,6 +148,7 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : NW == 5 ? 3 : 1)) swee
 
   if (tid == 0) { mbar_init(bar, 1); fence_mbar_init(); }
   for (int e = tid; e < PL::gpart; e += NT) Gs[e] = 0.0;
+  for (int e = tid; e < PL::gthsz; e += NT) fth[e] = 0.0;
   cta_sync<NT>();
   uint32_t phase = 0;
   const size_t pbase = (size_t)b * (T + 1);
@@ -151,7 +170,9 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : NW == 5 ? 3 : 1)) swee
     fence_proxy_async();
     cta_sync<NT>();
     if (tid == 0) {
-      tma_store_1d(p.gains + (pbase + phys_t(p, t)) * p.GL.stride, Gs, (uint32_t)PL::gpart * 8u);
+      double *gdst = p.gains + (pbase + phys_t(p, t)) * p.GL.stride;
+      tma_store_1d(gdst, Gs, (uint32_t)PL::gpart * 8u);
+      if constexpr (h > 0) tma_store_1d(gdst + PL::gfth, fth, (uint32_t)PL::gthsz * 8u);
       tma_store_commit();
     }
   };
@@ -161,6 +182,11 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : NW == 5 ? 3 : 1)) swee
     double *v = p.values + ((size_t)b * p.nslots + slot) * p.VL.stride;
     for (int e = tid; e < n * n; e += NT) v[p.VL.Pmat + e] = P[e];
     for (int i = tid; i < n; i += NT) v[p.VL.pvec + i] = pv[i];
+    if constexpr (h > 0) {
+      for (int e = tid; e < n * h; e += NT) v[p.VL.Vxt + e] = Pth[e];
+      for (int e = tid; e < h * h; e += NT) v[p.VL.Vtt + e] = Vtt[e];
+      for (int i = tid; i < h; i += NT) v[p.VL.vt + i] = vt[i];
+    }
     if (t == 0 && p.store_all_values) {                       // proximal-riccati.hxx:39-42
       for (int e = tid; e < n * n; e += NT) v[p.VL.Vxx + e] = P[e];
       for (int i = tid; i < n; i += NT) v[p.VL.vx + i] = pv[i];
@@ -172,10 +198,15 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : NW == 5 ? 3 : 1)) swee
   mbar_wait(bar, phase); phase ^= 1;
   for (int e = tid; e < n * n; e += NT) P[e] = Q[e];
   for (int i = tid; i < n; i += NT) pv[i] = qv[i];
+  if constexpr (h > 0) {                                  // Vxt = Gx, Vtt = Gth, vt = gamma  (:142-149, nu = 0)
+    for (int e = tid; e < n * h; e += NT) Pth[e] = Gx[e];
+    for (int e = tid; e < h * h; e += NT) Vtt[e] = Gth[e];
+    for (int i = tid; i < h; i += NT) vt[i] = gam[i];
+  }
   store_gains(T);
   {
     double *gT = p.gains + (pbase + phys_t(p, T)) * p.GL.stride;
-    for (int e = PL::gpart + tid; e < PL::gstride; e += NT) gT[e] = 0.0;
+    for (int e = PL::gpart + tid; e < PL::gfth; e += NT) gT[e] = 0.0;
   }
   store_value(T);
   fence_proxy_async();
@@ -196,11 +227,12 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : NW == 5 ? 3 : 1)) swee
     cta_sync<NT>();
     PH(0);
     // (1) [X1 | x1v] = Einv^T [P | pvec]          EinvP, -ptilde      (:175-178)
-    mma_gemm<n, n + 1, n, NW>(warp, lane,
+    //     theta columns: Pxttilde = -Einv^T Vxt -> Pxt                                   (:261-262)
+    mma_gemm<n, na, n, NW>(warp, lane,
         [&](int i, int k) { return Einv[k + i * n]; },
         [&](int k, int j) { return P[k + j * n]; },
         [](int, int) { return 0.0; },
-        [&](int i, int j, double v) { X1[i + j * n] = v; });
+        [&](int i, int j, double v) { if (j <= n) X1[i + j * n] = v; else Pxt[i + (j - n - 1) * n] = -v; });
     cta_sync<NT>();
     PH(1);
     // (2) Ptilde = X1 * Einv (lower triangle kept, mirrored); ||Ptilde||_F^2 on the fly  (:179-180)
@@ -228,6 +260,8 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : NW == 5 ? 3 : 1)) swee
     // (3) w = ptilde + Ptilde f -> pv                                                   (:182-187)
     gemv4<n, n, NT>(tid, [&](int i, int j) { return P[i + j * n]; }, [&](int j) { return f[j]; },
                     [&](int i) { return -x1v[i]; }, [&](int i, double v) { pv[i] = v; });
+    if constexpr (h > 0)
+      for (int e = tid; e < n * h; e += NT) Pth[e] = Pxt[e];     // right-hand sides of Lth0 = Lambda^{-1} Pxttilde
     if (!neumann) {
       for (int e = tid; e < n * n; e += NT) {
         const int i = e % n, j = e / n;
@@ -238,19 +272,19 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : NW == 5 ? 3 : 1)) swee
     PH(3);
     // (4) [Vxx | vx] = Lambda^{-1} [Ptilde | w]                                      (:185-190)
     if (neumann) {
-      mma_gemm<n, n + 1, n, NW>(warp, lane,
+      mma_gemm<n, na, n, NW>(warp, lane,
           [&](int i, int k) { return -mudyn * P[i + k * n]; },
           [&](int k, int j) { return P[k + j * n]; },
           [&](int i, int j) { return P[i + j * n]; },
           [&](int i, int j, double v) { X1[i + j * n] = v; });
       cta_sync<NT>();
       PH(4);
-      for (int e = tid; e < n * (n + 1); e += NT) {           // back into P, mirrored from the lower triangle
+      for (int e = tid; e < n * na; e += NT) {                // back into P, mirrored from the lower triangle
         const int i = e % n, j = e / n;
         P[e] = (j < n && i < j) ? X1[j + i * n] : X1[e];
       }
     } else {
-      if (!ldlt_solve_blocked<n, n + 1, NT>(tid, X1, RhsColMajor<n>{P}, Gs, dinv)) flags |= GARB200_FLAG_LLT_NOT_PD;
+      if (!ldlt_solve_blocked<n, na, NT>(tid, X1, RhsColMajor<n>{P}, Gs, dinv)) flags |= GARB200_FLAG_LLT_NOT_PD;
       PH(4);
       mirror_lower_ct<n, NT>(tid, P);
     }
@@ -262,13 +296,13 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : NW == 5 ? 3 : 1)) swee
       for (int i = tid; i < n; i += NT) v[p.VL.vx + i] = pv[i];
     }
     // (5) [AtV ; BtV] = [A | B]^T [Vxx | vx]: rows < n -> X1 (+ A^T vx), rows >= n -> BtV (+ B^T vx)
-    mma_gemm<n + m, n + 1, n, NW>(warp, lane,
+    mma_gemm<n + m, na, n, NW>(warp, lane,
         [&](int i, int k) { return A[k + i * n]; },           // [A | B] is one n x (n+m) col-major block
         [&](int k, int j) { return P[k + j * n]; },
         [](int, int) { return 0.0; },
         [&](int i, int j, double v) {
-          if (i < n) { if (j < n) X1[i + j * n] = v; else atvx[i] = v; }
-          else BtV[(i - n) + j * m] = v;
+          if (i < n) { if (j < n) X1[i + j * n] = v; else if (j == n) atvx[i] = v; }   // A^T Lth0 is not needed
+          else BtV[(i - n) + j * m] = v;                                             // B^T [Vxx | vx | Lth0]
         });
     cta_sync<NT>();
     PH(6);
@@ -285,16 +319,27 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : NW == 5 ? 3 : 1)) swee
           [&](int i, int k) { return BtV[i + k * m]; },
           [&](int k, int j) { return B[k + j * n]; },
           [&](int i, int j) { return R[i + j * m]; },
-          [&](int i, int j, double v) { kkt[i + j * s] = v; });
+          [&](int i, int j, double v) { kkt[i + j * sp] = v; });
       for (int i = tid; i < m; i += NT) ff[rK + i] = -(rv[i] + btvx[i]);          // -rhat
       if constexpr (c > 0) {
         constexpr int cc = c > 0 ? c : 1;
         for (int i = tid; i < c; i += NT) ff[rZ + i] = -d[i];
         for (int e = tid; e < c * s; e += NT) {
           const int i = e % cc, j = e / cc;
-          kkt[(m + i) + j * s] = (j < m) ? D[i + j * c] : ((j - m == i) ? -mueq : 0.0);
+          kkt[(m + i) + j * sp] = (j < m) ? D[i + j * c] : ((j - m == i) ? -mueq : 0.0);
         }
         for (int e = tid; e < c * n; e += NT) { const int i = e % cc, j = e / cc; fb[(rZ + i) * n + j] = -C[i + j * c]; }
+      }
+      if constexpr (sp > s) {        // padding rows of the blocked LDL^T: -I, decoupled
+        constexpr int pr = sp - s > 0 ? sp - s : 1;
+        for (int e = tid; e < (sp - s) * sp; e += NT) {
+          const int i = s + e % pr, j = e / pr;
+          kkt[i + j * sp] = (i == j) ? -1.0 : 0.0;
+        }
+      }
+      if constexpr (h > 0) {         // [-Guhat ; 0],  Guhat = Gu + B^T Lth0                  (:264-272)
+        for (int e = tid; e < m * h; e += NT) { const int i = e / hh, j = e % hh; fth[(rK + i) * h + j] = -(Gu[i + j * m] + BtVth[i + j * m]); }
+        for (int e = tid; e < c * h; e += NT) fth[rZ * h + e] = 0.0;
       }
     };
     auto build_rhs_K = [&]() {   // needs Shat complete
@@ -313,21 +358,21 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : NW == 5 ? 3 : 1)) swee
     cta_sync<NT>();
     PH(8);
     {
-      static_assert(s % 4 == 0, "specialised sweep needs (nu + nc) % 4 == 0");
       // blocked LDL^T solve (backward stable; an explicit inverse of Rhat was measurably less
       // accurate on the ill-conditioned knots of the reference distribution)
-      const bool okk = ldlt_solve_blocked<s, n + 1, NT, m>(tid, kkt, RhsGains<n>{ff, fb}, P, P + 4 * s);
+      const bool okk = ldlt_solve_blocked<sp, na, NT, m>(tid, kkt, RhsGainsTh<n, h, s>{ff, fb, fth}, P, P + 4 * sp);
       if (!okk) {                     // uniform: every thread computed the same pivots
         build_kkt();
         build_rhs_K();
         cta_sync<NT>();
         if (warp == 0) {
-          if (!bk_factor_warp(lane, s, kkt, s, kpiv, ksub)) flags |= GARB200_FLAG_BK_SINGULAR;
+          if (!bk_factor_warp(lane, s, kkt, sp, kpiv, ksub)) flags |= GARB200_FLAG_BK_SINGULAR;
         }
         cta_sync<NT>();
-        for (int col = tid; col < n + 1; col += NT) {
-          if (col == 0) bk_solve_column(s, kkt, s, kpiv, ksub, ff, 1);
-          else bk_solve_column(s, kkt, s, kpiv, ksub, fb + (col - 1), n);
+        for (int col = tid; col < na; col += NT) {
+          if (col == 0) bk_solve_column(s, kkt, sp, kpiv, ksub, ff, 1);
+          else if (col <= n) bk_solve_column(s, kkt, sp, kpiv, ksub, fb + (col - 1), n);
+          else bk_solve_column(s, kkt, sp, kpiv, ksub, fth + (col - n - 1), h);
         }
         cta_sync<NT>();
       }
@@ -340,6 +385,20 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : NW == 5 ? 3 : 1)) swee
       for (int k = 0; k < m; k++) { l = fma(BtV[k + i * m], ff[rK + k], l); tb = fma(B[i + k * n], ff[rK + k], tb); }
       ff[rL + i] = l;
       pv[i] = tb - mudyn * l;
+    }
+    if constexpr (h > 0) {          // Lth = Lth0 + BtV^T Kth ; Yth_pre = B Kth - mudyn Lth        (:274-280)
+      for (int e = tid; e < n * h; e += NT) {
+        const int i = e % n, j = e / n;
+        double l = Pth[i + j * n], tb = 0.0;
+#pragma unroll
+        for (int k = 0; k < m; k++) {
+          const double kth = fth[(rK + k) * h + j];
+          l = fma(BtV[k + i * m], kth, l);
+          tb = fma(B[i + k * n], kth, tb);
+        }
+        fth[(rL + i) * h + j] = l;
+        Pth[i + j * n] = tb - mudyn * l;
+      }
     }
     // (9) L = AtV^T + BtV^T K  (Vxx A == AtV^T: Vxx is exactly symmetric) -> fb rows rL     (:238-239)
     //     A_pre = A + B K - mudyn L -> P block                                            (:241-242)
@@ -433,11 +492,24 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : NW == 5 ? 3 : 1)) swee
     cta_sync<NT>();
     PH(10);
     // (10) [Afb | yff] = -Einv [A_pre | tv]                                              (:243-245)
-    mma_gemm<n, n + 1, n, NW>(warp, lane,
-        [&](int i, int k) { return -Einv[i + k * n]; },
+    //      rows n..n+h-1 of the same product: Pxttilde^T [A_pre | tv | Yth_pre] = Vxt^T [Afb | yff | Yth]
+    //      (Vxt^T Einv^{-1}... = Pxttilde^T exactly), the three Vxt-contractions of :286-298
+    mma_gemm<n + h, na, n, NW>(warp, lane,
+        [&](int i, int k) { return i < n ? -Einv[i + k * n] : Pxt[k + (i - n) * n]; },
         [&](int k, int j) { return P[k + j * n]; },
         [](int, int) { return 0.0; },
-        [&](int i, int j, double v) { if (j < n) gfbg[(rA + i) * n + j] = v; else ff[rA + i] = v; });
+        [&](int i, int j, double v) {
+          if (i < n) {
+            if (j < n) gfbg[(rA + i) * n + j] = v;
+            else if (j == n) ff[rA + i] = v;
+            else fth[(rA + i) * h + (j - n - 1)] = v;
+          } else {
+            const int a = i - n;
+            if (j < n) Vxn[j + a * n] = v;
+            else if (j == n) vtp[a] = v;
+            else Vttp[a + (j - n - 1) * h] = v;
+          }
+        });
     cta_sync<NT>();
     PH(11);
     // (11) [Pmat | pvec] = [Qhat | qhat] + Shat [K | kff] + C^T [Z | zff]                  (:249-250)
@@ -446,6 +518,32 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : NW == 5 ? 3 : 1)) swee
         [&](int k, int j) { return j < n ? fb[k * n + j] : ff[k]; },
         [&](int i, int j) { return j < n ? Q[i + j * n] : qv[i]; },
         [&](int i, int j, double v) { P[i + j * n] = v; });
+    if constexpr (h > 0) {
+      // Vxt = Gx + K^T Gu + Afb^T Vxt+ ; vt += gamma + Gu^T kff + Vxt+^T yff ;
+      // Vtt += Gth + Gu^T Kth + Vxt+^T Yth                                                (:286-298)
+      for (int e = tid; e < n * h; e += NT) {
+        const int i = e % n, j = e / n;
+        double v = Gx[e] + Vxn[e];
+#pragma unroll
+        for (int k = 0; k < m; k++) v = fma(fb[(rK + k) * n + i], Gu[k + j * m], v);
+        Pth[e] = v;
+      }
+      for (int e = tid; e < h * h + h; e += NT) {
+        if (e < h * h) {
+          const int a = e % hh, bcol = e / hh;
+          double v = Vtt[e] + Gth[e] + Vttp[e];
+#pragma unroll
+          for (int k = 0; k < m; k++) v = fma(Gu[k + a * m], fth[(rK + k) * h + bcol], v);
+          Vtt[e] = v;
+        } else {
+          const int a = e - h * h;
+          double v = vt[a] + gam[a] + vtp[a];
+#pragma unroll
+          for (int k = 0; k < m; k++) v = fma(Gu[k + a * m], ff[rK + k], v);
+          vt[a] = v;
+        }
+      }
+    }
     PH(12);
     store_gains(t);
     store_value(t);
@@ -462,6 +560,8 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : NW == 5 ? 3 : 1)) swee
     const int c0 = p.nc0, s0 = n + c0;
     const double *G0 = p.G0 + (size_t)b * c0 * n, *g0 = p.g0 + (size_t)b * c0;
     double *off = p.kkt0_ff + (size_t)b * s0;
+    double *ofth = h > 0 ? p.kkt0_fth + (size_t)b * s0 * h : nullptr;
+    double *x1th = X1 + n * (n + 1);      // theta columns next to x1v: one n x NA col-major right-hand-side block
     // G0 == I exactly (the initial-state constraint x0 = xhat of every MPC / DDP problem,
     // tests/gar/test_util.cpp:62-64)?  Then the second block row gives x0 = -g0 + mudyn lbd0 and
     // the first one collapses to (I + mudyn P0) lbd0 = P0 g0 - p0: an n x n SPD-type system of
@@ -481,6 +581,8 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : NW == 5 ? 3 : 1)) swee
       if (lane == 0) red[warp] = fro;
       gemv4<n, n, NT>(tid, [&](int i, int j) { return P[i + j * n]; }, [&](int j) { return g0[j]; },
                       [&](int i) { return -pv[i]; }, [&](int i, double v) { x1v[i] = v; });
+      if constexpr (h > 0)
+        for (int e = tid; e < n * h; e += NT) x1th[e] = -Pth[e];      // (I + mudyn P0) lbd0_th = -Vxt0
       cta_sync<NT>();
       fro = 0.0;
 #pragma unroll
@@ -490,16 +592,46 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : NW == 5 ? 3 : 1)) swee
         gemv4<n, n, NT>(tid, [&](int i, int j) { return -mudyn * P[i + j * n]; }, [&](int j) { return x1v[j]; },
                         [&](int i) { return x1v[i]; }, [&](int i, double v) { dinv[i] = v; });
         lam = dinv;
+        if constexpr (h > 0) {
+#pragma unroll 1
+          for (int j = 0; j < h; j++)
+            gemv4<n, n, NT>(tid, [&](int i, int k) { return -mudyn * P[i + k * n]; }, [&](int k) { return x1th[k + j * n]; },
+                            [&](int i) { return x1th[i + j * n]; }, [&](int i, double v) { Pxt[i + j * n] = v; });
+          cta_sync<NT>();
+          for (int e = tid; e < n * h; e += NT) x1th[e] = Pxt[e];
+        }
       } else {
         for (int e = tid; e < n * n; e += NT) {
           const int i = e % n, j = e / n;
           if (i >= j) X1[e] = (i == j ? 1.0 : 0.0) + mudyn * P[e];
         }
         cta_sync<NT>();
-        if (!ldlt_solve_blocked<n, 1, NT>(tid, X1, RhsColMajor<n>{x1v}, Gs, dinv)) flags |= GARB200_FLAG_LLT_NOT_PD;
+        if (!ldlt_solve_blocked<n, NA, NT>(tid, X1, RhsColMajor<n>{x1v}, Gs, dinv)) flags |= GARB200_FLAG_LLT_NOT_PD;
       }
       cta_sync<NT>();
       for (int i = tid; i < n; i += NT) { off[i] = fma(mudyn, lam[i], -g0[i]); off[n + i] = lam[i]; }
+      if constexpr (h > 0) {
+        // x0_th = mudyn lbd0_th ; thGrad = vt + Vxt^T x0 ; thHess = Vtt + Vxt^T x0_th         (:59-61)
+        for (int e = tid; e < n * h; e += NT) {
+          const int i = e / hh, j = e % hh;
+          const double l = x1th[i + j * n];
+          ofth[i * h + j] = mudyn * l;
+          ofth[(n + i) * h + j] = l;
+        }
+        for (int e = tid; e < h * h + h; e += NT) {
+          if (e < h * h) {
+            const int a = e % hh, bb = e / hh;
+            double acc = Vtt[e];
+            for (int i = 0; i < n; i++) acc = fma(Pth[i + a * n], mudyn * x1th[i + bb * n], acc);
+            p.thHess[(size_t)b * h * h + e] = acc;
+          } else {
+            const int a = e - h * h;
+            double acc = vt[a];
+            for (int i = 0; i < n; i++) acc = fma(Pth[i + a * n], fma(mudyn, lam[i], -g0[i]), acc);
+            p.thGrad[(size_t)b * h + a] = acc;
+          }
+        }
+      }
     } else {
       const int ld0 = s0 | 1;                        // odd leading dimension: conflict-free rows and columns
       double *K0 = sm;                               // overlays rec | X1 (size checked on the host)
@@ -518,6 +650,35 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : NW == 5 ? 3 : 1)) swee
       if (warp == 0) bk_solve_vec_warp<(2 * n + 31) / 32>(lane, s0, K0, ld0, kpiv, ksub, ff0, reinterpret_cast<int *>(wk0));
       cta_sync<NT>();
       for (int i = tid; i < s0; i += NT) off[i] = ff0[i];
+      if constexpr (h > 0) {
+        // theta columns one after the other through the same warp solve; X1 (free here? no: K0
+        // overlays it) -> the columns live in Pxt|Vxn (2 n h >= s0 h doubles)
+        double *fth0 = Pxt;
+        static_assert(PL::Vxn == PL::Pxt + n * h, "Pxt and Vxn must be adjacent");
+#pragma unroll 1
+        for (int j = 0; j < h; j++) {
+          cta_sync<NT>();
+          for (int i = tid; i < s0; i += NT) ff0[i] = (i < n) ? -Pth[i + j * n] : 0.0;
+          cta_sync<NT>();
+          if (warp == 0) bk_solve_vec_warp<(2 * n + 31) / 32>(lane, s0, K0, ld0, kpiv, ksub, ff0, reinterpret_cast<int *>(wk0));
+          cta_sync<NT>();
+          for (int i = tid; i < s0; i += NT) { ofth[i * h + j] = ff0[i]; if (i < n) fth0[i + j * n] = ff0[i]; }
+        }
+        cta_sync<NT>();
+        for (int e = tid; e < h * h + h; e += NT) {
+          if (e < h * h) {
+            const int a = e % hh, bb = e / hh;
+            double acc = Vtt[e];
+            for (int i = 0; i < n; i++) acc = fma(Pth[i + a * n], fth0[i + bb * n], acc);
+            p.thHess[(size_t)b * h * h + e] = acc;
+          } else {
+            const int a = e - h * h;
+            double acc = vt[a];
+            for (int i = 0; i < n; i++) acc = fma(Pth[i + a * n], off[i], acc);
+            p.thGrad[(size_t)b * h + a] = acc;
+          }
+        }
+      }
     }
   }
   for (int e = tid; e < n * n; e += NT)
@@ -533,9 +694,9 @@ __global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : NW == 5 ? 3 : 1)) swee
 }
 
 // ---- host side -----------------------------------------------------------------------------
-template <int NX, int NU, int NC, int NW>
+template <int NX, int NU, int NC, int NTH, int NW>
 static int launch_fast_t(const DevParams &p, cudaStream_t st) {
-  using PL = FastPlan<NX, NU, NC>;
+  using PL = FastPlan<NX, NU, NC, NTH>;
   static_assert(PL::kstride >= 0, "");
   if (p.KL.stride != PL::kstride || p.GL.stride != PL::gstride || p.KL.E != PL::oE || p.KL.f != PL::of)
     return -3;   // layout mismatch: never expected, fall back to the generic kernel
@@ -562,7 +723,7 @@ static int launch_fast_t(const DevParams &p, cudaStream_t st) {
     launched++;
   }
   const size_t smem = (size_t)PL::total * sizeof(double);
-  auto ks = p.phase_cycles ? sweep_kernel<NX, NU, NC, NW, true> : sweep_kernel<NX, NU, NC, NW, false>;
+  auto ks = p.phase_cycles ? sweep_kernel<NX, NU, NC, NTH, NW, true> : sweep_kernel<NX, NU, NC, NTH, NW, false>;
   if (cudaFuncSetAttribute(ks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -2;
   ks<<<p.batch, 32 * NW, smem, st>>>(p);
   if (cudaGetLastError() != cudaSuccess) return -2;
@@ -572,22 +733,23 @@ static int launch_fast_t(const DevParams &p, cudaStream_t st) {
 /// Returns the number of kernels launched, -3 if no specialisation matches (caller falls back
 /// to the generic kernel), < 0 otherwise on error.
 int launch_backward_fast(const DevParams &p, const int *h_nu_t, const int *h_nc_t, cudaStream_t st) {
-  if (p.num_legs >= 2 || p.nth != 0 || p.einv == nullptr || p.T < 1) return -3;
+  if (p.num_legs >= 2 || p.einv == nullptr || p.T < 1) return -3;
   if (h_nu_t[p.T] != 0 || h_nc_t[p.T] != 0) return -3;
   for (int t = 0; t < p.T; t++)
     if (h_nu_t[t] != p.nu || h_nc_t[t] != p.nc) return -3;
-  if (p.nx == 12 && p.nu == 4 && p.nc == 0) return launch_fast_t<12, 4, 0, 1>(p, st);
-  if (p.nx == 36 && p.nu == 12 && p.nc == 0) {
+  if (p.nx == 12 && p.nu == 4 && p.nc == 0 && p.nth == 0) return launch_fast_t<12, 4, 0, 0, 1>(p, st);
+  if (p.nx == 36 && p.nu == 12 && p.nc == 0 && p.nth == 0) {
     static const int nw = getenv("GARB200_NW36") ? atoi(getenv("GARB200_NW36")) : 5;   // tuning knob
-    return nw == 8 ? launch_fast_t<36, 12, 0, 8>(p, st) : nw == 5 ? launch_fast_t<36, 12, 0, 5>(p, st)
-                                                         : launch_fast_t<36, 12, 0, 4>(p, st);
+    return nw == 4 ? launch_fast_t<36, 12, 0, 0, 4>(p, st) : launch_fast_t<36, 12, 0, 0, 5>(p, st);
   }
+  if (p.nx == 36 && p.nu == 12 && p.nc == 6 && p.nth == 4) return launch_fast_t<36, 12, 6, 4, 5>(p, st);   // C3
   return -3;
 }
 
 bool fast_path_available(int nx, int nu, int nc, int nth, int num_legs) {
-  if (num_legs >= 2 || nth != 0) return false;
-  return (nx == 12 && nu == 4 && nc == 0) || (nx == 36 && nu == 12 && nc == 0);
+  if (num_legs >= 2) return false;
+  return (nx == 12 && nu == 4 && nc == 0 && nth == 0) || (nx == 36 && nu == 12 && nc == 0 && nth == 0) ||
+         (nx == 36 && nu == 12 && nc == 6 && nth == 4);
 }
 
 } // namespace garb200

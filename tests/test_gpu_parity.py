@@ -65,7 +65,11 @@ CASES = [
     (12, 4, 0, 0, 30, 4, 1e-3, "explicit_psd"),  # mudyn |Ptilde| large: LDL^T path of the specialised sweep
     (36, 12, 0, 0, 20, 2, 1e-2, "explicit_psd"),
     (12, 4, 0, 0, 30, 3, 1e-7, "explicit_psd"),
+    (36, 12, 6, 4, 12, 2, 1e-3, "explicit_psd"),  # C3 shape, LDL^T (non-Neumann) path with theta columns
+    (36, 12, 6, 4, 40, 2, 1e-8, "explicit"),
 ]
+
+FAST_DIMS = ((12, 4, 0, 0), (36, 12, 0, 0), (36, 12, 6, 4))
 
 
 @pytest.mark.parametrize("case", CASES, ids=lambda c: "nx%d_nu%d_nc%d_nth%d_T%d_B%d_%g_%s" % c)
@@ -74,7 +78,7 @@ def test_prox_parity(capi, oracle, case):
     _prox_parity(capi, oracle, case, capi.STORE_ALL_VALUES)
 
 
-FAST_SHAPES = [c for c in CASES if (c[0], c[1], c[2], c[3]) in ((12, 4, 0, 0), (36, 12, 0, 0))]
+FAST_SHAPES = [c for c in CASES if (c[0], c[1], c[2], c[3]) in FAST_DIMS]
 
 
 @pytest.mark.parametrize("case", FAST_SHAPES, ids=lambda c: "nx%d_nu%d_nc%d_nth%d_T%d_B%d_%g_%s" % c)
@@ -90,7 +94,7 @@ def _prox_parity(capi, oracle, case, flags):
     s = capi.Solver.for_problems(pp, flags=flags)
     s.upload(pp)
     s.backward(mu, mu)
-    fast_expected = (nx, nu, nc, nth) in ((12, 4, 0, 0), (36, 12, 0, 0)) and not (flags & capi.FORCE_GENERIC) and T >= 1
+    fast_expected = (nx, nu, nc, nth) in FAST_DIMS and not (flags & capi.FORCE_GENERIC) and T >= 1
     assert s.used_fast_path() == fast_expected
     xs, us, vs, lb = s.forward(theta)
     assert (s.get_flags() == 0).all()
@@ -369,4 +373,24 @@ def test_fast_path_general_initial_constraint(capi, oracle, shape):
     for b in range(3):
         ref = oracle.prox_solve(pp, mu, mu, b=b)
         assert relerr(s.get_initial(b)[0], ref["kkt0_ff"]) < 1e-9
+    s.close()
+
+
+def test_fast_path_general_initial_constraint_with_theta(capi, oracle):
+    """Same for the parametric C3 shape: dense G0 -> CTA Bunch-Kaufman with the theta columns,
+    kkt0.fth / thGrad / thHess against the oracle (proximal-riccati.hxx:53-61)."""
+    nx, nu, nc, nth, T, mu = 36, 12, 6, 4, 6, 1e-9
+    pp = generate_problems(2, T, nx, nu, nc, nth, seed=11, dist="explicit")
+    rng = np.random.default_rng(4)
+    pp.G0[1] = (np.eye(nx) + 0.3 * rng.standard_normal((nx, nx))).reshape(-1, order="F")
+    theta = rng.standard_normal((2, nth))
+    s, xs, us, vs, lb = solve_gpu(capi, pp, mu, theta=theta)
+    assert s.used_fast_path() and (s.get_flags() == 0).all()
+    for b in range(2):
+        ref = oracle.prox_solve(pp, mu, mu, theta=theta[b], b=b)
+        for got, key in ((xs[b], "xs"), (us[b], "us"), (vs[b], "vs"), (lb[b], "lbdas")):
+            assert relerr(got, ref[key]) < 1e-9, (b, key)
+        ff0, fth0, thg, thh = s.get_initial(b)
+        assert relerr(ff0, ref["kkt0_ff"]) < 1e-9 and relerr(fth0, ref["kkt0_fth"]) < 1e-9
+        assert relerr(thg, ref["thGrad"]) < 1e-9 and relerr(thh, ref["thHess"]) < 1e-9
     s.close()
