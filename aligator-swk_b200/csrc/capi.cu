@@ -125,6 +125,9 @@ int garb200_create(const garb200_config *cfg, garb200_solver **out) {
   p.T = T; p.nc0 = c.nc0; p.batch = c.batch; p.num_legs = legs ? c.num_legs : 0;
   p.shift = 0;
   p.store_all_values = (c.flags & GARB200_STORE_ALL_VALUES) ? 1 : 0;
+  p.uniform_knots = (s->nu_t[T] == 0 && s->nc_t[T] == 0) ? 1 : 0;
+  for (int t = 0; t < T; t++)
+    if (s->nu_t[t] != c.nu || s->nc_t[t] != c.nc) p.uniform_knots = 0;
   p.nslots = p.store_all_values ? T + 1 : (legs ? c.num_legs : 1);
   const int nth_eff = legs ? c.nx : c.nth;
   p.KL = garb200_make_knot_layout(c.nx, c.nu, c.nc, c.nth);

@@ -599,7 +599,12 @@ __device__ __forceinline__ bool kkt_solve_inverse(int warp, int lane, const doub
 // Returns false on an exactly zero pivot.
 // ------------------------------------------------------------------------------------------
 template <int N> struct GjShape {
-  static constexpr int LPM = N <= 16 ? 16 : 32;
+#ifndef GARB200_GJ_LPM_SMALL
+#define GARB200_GJ_LPM_SMALL 8
+#endif
+  // lanes per matrix: 8 for N <= 16 (four matrices per warp share the per-step pivot search and
+  // bookkeeping instructions; rows l and l + 8 per lane), a whole warp otherwise
+  static constexpr int LPM = N <= 16 ? GARB200_GJ_LPM_SMALL : 32;
   static constexpr int MPW = 32 / LPM;
   static constexpr int RPL = (N + LPM - 1) / LPM;
   static_assert(N <= 64, "register Gauss-Jordan: N <= 64");

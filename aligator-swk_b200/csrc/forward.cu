@@ -120,6 +120,88 @@ __global__ void __launch_bounds__(NT) forward_kernel(const DevParams p, const do
   }
 }
 
+// ---- small-record rollout: one WARP per problem, one lane per gain row -------------------
+// For records with nu + 2 nx <= 32 rows (the nx = 12 shape), nc = nth = 0, uniform knots: every
+// lane owns one row of [K; L; A] and keeps x in registers, so a knot is 6 vector loads + NX FMAs
+// per lane, one shared-memory broadcast of the new state and ONE store per lane — about 40
+// warp instructions per knot instead of ~500 for the runtime-dimension kernel above.  WPB
+// warps per CTA, each with its own NSTAGE-deep TMA ring and mbarriers; no CTA barrier at all.
+template <int NX, int NU, int WPB, int NSTAGE>
+__global__ void __launch_bounds__(32 * WPB) forward_small_kernel(const DevParams p, double *xs, double *us,
+                                                                   double *lbdas) {
+  constexpr int n = NX, m = NU, nrows = NU + 2 * NX;
+  static_assert(nrows <= 32 && NX % 2 == 0, "one lane per gain row");
+  constexpr int gff = 0, gfb = (nrows + 1) & ~1, gstride = (gfb + nrows * n + 1) & ~1;
+  extern __shared__ __align__(16) double sm[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.x * WPB + warp;
+  if (b >= p.batch) return;
+  const int T = p.T, c0 = p.nc0;
+  double *ring = sm + (size_t)warp * (NSTAGE * gstride + n + NSTAGE);
+  double *xsh = ring + NSTAGE * gstride;
+  uint64_t *bars = reinterpret_cast<uint64_t *>(xsh + n);
+  const size_t gbase = (size_t)b * (T + 1);
+  if (lane == 0) {
+    for (int s = 0; s < NSTAGE; s++) mbar_init(bars + s, 1);
+    fence_mbar_init();
+  }
+  __syncwarp();
+  if (lane == 0)
+    for (int s = 0; s < NSTAGE && s < T; s++) {
+      mbar_expect_tx(bars + s, gstride * 8u);
+      tma_load_1d(ring + s * gstride, p.gains + (gbase + phys_t(p, s)) * gstride, gstride * 8u, bars + s);
+    }
+  // computeInitial (riccati-kernel.hxx:153-164): x0 = kkt0.ff[0:n], lbd0 = kkt0.ff[n:n+c0]
+  const double *ff0 = p.kkt0_ff + (size_t)b * (n + c0);
+  const size_t xoff = (size_t)b * (T + 1) * n, uoff = (size_t)b * (T + 1) * m, loff = (size_t)b * (c0 + (size_t)T * n);
+  double x[n];
+#pragma unroll
+  for (int j = 0; j < n; j++) x[j] = ff0[j];
+  if (lane < n) xs[xoff + lane] = ff0[lane];
+  for (int i = lane; i < c0; i += 32) lbdas[loff + i] = ff0[n + i];
+  // where this lane's row goes: u (rows < m), lbd_{t+1} (next n rows), x_{t+1} (last n rows)
+  double *dst = nullptr; size_t dstride = 0;
+  if (lane < m) { dst = us + uoff + lane; dstride = m; }
+  else if (lane < m + n) { dst = lbdas + loff + c0 + (lane - m); dstride = n; }
+  else { dst = xs + xoff + n + (lane - m - n); dstride = n; }
+  const bool active = lane < nrows;
+  const int row = active ? lane : nrows - 1;
+#pragma unroll 1
+  for (int t = 0; t < T; t++) {
+    const int s = t % NSTAGE;
+    mbar_wait(bars + s, (uint32_t)((t / NSTAGE) & 1));
+    const double *rec = ring + s * gstride;
+    const double2 *rw = reinterpret_cast<const double2 *>(rec + gfb + row * n);
+    double acc = rec[gff + row];
+#pragma unroll
+    for (int j = 0; j < n / 2; j++) { const double2 v = rw[j]; acc = fma(v.x, x[2 * j], acc); acc = fma(v.y, x[2 * j + 1], acc); }
+    if (active) dst[(size_t)t * dstride] = acc;
+    if (lane >= m + n && active) xsh[lane - m - n] = acc;
+    __syncwarp();                       // xsh complete; every lane is done with ring slot s
+    if (lane == 0 && t + NSTAGE < T) {
+      fence_proxy_async();
+      mbar_expect_tx(bars + s, gstride * 8u);
+      tma_load_1d(ring + s * gstride, p.gains + (gbase + phys_t(p, t + NSTAGE)) * gstride, gstride * 8u, bars + s);
+    }
+#pragma unroll
+    for (int j = 0; j < n / 2; j++) { const double2 v = reinterpret_cast<const double2 *>(xsh)[j]; x[2 * j] = v.x; x[2 * j + 1] = v.y; }
+    __syncwarp();
+  }
+  if (lane < m) us[uoff + (size_t)T * m + lane] = 0.0;     // terminal knot has no control: defined padding
+}
+
+template <int NX, int NU>
+static int launch_forward_small(const DevParams &p, double *xs, double *us, double *lbdas, cudaStream_t st) {
+  constexpr int WPB = 4, NSTAGE = 4;
+  constexpr int nrows = NU + 2 * NX, gfb = (nrows + 1) & ~1, gstride = (gfb + nrows * NX + 1) & ~1;
+  if (p.GL.stride != gstride || p.GL.fb != gfb) return -3;
+  const size_t smem = (size_t)WPB * (NSTAGE * gstride + NX + NSTAGE) * sizeof(double);
+  auto kern = forward_small_kernel<NX, NU, WPB, NSTAGE>;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -2;
+  kern<<<(p.batch + WPB - 1) / WPB, 32 * WPB, smem, st>>>(p, xs, us, lbdas);
+  return cudaGetLastError() == cudaSuccess ? 1 : -2;
+}
+
 static size_t forward_smem(const DevParams &p, int nstage) {
   size_t d = (size_t)nstage * p.GL.stride + ((p.nx + 1) & ~1) + ((p.GL.nth + 2) & ~1) +
              ((p.GL.nrows + 1) & ~1) + nstage + 2;
@@ -141,6 +223,10 @@ static int launch_forward_t(const DevParams &p, const double *d_theta, double *x
 
 int launch_forward(const DevParams &p, const double *d_theta, double *xs, double *us, double *vs,
                    double *lbdas, cudaStream_t st) {
+  if (p.uniform_knots && p.num_legs < 2 && p.nc == 0 && p.GL.nth == 0 && p.nx == 12 && p.nu == 4) {
+    const int rc = launch_forward_small<12, 4>(p, xs, us, lbdas, st);
+    if (rc != -3) return rc;
+  }
   if (p.GL.stride * 8 <= 4096) return launch_forward_t<32, 4>(p, d_theta, xs, us, vs, lbdas, st);
   if (forward_smem(p, 3) <= 100u * 1024u) return launch_forward_t<128, 3>(p, d_theta, xs, us, vs, lbdas, st);
   return launch_forward_t<128, 2>(p, d_theta, xs, us, vs, lbdas, st);

@@ -19,6 +19,7 @@ struct DevParams {
   int T, nc0, batch, num_legs;
   int shift;            // ring offset of the time axis (cycleAppend)
   int store_all_values;
+  int uniform_knots;    // 1: every knot t < T has (nu, nc), the terminal knot has nu = nc = 0
   int nslots;           // value slots per problem (T+1 when storing all, else #legs or 1)
   const int *nu_t, *nc_t;         // [T+1] logical-time dims
   double *knots;                  // [batch][T+1][KL.stride]   (physical time order)

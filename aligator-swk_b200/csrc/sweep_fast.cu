@@ -27,7 +27,7 @@ __global__ void __launch_bounds__(32 * WPB) einv_kernel(const DevParams p) {
   __shared__ int s_piv[WPB * MPW][NP];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int mi = lane / LPM, sub = lane % LPM;
-  const unsigned mask = (LPM == 32) ? 0xffffffffu : (0xffffu << (16 * mi));
+  const unsigned mask = (LPM == 32) ? 0xffffffffu : (((1u << LPM) - 1u) << (LPM * mi));
   const long long total = (long long)p.batch * p.T;
   long long w = ((long long)blockIdx.x * WPB + warp) * MPW + mi;
   const bool valid = w < total;
@@ -101,7 +101,7 @@ template <int NX, int NU, int NC, int NTH = 0> struct FastPlan {
 };
 
 template <int NX, int NU, int NC, int NTH, int NW, bool PROF>
-__global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : (NW == 5 && NC == 0 && NTH == 0) ? 3 : NW == 5 ? 2 : 1))
+__global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : (NW == 5 && NC == 0 && NTH == 0) ? 3 : NW == 5 ? 2 : NW == 1 ? 24 : 1))
 sweep_kernel(const DevParams p) {
   extern __shared__ __align__(16) double sm[];
   using PL = FastPlan<NX, NU, NC, NTH>;
