@@ -137,6 +137,54 @@ __device__ __forceinline__ void mma_gemm(int warp, int lane, FA a, FB b, FC cin,
   }
 }
 
+// Symmetric product: only the 8x8 tiles on or below the diagonal of the N x N result are
+// computed (TM (TM + 1) / 2 instead of TM^2 tiles), dealt round-robin to the warps.  `store` still
+// sees every element of a diagonal tile and filters i >= j itself.  (Skipping the upper tiles of
+// Qhat and Pmat the same way was measured and lost: their mirrored stores cost more than the
+// DMMAs saved.)
+template <int N, int K, int NW, class FA, class FB, class FC, class FS>
+__device__ __forceinline__ void mma_gemm_lower(int warp, int lane, FA a, FB b, FC cin, FS store) {
+  constexpr int TM = (N + 7) / 8, NTILE = TM * (TM + 1) / 2;
+  constexpr int NSLOT = (NTILE + NW - 1) / NW, KS = (K + 3) / 4;
+  static_assert(K % 4 == 0 && TM <= 8, "mma_gemm_lower: K % 4 == 0, N <= 64");
+  const int g = lane >> 2, q = lane & 3;
+  double acc[NSLOT][2];
+  int ia[NSLOT], jb[NSLOT], ti_[NSLOT], tj_[NSLOT];
+#pragma unroll
+  for (int u = 0; u < NSLOT; u++) {
+    const int t = min(warp + NW * u, NTILE - 1);
+    int ti = 0;
+#pragma unroll
+    for (int r = 1; r < TM; r++) if (t >= r * (r + 1) / 2) ti = r;      // row of the packed lower triangle
+    const int tj = t - ti * (ti + 1) / 2;
+    ti_[u] = ti; tj_[u] = tj;
+    ia[u] = min(ti * 8 + g, N - 1);
+    jb[u] = min(tj * 8 + g, N - 1);
+    const int jc = tj * 8 + 2 * q;
+    acc[u][0] = cin(ia[u], min(jc, N - 1));
+    acc[u][1] = cin(ia[u], min(jc + 1, N - 1));
+  }
+#pragma unroll
+  for (int ks = 0; ks < KS; ks++) {
+    const int k = ks * 4 + q;
+    double av[NSLOT], bv[NSLOT];
+#pragma unroll
+    for (int u = 0; u < NSLOT; u++) { av[u] = a(ia[u], k); bv[u] = b(k, jb[u]); }
+#pragma unroll
+    for (int u = 0; u < NSLOT; u++) dmma_884(acc[u][0], acc[u][1], av[u], bv[u]);
+  }
+#pragma unroll
+  for (int u = 0; u < NSLOT; u++) {
+    if (warp + NW * u < NTILE) {
+      const int ic = ti_[u] * 8 + g, jc = tj_[u] * 8 + 2 * q;
+      if (ic < N) {
+        if (jc < N) store(ic, jc, acc[u][0]);
+        if (jc + 1 < N) store(ic, jc + 1, acc[u][1]);
+      }
+    }
+  }
+}
+
 // y(i) = yin(i) + alpha * sum_j A(i,j) x(j): 4 threads per row + 2 shuffles; A col-major.
 // Threads beyond 4*M idle.  NT must be a multiple of 32.  fin / fout are functors.
 template <int M, int K, int NT, class FA, class FX, class FI, class FO>

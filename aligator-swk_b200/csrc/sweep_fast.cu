@@ -237,7 +237,7 @@ sweep_kernel(const DevParams p) {
     PH(1);
     // (2) Ptilde = X1 * Einv (lower triangle kept, mirrored); ||Ptilde||_F^2 on the fly  (:179-180)
     double fro = 0.0;
-    mma_gemm<n, n, n, NW>(warp, lane,
+    mma_gemm_lower<n, n, NW>(warp, lane,
         [&](int i, int k) { return X1[i + k * n]; },
         [&](int k, int j) { return Einv[k + j * n]; },
         [](int, int) { return 0.0; },

@@ -296,10 +296,13 @@ def test_collapse_feedback(capi, oracle):
     s.close()
 
 
-def test_cycle_append(capi, oracle):
+@pytest.mark.parametrize("dims", [(4, 2, 6, 3), (12, 4, 7, 3), (36, 12, 5, 2)], ids=lambda d: "nx%d_nu%d_T%d_B%d" % d)
+def test_cycle_append(capi, oracle, dims):
     """cycleAppend (proximal-riccati.hxx:80-88, mpc-util.hpp:17-22): factor storage rotates
-    left over [0, N), the new knot becomes knot N-1, and the next solve sees the rotated problem."""
-    nx, nu, T, B, mu = 4, 2, 6, 3, 1e-10
+    left over [0, N), the new knot becomes knot N-1, and the next solve sees the rotated problem.
+    The nx = 12 / 36 shapes run the specialised sweep and rollout kernels through the ring offset."""
+    nx, nu, T, B = dims
+    mu = 1e-10
     pp = generate_problems(B, T, nx, nu, seed=5)
     extra = generate_problems(1, 1, nx, nu, seed=6)
     s = capi.Solver.for_problems(pp)
