@@ -360,27 +360,55 @@ def e2e_run(torch, capi, s_dev, w, K, W, dist, world, theta):
     k, a, b = s_dev.download_packed(0, Be)
     knots[:], G0[:], g0[:] = k, a, b
     del k, a, b
-    s = s_dev if Be == B else capi.Solver(nx, nu, nc, nth, horizon=T, batch=Be, num_legs=legs, device=torch.cuda.current_device())
     out = (pinned(Be, T + 1, nx), pinned(Be, T + 1, max(nu, 1))[:, :, :nu], pinned(Be, T + 1, max(nc, 1))[:, :, :nc],
            pinned(Be, nx + T * nx))
     if nu == 0 or nc == 0:
         out = tuple(np.ascontiguousarray(o) for o in out)
     th = None if theta is None else np.ascontiguousarray(theta[:Be])
 
-    def step():
-        s.upload_packed(knots, G0, g0)
-        s.backward(MU, MU)
-        s.forward(th, out=out)
+    # The batch goes through NCH independent solver handles (contiguous slices of the problems),
+    # each on its own CUDA stream and driven by its own host thread: the H2D copy of one slice
+    # overlaps the sweep of another and the D2H of a third (garb200_forward blocks only its own
+    # stream; ctypes releases the GIL).  Same C-ABI calls a user would make for a sharded batch.
+    from aligator_swk_b200 import sharding
+    NCH = 4 if (Be >= 64 and legs < 2) else 1
+    dev = torch.cuda.current_device()
+    chunks = []
+    for c in range(NCH):
+        lo, hi = sharding.shard_bounds(Be, c, NCH)
+        sc = capi.Solver(nx, nu, nc, nth, horizon=T, batch=hi - lo, num_legs=legs, device=dev)
+        st = torch.cuda.Stream()
+        sc.set_stream(st.cuda_stream)
+        chunks.append((sc, st, lo, hi))
 
-    for _ in range(W):
-        step()
+    def run_chunk(c, nsteps):
+        sc, st, lo, hi = chunks[c]
+        torch.cuda.set_device(dev)
+        o = tuple(x[lo:hi] for x in out)
+        for _ in range(nsteps):
+            sc.upload_packed(knots[lo:hi], G0[lo:hi], g0[lo:hi])
+            sc.backward(MU, MU)
+            sc.forward(None if th is None else th[lo:hi], out=o)
+
+    def run(nsteps):
+        if NCH == 1:
+            run_chunk(0, nsteps)
+            return
+        ts = [threading.Thread(target=run_chunk, args=(c, nsteps)) for c in range(NCH)]
+        for t_ in ts:
+            t_.start()
+        for t_ in ts:
+            t_.join()
+
+    run(W)
     torch.cuda.synchronize()
     if dist is not None:
         dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(K):
-        step()
+    torch.cuda.synchronize()
+    run(K)                               # every forward() returns with its results in host memory
+    torch.cuda.synchronize()
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
@@ -392,10 +420,11 @@ def e2e_run(torch, capi, s_dev, w, K, W, dist, world, theta):
     d2h = sum(o.nbytes for o in out)
     r = {"value": Be * world / (ms * 1e-3), "unit": "solves/s", "h2d_bytes_per_step": int(h2d),
          "d2h_bytes_per_step": int(d2h), "ms_per_step": ms, "batch_per_gpu": Be}
+    r["streams"] = NCH
     if note:
         r["note"] = note
-    if s is not s_dev:
-        s.close()
+    for sc, _, _, _ in chunks:
+        sc.close()
     return r
 
 
