@@ -23,21 +23,15 @@ __device__ __forceinline__ void dmma_884(double &c0, double &c1, double a, doubl
       : "d"(a), "d"(b));
 }
 
-/// Strided matrix view with compile-time strides: element (i,j) at p[i*RS + j*CS].
-template <int RS, int CS> struct MV {
-  double *p;
-  __device__ __forceinline__ double operator()(int i, int j) const { return p[i * RS + j * CS]; }
-};
-
 // ------------------------------------------------------------------------------------------
 // C(i,j) = cin(i,j) + sum_k a(i,k) b(k,j),  M x N x K, distributed over NW warps.
 // a / b / cin / store are functors (lambdas): a(i,k), b(k,j), cin(i,j) -> double,
 // store(i,j,v).  Indices handed to a/b/cin are always clamped into range; padded rows /
 // columns of the 8x8 tiles compute garbage that is never stored.  K is zero-filled to a
-// multiple of 4.  TB = number of 8-column tiles that share one A fragment.
+// multiple of 4.
 // No barrier inside: the caller synchronises before (operands ready) and after.
 // ------------------------------------------------------------------------------------------
-template <int M, int N, int K, int NW, int TB = 1, class FA, class FB, class FC, class FS>
+template <int M, int N, int K, int NW, class FA, class FB, class FC, class FS>
 __device__ __forceinline__ void mma_gemm(int warp, int lane, FA a, FB b, FC cin, FS store) {
   if constexpr (M <= 0 || N <= 0) return;
   constexpr int TM = (M + 7) / 8, TN = (N + 7) / 8, NTILE = TM * TN;
@@ -220,52 +214,6 @@ template <int N, int NT> __device__ __forceinline__ void mirror_lower_ct(int tid
 }
 
 // ------------------------------------------------------------------------------------------
-// Solve S X = R in place for SPD S (lower triangle read and destroyed, col-major ld N) and
-// R an N x NR col-major block (ld N).  Square-root-free LDL^T elimination fused with the
-// forward substitution, then a column-oriented backward substitution with the reciprocal
-// pivots kept in `dinv` (N doubles of scratch).  One barrier per pivot in each phase.
-// Thread (r0, c0): row slot r0 = tid % N, column group c0 = tid / N (CG = NT / N groups).
-// Returns false when a pivot is not positive (LLT would report NumericalIssue).
-// ------------------------------------------------------------------------------------------
-template <int N, int NR, int NT>
-__device__ __forceinline__ bool ldlt_solve(int tid, double *S, double *R, double *dinv) {
-  constexpr int CG = (NT / N) > 0 ? (NT / N) : 1;
-  static_assert(NT >= N, "ldlt_solve needs at least N threads");
-  const int c0 = tid / N;
-  const int r0 = (c0 < CG) ? tid - c0 * N : (1 << 28);
-  bool ok = true;
-#pragma unroll 1
-  for (int k = 0; k < N; k++) {
-    const double d = S[k + k * N];
-    if (!(d > 0.0)) ok = false;
-    const double di = 1.0 / d;
-    const int i = k + 1 + r0;
-    if (i < N) {
-      const double l = S[i + k * N] * di;
-      for (int j = k + 1 + c0; j <= i; j += CG) S[i + j * N] = fma(-l, S[j + k * N], S[i + j * N]);
-#pragma unroll 4
-      for (int j = c0; j < NR; j += CG) R[i + j * N] = fma(-l, R[k + j * N], R[i + j * N]);
-    }
-    if (tid == 0) dinv[k] = di;
-    cta_sync<NT>();
-  }
-#pragma unroll 1
-  for (int k = N - 1; k >= 0; k--) {
-    const double di = dinv[k];
-    const int i = r0;                       // rows i < k
-    if (i < k) {
-      const double l = S[k + i * N] * di;
-#pragma unroll 4
-      for (int j = c0; j < NR; j += CG) R[i + j * N] = fma(-l, R[k + j * N], R[i + j * N]);
-    }
-    cta_sync<NT>();
-    for (int j = tid; j < NR; j += NT) R[k + j * N] *= di;   // row k is final, nobody reads it again unscaled
-  }
-  cta_sync<NT>();
-  return ok;
-}
-
-// ------------------------------------------------------------------------------------------
 // Runtime-extent DMMA update with ONE k-step (K = 4):  C(i,j) = cin(i,j) + sum_{k<4} a(i,k) b(k,j)
 // for i < M, j < N; `lower`: only the 8x8 tiles on or below the diagonal (M == N).
 // ------------------------------------------------------------------------------------------
@@ -314,14 +262,6 @@ template <int LD> struct RhsColMajor {
   __device__ __forceinline__ double get(int i, int j) const { return p[i + j * LD]; }
   __device__ __forceinline__ void set(int i, int j, double v) const { p[i + j * LD] = v; }
 };
-/// The (1 + n) right-hand sides of the reduced KKT system where they sit in a gains record:
-/// column j < n is column j of the row-major fb rows, column n is ff (riccati-kernel.hpp:76-78).
-template <int NXc> struct RhsGains {
-  double *ff, *fb;
-  __device__ __forceinline__ double get(int i, int j) const { return j < NXc ? fb[i * NXc + j] : ff[i]; }
-  __device__ __forceinline__ void set(int i, int j, double v) const { if (j < NXc) fb[i * NXc + j] = v; else ff[i] = v; }
-};
-
 /// The same with the theta block and padding: column j > n is column j - n - 1 of the row-major
 /// fth rows; rows >= S (padding of the blocked factorisation) read 0 and drop writes.
 template <int NXc, int H, int S> struct RhsGainsTh {
@@ -336,20 +276,18 @@ template <int NXc, int H, int S> struct RhsGainsTh {
   }
 };
 
-/// A window of NRW columns starting at col0 of the same block; columns past n read 0 and drop writes.
-template <int NXc> struct RhsGainsPart {
-  double *ff, *fb;
-  int col0;
-  __device__ __forceinline__ double get(int i, int j) const {
-    const int jj = col0 + j;
-    return jj < NXc ? fb[i * NXc + jj] : (jj == NXc ? ff[i] : 0.0);
-  }
-  __device__ __forceinline__ void set(int i, int j, double v) const {
-    const int jj = col0 + j;
-    if (jj < NXc) fb[i * NXc + jj] = v; else if (jj == NXc) ff[i] = v;
-  }
-};
-
+// ------------------------------------------------------------------------------------------
+// Solve S X = R in place by a BLOCKED square-root-free LDL^T (N % 4 == 0, lower triangle of the
+// col-major S read and overwritten by L; R: N x NR right-hand sides through an accessor).
+// Four pivots per block step: (A) every thread factors the 4x4 diagonal block redundantly in
+// registers, threads < N-r0-4 turn their row of the panel into L and keep the unscaled row in
+// Wp, threads CO.. forward-substitute one right-hand-side column each; (B) the trailing matrix and
+// the right-hand sides below the block are updated with K = 4 DMMA tiles (mma_k4).  Backward
+// substitution mirrors it (C: 4 rows per column in registers, D: DMMA update of the rows above).
+// The pivot signs are checked against (+)^NPOS (-)^(N-NPOS): returns false when the matrix does
+// not have that inertia (SPD: NPOS = N; quasi-definite KKT block: NPOS = nu).
+// Scratch: Wp 4 (N - 4) doubles, dinv N doubles.  Needs NT >= round32(N - 4) + NR threads.
+// ------------------------------------------------------------------------------------------
 template <int N, int NR, int NT, int NPOS = N, class RH>
 __device__ __forceinline__ bool ldlt_solve_blocked(int tid, double *S, RH R, double *Wp, double *dinv) {
   static_assert(N % 4 == 0, "blocked LDL^T needs N % 4 == 0");
@@ -470,176 +408,9 @@ __device__ __forceinline__ bool ldlt_solve_blocked(int tid, double *S, RH R, dou
 }
 
 // ------------------------------------------------------------------------------------------
-// X = E^{-1} by LU with row partial pivoting, executed by ONE warp on a row-major work
-// array W[N][LDW] (LDW = 2N+1, odd => lane-private rows are bank-conflict free).
-// Lanes own rows (lane, lane+32, ...); rows never move, `piv[k]` records the pivot row of
-// step k.  Phase 1 factors E in place (multipliers stored below the pivots), phases 2/3 run
-// the two triangular solves with ONE OUTPUT COLUMN PER LANE, so they need no barrier.
-// Xg: col-major N x N output in global memory.  Returns false on an exactly zero pivot.
-// Tie-break on equal |pivot candidates|: lowest row index (Eigen: lowest position).
-// ------------------------------------------------------------------------------------------
-template <int N>
-__device__ __forceinline__ bool lu_inverse_warp(int lane, const double *__restrict__ Eg, double *W,
-                                                int *piv, double *__restrict__ Xg) {
-  constexpr int LDW = 2 * N + 1;
-  constexpr int RPL = (N + 31) / 32;     // rows per lane
-  // load E (col-major in global: consecutive lanes -> consecutive addresses)
-  for (int j = 0; j < N; j++)
-#pragma unroll
-    for (int s = 0; s < RPL; s++) {
-      const int i = lane + 32 * s;
-      if (i < N) W[i * LDW + j] = Eg[i + j * N];
-    }
-  unsigned active = 0;   // bit s: own row lane+32s not yet used as a pivot
-#pragma unroll
-  for (int s = 0; s < RPL; s++) if (lane + 32 * s < N) active |= 1u << s;
-  __syncwarp();
-  bool ok = true;
-#pragma unroll 1
-  for (int k = 0; k < N; k++) {
-    // pivot search: max |W[i][k]| over active rows; 64-bit key = |value| bits, low 6 bits <- ~row
-    unsigned long long best = 0ull;
-    bool any = false;
-#pragma unroll
-    for (int s = 0; s < RPL; s++) {
-      const int i = lane + 32 * s;
-      if ((active >> s) & 1u) {
-        unsigned long long key = (unsigned long long)__double_as_longlong(fabs(W[i * LDW + k]));
-        key = (key & ~0x7Full) | (unsigned long long)(127 - i);   // N <= 128
-        if (!any || key > best) best = key;
-        any = true;
-      }
-    }
-    const unsigned hi = any ? (unsigned)(best >> 32) : 0u, lo = (unsigned)best;
-    const unsigned mhi = __reduce_max_sync(0xffffffffu, hi);
-    const unsigned mlo = __reduce_max_sync(0xffffffffu, (any && hi == mhi) ? lo : 0u);
-    const int r = 127 - (int)(mlo & 0x7Fu);
-    const double pv = W[r * LDW + k];
-    if (pv == 0.0) ok = false;
-    const double pinv = 1.0 / pv;
-    if (lane == 0) piv[k] = r;
-#pragma unroll
-    for (int s = 0; s < RPL; s++) {
-      const int i = lane + 32 * s;
-      if (i == r) active &= ~(1u << s);
-      else if ((active >> s) & 1u) {
-        double *row = W + i * LDW;
-        const double *prow = W + r * LDW;
-        const double l = row[k] * pinv;
-        row[k] = l;
-        for (int j = k + 1; j < N; j++) row[j] = fma(-l, prow[j], row[j]);
-      }
-    }
-    __syncwarp();
-  }
-  // phase 2: Y = L^{-1} P  (column j per lane): y_{r_k} = [r_k == j] - sum_{s<k} l(r_k, s) y_{r_s}
-  // phase 3: X = U^{-1} Y               : x_k = (y_{r_k} - sum_{s>k} u(r_k, s) x_s) / u(r_k, k)
-  for (int j = lane; j < N; j += 32) {
-    double *col = W + N + j;               // element of row i: col[i * LDW]
-#pragma unroll 1
-    for (int k = 0; k < N; k++) {
-      const int rk = piv[k];
-      const double *row = W + rk * LDW;
-      double acc = (rk == j) ? 1.0 : 0.0;
-      for (int s = 0; s < k; s++) acc = fma(-row[s], col[piv[s] * LDW], acc);
-      col[rk * LDW] = acc;
-    }
-#pragma unroll 1
-    for (int k = N - 1; k >= 0; k--) {
-      const int rk = piv[k];
-      const double *row = W + rk * LDW;
-      double acc = col[rk * LDW];
-      for (int s = k + 1; s < N; s++) acc = fma(-row[s], col[piv[s] * LDW], acc);
-      col[rk * LDW] = acc / row[k];
-    }
-  }
-  __syncwarp();
-  // X(k, j) = W[piv[k]][N + j]  -> col-major global, consecutive lanes = consecutive k
-  for (int j = 0; j < N; j++)
-    for (int k = lane; k < N; k += 32) Xg[k + j * N] = W[piv[k] * LDW + N + j];
-  return ok;
-}
-
-// ------------------------------------------------------------------------------------------
-// Reduced stage KKT system (s = nu + nc <= 32 unknowns, 1 + n right-hand sides sitting in a
-// gains record).  The matrix [Rhat D^T; D -mueq I] is quasi-definite for a convex stage, so
-// elimination in the natural order needs no pivoting and its pivots carry the inertia
-// (+)^NPOS (-)^(S-NPOS), which is verified.  Every warp inverts the matrix redundantly in
-// REGISTERS (lane i owns row i, Gauss-Jordan, pivot row broadcast by shuffles: no shared-memory
-// round trip, no CTA barrier), parks the inverse in its private scratch and multiplies it into
-// the column blocks it owns on the tensor pipe.  Returns false if the inertia check fails
-// (caller falls back to Bunch-Kaufman); the right-hand sides are then garbage.
-// ------------------------------------------------------------------------------------------
-template <int S, int NPOS, int NXc, int NW>
-__device__ __forceinline__ bool kkt_solve_inverse(int warp, int lane, const double *K, double *inv,
-                                                  double *ff, double *fb) {
-  static_assert(S <= 32, "reduced KKT: nu + nc <= 32");
-  double a[S];
-  const int row = min(lane, S - 1);
-#pragma unroll
-  for (int j = 0; j < S; j++) a[j] = (j <= row) ? K[row + j * S] : K[j + row * S];   // symmetric from lower
-  bool ok = true;
-#pragma unroll
-  for (int k = 0; k < S; k++) {
-    const double pv = __shfl_sync(0xffffffffu, a[k], k);
-    if (!((k < NPOS ? pv : -pv) > 0.0)) ok = false;
-    const double pinv = __drcp_rn(pv);
-    const bool isp = lane == k;
-    const double f = isp ? 0.0 : a[k] * pinv;
-#pragma unroll
-    for (int j = 0; j < S; j++) {
-      if (j == k) continue;
-      const double bj = __shfl_sync(0xffffffffu, a[j], k);
-      a[j] = fma(-f, bj, a[j]);
-    }
-    a[k] = isp ? pinv : -f;
-    if (isp) {
-#pragma unroll
-      for (int j = 0; j < S; j++) if (j != k) a[j] *= pinv;
-    }
-  }
-  if (lane < S) {
-#pragma unroll
-    for (int j = 0; j < S; j++) inv[lane + j * S] = a[j];
-  }
-  __syncwarp();
-  // X = inv * RHS, column blocks tj = warp, warp + NW, ...
-  constexpr int NR = NXc + 1, TM = (S + 7) / 8, TN = (NR + 7) / 8, KS = (S + 3) / 4;
-  const RhsGains<NXc> R{ff, fb};
-  const int g = lane >> 2, q = lane & 3;
-  for (int tj = warp; tj < TN; tj += NW) {
-    const int jb = min(tj * 8 + g, NR - 1);
-    double bv[KS], c0[TM], c1[TM];
-#pragma unroll
-    for (int ks = 0; ks < KS; ks++) { const int k = ks * 4 + q; bv[ks] = k < S ? R.get(k, jb) : 0.0; }
-#pragma unroll
-    for (int ti = 0; ti < TM; ti++) {
-      c0[ti] = 0.0; c1[ti] = 0.0;
-      const int ia = min(ti * 8 + g, S - 1);
-#pragma unroll
-      for (int ks = 0; ks < KS; ks++) {
-        const int k = ks * 4 + q;
-        const double av = k < S ? inv[ia + k * S] : 0.0;
-        dmma_884(c0[ti], c1[ti], av, bv[ks]);
-      }
-    }
-    __syncwarp();
-#pragma unroll
-    for (int ti = 0; ti < TM; ti++) {
-      const int ic = ti * 8 + g, jc = tj * 8 + 2 * q;
-      if (ic < S) {
-        if (jc < NR) R.set(ic, jc, c0[ti]);
-        if (jc + 1 < NR) R.set(ic, jc + 1, c1[ti]);
-      }
-    }
-  }
-  return ok;
-}
-
-// ------------------------------------------------------------------------------------------
 // X = E^{-1} entirely in REGISTERS: in-place Gauss-Jordan elimination with row partial
 // pivoting (same pivot rule as PartialPivLU: largest |entry| of the column among the rows not
-// yet used).  LPM lanes own one matrix (16 for N <= 16: two matrices per warp), lane `sub`
+// yet used).  LPM lanes own one matrix (8 for N <= 16: four matrices per warp), lane `sub`
 // holds rows sub, sub + LPM, ...  All loops are unrolled so every register index is static;
 // per step the pivot row travels through N doubles of shared memory (`srow`) as a broadcast.
 // Rows never move: step k records its pivot row in spiv[k] and the row remembers its step,
