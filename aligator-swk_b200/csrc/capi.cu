@@ -134,7 +134,10 @@ int garb200_create(const garb200_config *cfg, garb200_solver **out) {
   p.GL = garb200_make_gain_layout(c.nx, c.nu, c.nc, nth_eff);
   p.VL = garb200_make_value_layout(c.nx, nth_eff);
   p.mudyn = p.mueq = 0.0;
-  if (backward_smem_bytes(p) > 227u * 1024u) {
+  const bool want_fast = !(c.flags & GARB200_FORCE_GENERIC) && fast_path_available(c.nx, c.nu, c.nc, c.nth, c.num_legs);
+  // (a shape with a specialised sweep may exceed the generic kernel's shared-memory plan: it then has
+  //  no generic fallback and ragged knots are refused at backward())
+  if (!want_fast && backward_smem_bytes(p) > 227u * 1024u) {
     char buf[256];
     snprintf(buf, sizeof buf, "dimensions need %zu bytes of shared memory per CTA (> 227 KB): "
              "nx=%d nu=%d nc=%d nth=%d not supported by this kernel generation",
@@ -158,7 +161,7 @@ int garb200_create(const garb200_config *cfg, garb200_solver **out) {
   TRYB(dmalloc(s, &p.gains, B * (T + 1) * p.GL.stride));
   TRYB(dmalloc(s, &p.values, B * p.nslots * p.VL.stride));
   p.einv = nullptr;
-  if (!(c.flags & GARB200_FORCE_GENERIC) && fast_path_available(c.nx, c.nu, c.nc, c.nth, c.num_legs))
+  if (want_fast)
     TRYB(dmalloc(s, &p.einv, B * (size_t)T * n * n));
   TRYB(dmalloc(s, &p.kkt0_ff, B * (n + c.nc0)));
   TRYB(dmalloc(s, &p.kkt0_fth, B * (n + c.nc0) * c.nth));

@@ -131,6 +131,64 @@ __device__ __forceinline__ void mma_gemm(int warp, int lane, FA a, FB b, FC cin,
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// Row-strip GEMM for operands that do not all fit in shared memory (nx = 76): a warp owns whole
+// 8-row strips of C (strip s -> warp s % NW, or the mirrored assignment with REV so that two
+// back-to-back uneven GEMMs load the warps evenly).  The strip-side operand a(i, k) may live in
+// GLOBAL memory: with PRE its K/4 fragments of the strip are fetched into registers before the
+// first DMMA issues (one L2 round trip per strip instead of one per k-step), and every element of
+// it is read exactly once per GEMM.  b(k, j) is read by every warp and must be in shared memory.
+// ------------------------------------------------------------------------------------------
+template <int M, int N, int K, int NW, bool PRE, bool REV, class FA, class FB, class FC, class FS>
+__device__ __forceinline__ void strip_gemm(int warp, int lane, FA a, FB b, FC cin, FS store) {
+  constexpr int TM = (M + 7) / 8, TN = (N + 7) / 8, KS = (K + 3) / 4;
+  const int g = lane >> 2, q = lane & 3;
+  const int w0 = REV ? (NW - 1 - warp) : warp;
+  int jb[TN];
+#pragma unroll
+  for (int u = 0; u < TN; u++) jb[u] = min(u * 8 + g, N - 1);
+#pragma unroll 1
+  for (int sidx = w0; sidx < TM; sidx += NW) {
+    const int ic = sidx * 8 + g, ia = min(ic, M - 1);
+    double av[PRE ? KS : 1];
+    if constexpr (PRE) {
+#pragma unroll
+      for (int ks = 0; ks < KS; ks++) {
+        const int k = ks * 4 + q;
+        av[ks] = (K % 4 == 0 || k < K) ? a(ia, min(k, K - 1)) : 0.0;
+      }
+    }
+    double acc[TN][2];
+#pragma unroll
+    for (int u = 0; u < TN; u++) {
+      const int jc = u * 8 + 2 * q;
+      acc[u][0] = cin(ia, min(jc, N - 1));
+      acc[u][1] = cin(ia, min(jc + 1, N - 1));
+    }
+#pragma unroll
+    for (int ks = 0; ks < KS; ks++) {
+      const int k = ks * 4 + q;
+      const bool kv = (K % 4 == 0) || (k < K);
+      const int kc = min(k, K - 1);
+      double a1;
+      if constexpr (PRE) a1 = av[ks]; else a1 = kv ? a(ia, kc) : 0.0;
+      double bv[TN];
+#pragma unroll
+      for (int u = 0; u < TN; u++) bv[u] = kv ? b(kc, jb[u]) : 0.0;
+#pragma unroll
+      for (int u = 0; u < TN; u++) dmma_884(acc[u][0], acc[u][1], a1, bv[u]);
+    }
+    if (ic < M) {
+#pragma unroll
+      for (int u = 0; u < TN; u++) {
+        const int jc = u * 8 + 2 * q;
+        if (jc < N) store(ic, jc, acc[u][0]);
+        if (jc + 1 < N) store(ic, jc + 1, acc[u][1]);
+      }
+    }
+  }
+}
+
 // Symmetric product: only the 8x8 tiles on or below the diagonal of the N x N result are
 // computed (TM (TM + 1) / 2 instead of TM^2 tiles), dealt round-robin to the warps.  `store` still
 // sees every element of a diagonal tile and filters i >= j itself.  (Skipping the upper tiles of

@@ -743,13 +743,14 @@ int launch_backward_fast(const DevParams &p, const int *h_nu_t, const int *h_nc_
     return nw == 4 ? launch_fast_t<36, 12, 0, 0, 4>(p, st) : launch_fast_t<36, 12, 0, 0, 5>(p, st);
   }
   if (p.nx == 36 && p.nu == 12 && p.nc == 6 && p.nth == 4) return launch_fast_t<36, 12, 6, 4, 5>(p, st);   // C3
+  if (big_path_available(p.nx, p.nu, p.nc, p.nth)) return launch_backward_big(p, st);                     // C5
   return -3;
 }
 
 bool fast_path_available(int nx, int nu, int nc, int nth, int num_legs) {
   if (num_legs >= 2) return false;
   return (nx == 12 && nu == 4 && nc == 0 && nth == 0) || (nx == 36 && nu == 12 && nc == 0 && nth == 0) ||
-         (nx == 36 && nu == 12 && nc == 6 && nth == 4);
+         (nx == 36 && nu == 12 && nc == 6 && nth == 4) || big_path_available(nx, nu, nc, nth);
 }
 
 } // namespace garb200

@@ -67,9 +67,14 @@ CASES = [
     (12, 4, 0, 0, 30, 3, 1e-7, "explicit_psd"),
     (36, 12, 6, 4, 12, 2, 1e-3, "explicit_psd"),  # C3 shape, LDL^T (non-Neumann) path with theta columns
     (36, 12, 6, 4, 40, 2, 1e-8, "explicit"),
+    (76, 32, 0, 0, 12, 3, 1e-11, "ref"),     # C5 shape (Talos walk): streaming sweep, sweep_big.cu
+    (76, 32, 0, 0, 6, 2, 1e-8, "explicit"),
+    (76, 32, 0, 0, 5, 2, 1e-2, "explicit_psd"),   # C5 shape, LDL^T (non-Neumann) path
 ]
 
-FAST_DIMS = ((12, 4, 0, 0), (36, 12, 0, 0), (36, 12, 6, 4))
+FAST_DIMS = ((12, 4, 0, 0), (36, 12, 0, 0), (36, 12, 6, 4), (76, 32, 0, 0))
+# shapes whose knot record exceeds the generic kernel's shared-memory plan: specialised sweep only
+NO_GENERIC_DIMS = ((76, 32, 0, 0),)
 
 
 @pytest.mark.parametrize("case", CASES, ids=lambda c: "nx%d_nu%d_nc%d_nth%d_T%d_B%d_%g_%s" % c)
@@ -78,7 +83,7 @@ def test_prox_parity(capi, oracle, case):
     _prox_parity(capi, oracle, case, capi.STORE_ALL_VALUES)
 
 
-FAST_SHAPES = [c for c in CASES if (c[0], c[1], c[2], c[3]) in FAST_DIMS]
+FAST_SHAPES = [c for c in CASES if (c[0], c[1], c[2], c[3]) in FAST_DIMS and (c[0], c[1], c[2], c[3]) not in NO_GENERIC_DIMS]
 
 
 @pytest.mark.parametrize("case", FAST_SHAPES, ids=lambda c: "nx%d_nu%d_nc%d_nth%d_T%d_B%d_%g_%s" % c)
@@ -210,6 +215,9 @@ def test_error_conventions(capi):
         s.synchronize()
     assert e.value.code == capi.ERR_NUMERIC
     assert s.get_flags()[0] & 1
+    # nx = 76 only has the streaming sweep: the generic kernel's shared-memory plan does not fit
+    with pytest.raises(capi.GarB200Error):
+        capi.Solver(76, 32, horizon=5, flags=capi.FORCE_GENERIC)
 
 
 def test_device_generator_roundtrip(capi, oracle):
@@ -296,7 +304,7 @@ def test_collapse_feedback(capi, oracle):
     s.close()
 
 
-@pytest.mark.parametrize("dims", [(4, 2, 6, 3), (12, 4, 7, 3), (36, 12, 5, 2)], ids=lambda d: "nx%d_nu%d_T%d_B%d" % d)
+@pytest.mark.parametrize("dims", [(4, 2, 6, 3), (12, 4, 7, 3), (36, 12, 5, 2), (76, 32, 4, 2)], ids=lambda d: "nx%d_nu%d_T%d_B%d" % d)
 def test_cycle_append(capi, oracle, dims):
     """cycleAppend (proximal-riccati.hxx:80-88, mpc-util.hpp:17-22): factor storage rotates
     left over [0, N), the new knot becomes knot N-1, and the next solve sees the rotated problem.
@@ -342,7 +350,7 @@ def test_cycle_append(capi, oracle, dims):
     s.close()
 
 
-@pytest.mark.parametrize("shape", [(12, 4, 20), (36, 12, 12)])
+@pytest.mark.parametrize("shape", [(12, 4, 20), (36, 12, 12), (76, 32, 6)])
 def test_fast_path_indefinite_kkt_falls_back_to_bunch_kaufman(capi, oracle, shape):
     """The specialised sweep factors the reduced KKT matrix without pivoting after checking its
     inertia; a knot with an indefinite Rhat must be re-factorised with Bunch-Kaufman pivoting and
@@ -359,7 +367,7 @@ def test_fast_path_indefinite_kkt_falls_back_to_bunch_kaufman(capi, oracle, shap
     s.close()
 
 
-@pytest.mark.parametrize("shape", [(12, 4, 15), (36, 12, 10)])
+@pytest.mark.parametrize("shape", [(12, 4, 15), (36, 12, 10), (76, 32, 4)])
 def test_fast_path_general_initial_constraint(capi, oracle, shape):
     """The specialised sweep solves the initial stage in reduced form when G0 == I exactly and
     with Bunch-Kaufman on [P0 G0^T; G0 -mu I] otherwise (proximal-riccati.hxx:44-62): a dense
