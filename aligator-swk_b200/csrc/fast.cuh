@@ -800,4 +800,168 @@ __device__ __forceinline__ bool gj_inverse_dmma(int lane, const double *__restri
   return ok;
 }
 
+// ------------------------------------------------------------------------------------------
+// The same block Gauss-Jordan inverse for matrices too large for one warp's registers (nx = 76):
+// one CTA of NWARP warps per matrix, the padded matrix ROW-major in shared memory (double2 tile
+// accesses), warp 0 pivots the 4-column panel (row-per-lane, partial pivoting over all unpivoted
+// rows) while the other CTAs of the SM run their rank-4 DMMA updates; two barriers per block step.
+// Deferred block transforms, final block-diagonal product and the un-permuting store are those of
+// gj_inverse_dmma; the "rows sorted by pivot step" copy is replaced by an indirect row lookup.
+// ------------------------------------------------------------------------------------------
+template <int N> struct GjCta {
+  static_assert(N % 4 == 0 && N <= 124, "CTA block Gauss-Jordan: N % 4 == 0, N <= 124 (7-bit row key)");
+  static constexpr int NTL = (N + 7) / 8, NP = NTL * 8, NB = N / 4;
+  static constexpr int LD = (NP % 16 == 8) ? NP : NP + 8;          // == 8 (mod 16): conflict-free double2 tiles
+  static constexpr int PLD = (NP % 16 == 8) ? NP + 4 : NP + 12;    // == 12 (mod 16): conflict-free B fragments
+  static constexpr int RPL = (NP + 31) / 32;
+  static constexpr int PAN = NP * LD, PROW = PAN + NP * 4, BINV = PROW + 4 * PLD;
+  static constexpr int SMEM = BINV + 16 * (2 * NTL);
+  static constexpr int SINTS = 2 * NP;
+};
+
+template <int N, int NWARP>
+__device__ __forceinline__ bool gj_inverse_cta(int tid, const double *__restrict__ Eg, double *__restrict__ Xg,
+                                               double *sw, int *si) {
+  using G = GjCta<N>;
+  constexpr int NTL = G::NTL, NP = G::NP, NB = G::NB, LD = G::LD, PLD = G::PLD, RPL = G::RPL, NT = 32 * NWARP;
+  double *M = sw, *pan = sw + G::PAN, *prow = sw + G::PROW, *sbinv = sw + G::BINV;
+  int *spiv = si, *sstep = si + NP;
+  const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, q = lane & 3;
+  for (int e = tid; e < NP * LD; e += NT) M[e] = 0.0;
+  for (int e = tid; e < 16 * (2 * NTL - NB); e += NT) sbinv[16 * NB + e] = 0.0;
+  __syncthreads();
+  for (int e = tid; e < N * N; e += NT) M[(e % N) * LD + (e / N)] = Eg[e];
+  bool act[RPL];
+#pragma unroll
+  for (int s = 0; s < RPL; s++) act[s] = lane + 32 * s < N;
+  int bad = 0;
+  __syncthreads();
+#pragma unroll 1
+  for (int kb = 0; kb < NB; kb++) {
+    const int c0 = 4 * kb;
+    if (warp == 0) {
+      double a[RPL][4];
+#pragma unroll
+      for (int s = 0; s < RPL; s++) {
+        const int row = lane + 32 * s;
+        if (row < NP) {
+          const double2 lo = *reinterpret_cast<const double2 *>(M + row * LD + c0), hi = *reinterpret_cast<const double2 *>(M + row * LD + c0 + 2);
+          a[s][0] = lo.x; a[s][1] = lo.y; a[s][2] = hi.x; a[s][3] = hi.y;
+        } else {
+          a[s][0] = a[s][1] = a[s][2] = a[s][3] = 0.0;
+        }
+      }
+      int rsel[4];
+#pragma unroll
+      for (int ss = 0; ss < 4; ss++) {
+        unsigned best = 0u;
+#pragma unroll
+        for (int s = 0; s < RPL; s++) {
+          const unsigned hi32 = (unsigned)__double2hiint(a[s][ss]) & 0x7fffffffu;
+          const unsigned key = (hi32 & ~0x7Fu) | (unsigned)(127 - (lane + 32 * s));
+          if (act[s] && key > best) best = key;
+        }
+        const unsigned mx = __reduce_max_sync(0xffffffffu, best);
+        const int r = 127 - (int)(mx & 0x7Fu);
+        const int rl = r & 31, rs = r >> 5;
+        rsel[ss] = r;
+        double pr[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          double v = a[0][j];
+#pragma unroll
+          for (int s = 1; s < RPL; s++) if (rs == s) v = a[s][j];
+          pr[j] = __shfl_sync(0xffffffffu, v, rl);
+        }
+        if (mx == 0u || pr[ss] == 0.0) bad = 1;
+        const double pinv = __drcp_rn(pr[ss]);
+#pragma unroll
+        for (int j = 0; j < 4; j++) pr[j] *= pinv;
+#pragma unroll
+        for (int s = 0; s < RPL; s++) {
+          const bool isp = (lane + 32 * s) == r;
+          const double mm = a[s][ss];
+#pragma unroll
+          for (int j = 0; j < 4; j++)
+            if (j != ss) a[s][j] = isp ? pr[j] : fma(-mm, pr[j], a[s][j]);
+          a[s][ss] = isp ? pinv : -mm * pinv;
+          if (isp) act[s] = false;
+        }
+      }
+      // W -> pan (A operand of the update), the matrix' own panel columns -> 0 (they receive W,
+      // resp. e_s for the pivot rows, through the identity block of prow)
+#pragma unroll
+      for (int s = 0; s < RPL; s++) {
+        const int row = lane + 32 * s;
+        if (row < NP) {
+          *reinterpret_cast<double2 *>(pan + row * 4) = make_double2(a[s][0], a[s][1]);
+          *reinterpret_cast<double2 *>(pan + row * 4 + 2) = make_double2(a[s][2], a[s][3]);
+          *reinterpret_cast<double2 *>(M + row * LD + c0) = make_double2(0.0, 0.0);
+          *reinterpret_cast<double2 *>(M + row * LD + c0 + 2) = make_double2(0.0, 0.0);
+        }
+      }
+      if (lane < 4) {
+        const int r = lane == 0 ? rsel[0] : lane == 1 ? rsel[1] : lane == 2 ? rsel[2] : rsel[3];
+        spiv[c0 + lane] = r;
+        sstep[r] = c0 + lane;
+      }
+      __syncwarp();
+      // raw pivot rows -> prow, panel columns of prow = I_4
+#pragma unroll
+      for (int sr = 0; sr < 4; sr++) {
+        const int r = rsel[sr];
+        for (int col = lane; col < NP; col += 32)
+          prow[sr * PLD + col] = (col >= c0 && col < c0 + 4) ? ((col - c0 == sr) ? 1.0 : 0.0) : M[r * LD + col];
+      }
+      if (lane < 16) {
+        const int sr = lane >> 2, sc = lane & 3;
+        const int r = sr == 0 ? rsel[0] : sr == 1 ? rsel[1] : sr == 2 ? rsel[2] : rsel[3];
+        sbinv[16 * kb + lane] = pan[r * 4 + sc];       // B^{-1}(sr, sc)
+        pan[r * 4 + sc] = 0.0;                         // W = 0 for the pivot rows
+        M[r * LD + c0 + sc] = (sr == sc) ? 1.0 : 0.0;
+      }
+    }
+    __syncthreads();
+    // rank-4 update: one DMMA per tile, whole 8-row strips per warp
+    for (int mt = warp; mt < NTL; mt += NWARP) {
+      const double af = pan[(g + 8 * mt) * 4 + q];
+      double2 c[NTL];
+      double bf[NTL];
+      double *Mr = M + (g + 8 * mt) * LD + 2 * q;
+#pragma unroll
+      for (int nt = 0; nt < NTL; nt++) { bf[nt] = prow[q * PLD + g + 8 * nt]; c[nt] = *reinterpret_cast<const double2 *>(Mr + 8 * nt); }
+#pragma unroll
+      for (int nt = 0; nt < NTL; nt++) dmma_884(c[nt].x, c[nt].y, af, bf[nt]);
+#pragma unroll
+      for (int nt = 0; nt < NTL; nt++) *reinterpret_cast<double2 *>(Mr + 8 * nt) = c[nt];
+    }
+    __syncthreads();
+  }
+  // X rows = blockdiag(B_kb^{-1}) * (rows in pivot-step order);  X(step(r), piv[c])
+  for (int mt = warp; mt < NTL; mt += NWARP) {
+    double x[NTL][2];
+#pragma unroll
+    for (int nt = 0; nt < NTL; nt++) x[nt][0] = x[nt][1] = 0.0;
+#pragma unroll
+    for (int j = 0; j < 2; j++) {
+      if (2 * mt + j < NB) {
+        const double av = ((g >> 2) == j) ? sbinv[16 * (2 * mt + j) + 4 * (g & 3) + q] : 0.0;
+        const double *Yr = M + spiv[8 * mt + 4 * j + q] * LD + g;
+#pragma unroll
+        for (int nt = 0; nt < NTL; nt++) dmma_884(x[nt][0], x[nt][1], av, Yr[8 * nt]);
+      }
+    }
+    const int row = g + 8 * mt;
+    if (row < N) {
+#pragma unroll
+      for (int nt = 0; nt < NTL; nt++) {
+        const int col = 8 * nt + 2 * q;
+        if (col < N) Xg[row + spiv[col] * N] = x[nt][0];
+        if (col + 1 < N) Xg[row + spiv[col + 1] * N] = x[nt][1];
+      }
+    }
+  }
+  return __syncthreads_or(bad) == 0;
+}
+
 } // namespace garb200

@@ -39,6 +39,20 @@ __global__ void __launch_bounds__(NT) einv_cta_kernel(const DevParams p) {
   if (!ok && tid == 0) atomicOr(reinterpret_cast<int *>(p.flags) + b, GARB200_FLAG_LU_SINGULAR);
 }
 
+// The same pre-pass as a block Gauss-Jordan on the tensor pipe (gj_inverse_cta, fast.cuh).
+template <int N, int NWARP>
+__global__ void __launch_bounds__(32 * NWARP, 3) einv_cta_dmma_kernel(const DevParams p) {
+  using G = GjCta<N>;
+  extern __shared__ __align__(16) double sm[];
+  int *si = reinterpret_cast<int *>(sm + G::SMEM);
+  const long long w = blockIdx.x;
+  const int b = (int)(w / p.T), t = (int)(w % p.T);
+  const double *Eg = p.knots + ((size_t)b * (p.T + 1) + phys_t(p, t)) * p.KL.stride + p.KL.E;
+  double *Xg = p.einv + ((size_t)b * p.T + phys_t(p, t)) * (size_t)(N * N);
+  const bool ok = gj_inverse_cta<N, NWARP>(threadIdx.x, Eg, Xg, sm, si);
+  if (!ok && threadIdx.x == 0) atomicOr(reinterpret_cast<int *>(p.flags) + b, GARB200_FLAG_LU_SINGULAR);
+}
+
 // ---- record offsets (identical to garb200_make_knot_layout / garb200_make_gain_layout) ---------
 template <int NX, int NU> struct BigPlan {
   static constexpr int n = NX, m = NU, s = NU, na = NX + 1;
@@ -441,7 +455,15 @@ static int launch_big_t(const DevParams &p, cudaStream_t st) {
     return -3;
   const long long total = (long long)p.batch * p.T;
   int launched = 0;
-  if (total > 0) {
+  static const bool lu_prepass = [] { const char *e = getenv("GARB200_EINV"); return e && e[0] == 'l'; }();
+  if (total > 0 && !lu_prepass) {
+    constexpr int EW = 5;
+    constexpr size_t esm = (size_t)GjCta<NX>::SMEM * sizeof(double) + (size_t)GjCta<NX>::SINTS * sizeof(int);
+    if (cudaFuncSetAttribute(einv_cta_dmma_kernel<NX, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)esm) != cudaSuccess) return -2;
+    einv_cta_dmma_kernel<NX, EW><<<(unsigned)total, 32 * EW, esm, st>>>(p);
+    if (cudaGetLastError() != cudaSuccess) return -2;
+    launched++;
+  } else if (total > 0) {
     constexpr int ENT = 256;
     const size_t esm = (size_t)3 * NX * NX * sizeof(double) + (size_t)3 * NX * sizeof(int) + 16;
     if (cudaFuncSetAttribute(einv_cta_kernel<ENT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)esm) != cudaSuccess) return -2;
