@@ -13,7 +13,8 @@
 // leg kernel left them (value records, knot records, G0); only the factors
 // (Bunch-Kaufman of every Schur-complemented diagonal block and the U^T blocks) are
 // written, because the refinement steps and the forward substitution re-read them.
-#include "device_linalg.cuh"
+#include <cstdlib>
+#include "fast.cuh"
 #include "kernels.cuh"
 
 namespace garb200 {
@@ -76,11 +77,13 @@ __device__ __forceinline__ void gemv_sub4(const G &g, int M, int K, const double
 }
 
 template <int NT>
-__global__ void __launch_bounds__(NT) condensed_kernel(const DevParams p) {
+__global__ void __launch_bounds__(NT) condensed_kernel(const DevParams p, const int only_marked) {
   extern __shared__ __align__(16) double sm[];
   using G = Group<NT>;
   G g; g.tid = threadIdx.x; g.bar_id = 0;
   const int b = blockIdx.x;
+  // second launch behind condensed_fast_kernel: only the problems it handed back (refine_steps == -1)
+  if (only_marked && p.refine_steps[b] != -1) return;
   const Csys cs(p, b);
   const int n = cs.n, nb = cs.nb, N = nb - 1;
   double *sD = sm, *sD2 = sD + n * n, *sB = sD2 + n * n, *sC = sB + n * n;
@@ -212,6 +215,210 @@ __global__ void __launch_bounds__(NT) condensed_kernel(const DevParams p) {
   if (g.tid == 0) p.refine_steps[b] = steps;
 }
 
+// ------------------------------------------------------------------------------------------
+// Dimension-specialised condensed solve (nx = N, nc0 = N): the same up-looking block elimination,
+// refinement and forward substitution (block-tridiagonal.hpp:80-179), restated for the GPU's
+// latency budget.  The Schur-complemented diagonal blocks are symmetric INDEFINITE for the
+// reference's problem distribution (its generator zeroes a block of Q), so a pivoted factorisation
+// is required; here every block is inverted by the block Gauss-Jordan with partial pivoting on the
+// tensor pipe (gj_inverse_dmma, one warp, matrix in registers), and
+//   * U^T = D^{-1} B^T and the Schur update D_i -= B U^T are DMMA GEMMs, the solved right-hand side a
+//     GEMV; D^{-1} is also the block solve of the refinement steps, whose residuals are evaluated
+//     against the ORIGINAL blocks, so the rounding of the explicit inverse is corrected there (the
+//     reference runs the same <= 5 refinement steps on its Bunch-Kaufman factors);
+//   * the next blocks arrive by TMA while the current one is inverted;
+//   * solution, residual and right-hand side live in shared memory; the residual is evaluated by
+//     all threads over (block, row) pairs at once; the sequential GEMV chains fetch the next matrix
+//     rows into registers before the barrier of the current step.
+// A zero pivot hands the problem to the Bunch-Kaufman kernel above (refine_steps = -1).
+// ------------------------------------------------------------------------------------------
+template <int N, int NW>
+__global__ void __launch_bounds__(32 * NW, 1) condensed_fast_kernel(const DevParams p) {
+  extern __shared__ __align__(16) double sm[];
+  using GJ = GjDmma<N>;
+  constexpr int n = N, nn = N * N, NT = 32 * NW, RPT = (N + 3) / 4;
+  static_assert(N % 2 == 0, "16-byte aligned TMA destinations");
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.x;
+  const Csys cs(p, b);
+  const int nb = cs.nb, Nn = nb - 1;
+  const int vlen = nb * n;
+  double *sD = sm, *sInv = sD + nn, *sC = sInv + nn, *sB0 = sC + nn, *sG0 = sB0 + 2 * nn;
+  double *gjw = sG0 + 2 * nn, *sx = gjw + ((GJ::SMEM + 1) & ~1), *sy = sx + n, *red = sy + n;
+  double *ssol = red + 16, *serr = ssol + vlen, *srhs = serr + vlen;
+  uint64_t *bars = reinterpret_cast<uint64_t *>(srhs + vlen);
+  int *gji = reinterpret_cast<int *>(bars + 2);
+  __shared__ int s_fail;
+  const size_t bb = (size_t)nn;
+  double *facD = p.cdiagF + (size_t)b * nb * bb, *facU = p.csubF + (size_t)b * nb * bb;
+  const double mu = p.mudyn;
+
+  if (tid == 0) { mbar_init(bars, 1); mbar_init(bars + 1, 1); fence_mbar_init(); s_fail = 0; }
+  for (int e = tid; e < vlen; e += NT) { const double v = cs.rhs(e / n, e % n); srhs[e] = v; ssol[e] = v; }
+  for (int e = tid; e < nn; e += NT) sD[e] = cs.diag_ptr(Nn)[e];
+  __syncthreads();
+  auto prefetch = [&](int i) {        // thread 0: super(i) and diag(i) -> buffers i & 1
+    const int bf = i & 1;
+    fence_proxy_async();
+    mbar_expect_tx(bars + bf, (uint32_t)(nn * 8) * (i > 0 ? 2u : 1u));
+    tma_load_1d(sB0 + bf * nn, cs.super_ptr(i), (uint32_t)nn * 8u, bars + bf);
+    if (i > 0) tma_load_1d(sG0 + bf * nn, cs.diag_ptr(i), (uint32_t)nn * 8u, bars + bf);
+  };
+  if (tid == 0) prefetch(Nn - 1);
+  bool failed = false;
+#pragma unroll 1
+  for (int i = Nn - 1; i >= 0; i--) {                  // block-tridiagonal.hpp:98-123
+    const int bf = i & 1;
+    const double *sB = sB0 + bf * nn, *sG = sG0 + bf * nn;
+    if (warp == 0) {
+      if (!gj_inverse_dmma<n>(lane, sD, sInv, true, gjw, gji) && lane == 0) s_fail = 1;
+    }
+    mbar_wait(bars + bf, (uint32_t)(((Nn - 1 - i) >> 1) & 1));
+    if (tid == 0 && i > 0) prefetch(i - 1);
+    __syncthreads();
+    if (s_fail) {
+      if (i > 0) mbar_wait(bars + (bf ^ 1), (uint32_t)(((Nn - i) >> 1) & 1));   // drain the pending prefetch
+      failed = true;
+      break;
+    }
+    // U^T = D^{-1} B^T ; rhs[i+1] <- D^{-1} rhs[i+1]
+    mma_gemm<n, n, n, NW>(warp, lane,
+        [&](int r, int k) { return sInv[r + k * n]; },
+        [&](int k, int c) { return sB[c + k * n]; },
+        [](int, int) { return 0.0; },
+        [&](int r, int c, double v) { sC[r + c * n] = v; });
+    gemv4<n, n, NT>(tid, [&](int r, int j) { return sInv[r + j * n]; }, [&](int j) { return ssol[(i + 1) * n + j]; },
+                    [](int) { return 0.0; }, [&](int r, double v) { sx[r] = v; });
+    __syncthreads();
+    for (int e = tid; e < nn; e += NT) { facU[(size_t)i * bb + e] = sC[e]; facD[(size_t)(i + 1) * bb + e] = sInv[e]; }
+    // diag[i] -= B U^T ; rhs[i] -= B rhs[i+1]
+    mma_gemm<n, n, n, NW>(warp, lane,
+        [&](int r, int k) { return -sB[r + k * n]; },
+        [&](int k, int c) { return sC[k + c * n]; },
+        [&](int r, int c) { return i == 0 ? (r == c ? -mu : 0.0) : sG[r + c * n]; },
+        [&](int r, int c, double v) { sD[r + c * n] = v; });
+    gemv4<n, n, NT>(tid, [&](int r, int j) { return -sB[r + j * n]; }, [&](int j) { return sx[j]; },
+                    [&](int r) { return ssol[i * n + r]; }, [&](int r, double v) { sy[r] = v; });
+    __syncthreads();
+    if (tid < n) { ssol[(i + 1) * n + tid] = sx[tid]; ssol[i * n + tid] = sy[tid]; }
+  }
+  if (!failed) {
+    __syncthreads();
+    if (warp == 0) {
+      if (!gj_inverse_dmma<n>(lane, sD, sInv, true, gjw, gji) && lane == 0) s_fail = 1;
+    }
+    __syncthreads();
+    if (s_fail) failed = true;
+  }
+  if (failed) {                        // uniform over the CTA: hand the problem to the Bunch-Kaufman kernel
+    if (tid == 0) p.refine_steps[b] = -1;
+    return;
+  }
+  gemv4<n, n, NT>(tid, [&](int r, int j) { return sInv[r + j * n]; }, [&](int j) { return ssol[j]; },
+                  [](int) { return 0.0; }, [&](int r, double v) { sx[r] = v; });
+  for (int e = tid; e < nn; e += NT) facD[e] = sInv[e];
+  __syncthreads();
+  if (tid < n) ssol[tid] = sx[tid];
+  __syncthreads();
+
+  // sequential GEMV chain helper: y_dst[r] = y_src[r] - sum_j A(r, j) x[j], 4 threads per row, the
+  // matrix rows already in registers (fetched before the previous barrier)
+  const int gr = tid >> 2, gq = tid & 3;
+  auto fetch = [&](const double *A, double (&a)[RPT]) {         // A col-major n x n, global
+#pragma unroll
+    for (int u = 0; u < RPT; u++) { const int j = gq + 4 * u; a[u] = (gr < n && j < n) ? __ldg(A + gr + (size_t)j * n) : 0.0; }
+  };
+  auto apply = [&](const double (&a)[RPT], const double *x, const double *ysrc, double *ydst, double sgn) {
+    double acc = 0.0;
+#pragma unroll
+    for (int u = 0; u < RPT; u++) { const int j = gq + 4 * u; if (j < n) acc = fma(a[u], x[j], acc); }
+    acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+    if (gr < n && gq == 0) ydst[gr] = (ysrc ? ysrc[gr] : 0.0) + sgn * acc;
+  };
+  static_assert(NT >= 4 * N, "GEMV chain: 4 threads per row");
+  {
+    double a[RPT];
+    fetch(facU, a);
+    for (int i = 0; i < Nn; i++) {                     // :131-134  rhs[i+1] -= U^T_{i+1} rhs[i]
+      double an[RPT];
+      if (i + 1 < Nn) fetch(facU + (size_t)(i + 1) * bb, an);
+      apply(a, ssol + i * n, ssol + (i + 1) * n, ssol + (i + 1) * n, -1.0);
+      __syncthreads();
+#pragma unroll
+      for (int u = 0; u < RPT; u++) a[u] = an[u];
+    }
+  }
+
+  // ---- iterative refinement (parallel-solver.hxx:155-175) -------------------------------
+  int steps = 0;
+  for (int it = 0; it < 5; it++) {
+    double mx = 0.0;
+    for (int idx = tid; idx < vlen; idx += NT) {       // err = rhs - A sol, all (block, row) pairs at once
+      const int k = idx / n, r = idx % n;
+      double acc = 0.0;
+      if (k == 0) acc = -mu * ssol[r];
+      else {
+        const double *Dk = cs.diag_ptr(k);
+        for (int j = 0; j < n; j++) acc = fma(__ldg(Dk + r + (size_t)j * n), ssol[k * n + j], acc);
+      }
+      if (k < Nn) {
+        const double *Sk = cs.super_ptr(k);
+        for (int j = 0; j < n; j++) acc = fma(__ldg(Sk + r + (size_t)j * n), ssol[(k + 1) * n + j], acc);
+      }
+      if (k > 0) {
+        const double *Sp = cs.super_ptr(k - 1);
+        for (int j = 0; j < n; j++) acc = fma(__ldg(Sp + j + (size_t)r * n), ssol[(k - 1) * n + j], acc);
+      }
+      const double e = srhs[idx] - acc;
+      serr[idx] = e;
+      const double ae = fabs(e);
+      if (!(ae <= mx)) mx = ae;
+    }
+    mx = warp_max(mx);
+    if (lane == 0) red[warp] = mx;
+    __syncthreads();
+    double resdl = 0.0;
+    for (int w = 0; w < NW; w++) resdl = fmax(resdl, red[w]);
+    __syncthreads();
+    if (resdl <= 1e-11) break;                        // condensedThreshold (parallel-solver.hpp:101)
+    // refinement step on err (block-tridiagonal.hpp:144-179) with D^{-1} as the block solve
+    {
+      double a[RPT], a2[RPT];
+      fetch(facD + (size_t)Nn * bb, a);
+      for (int i = Nn; i >= 0; i--) {
+        if (i > 0) fetch(cs.super_ptr(i - 1), a2);
+        apply(a, serr + i * n, nullptr, sx, 1.0);                    // z = D_i^{-1} e_i
+        __syncthreads();
+        if (tid < n) serr[i * n + tid] = sx[tid];
+        if (i > 0) {
+          fetch(facD + (size_t)(i - 1) * bb, a);
+          apply(a2, sx, serr + (i - 1) * n, serr + (i - 1) * n, -1.0);   // e_{i-1} -= B_{i-1} z
+        }
+        __syncthreads();
+      }
+    }
+    {
+      double a[RPT];
+      fetch(facU, a);
+      for (int i = 0; i < Nn; i++) {
+        double an[RPT];
+        if (i + 1 < Nn) fetch(facU + (size_t)(i + 1) * bb, an);
+        apply(a, serr + i * n, serr + (i + 1) * n, serr + (i + 1) * n, -1.0);
+        __syncthreads();
+#pragma unroll
+        for (int u = 0; u < RPT; u++) a[u] = an[u];
+      }
+    }
+    for (int e = tid; e < vlen; e += NT) ssol[e] += serr[e];
+    __syncthreads();
+    steps++;
+  }
+  double *sol = p.csol + (size_t)b * cs.vlen();
+  for (int e = tid; e < vlen; e += NT) sol[e] = ssol[e];
+  if (tid == 0) p.refine_steps[b] = steps;
+}
+
 // K0 -= Kth0 * sub[1]; after the reference's swap (parallel-solver.hxx:152-153)
 // condensedKktSystem.subdiagonal[1] is the ORIGINAL block super[1]^T = Vxt(knot 0)^T.
 __global__ void collapse_kernel(const DevParams p) {
@@ -241,8 +448,25 @@ int launch_condensed(const DevParams &p, cudaStream_t st) {
   auto kern = condensed_kernel<NT>;
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
     return -2;
-  kern<<<p.batch, NT, smem, st>>>(p);
-  return cudaGetLastError() == cudaSuccess ? 1 : -2;
+  int launched = 0, only_marked = 0;
+  static const bool force_bk = [] { const char *e = getenv("GARB200_CONDENSED"); return e && e[0] == 'b'; }();
+  if (n == 36 && p.nc0 == 36 && !force_bk) {
+    constexpr int N = 36, NW = 5;
+    const size_t vlen = (size_t)2 * p.num_legs * N;
+    const size_t fd = (size_t)7 * N * N + GjDmma<N>::SMEM + 2 + 2 * N + 16 + 3 * vlen + 4 + GjDmma<N>::SINTS / 2 + 2;
+    if (fd * sizeof(double) <= 200u * 1024u) {
+      auto kf = condensed_fast_kernel<N, NW>;
+      if (cudaFuncSetAttribute(kf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(fd * sizeof(double))) != cudaSuccess) return -2;
+      kf<<<p.batch, 32 * NW, fd * sizeof(double), st>>>(p);
+      if (cudaGetLastError() != cudaSuccess) return -2;
+      launched++;
+      only_marked = 1;
+    }
+  }
+  static const bool fast_only = [] { const char *e = getenv("GARB200_CONDENSED"); return e && e[0] == 'f'; }();   // debugging
+  if (fast_only && only_marked) return launched;
+  kern<<<p.batch, NT, smem, st>>>(p, only_marked);
+  return cudaGetLastError() == cudaSuccess ? launched + 1 : -2;
 }
 
 int launch_collapse(const DevParams &p, cudaStream_t st) {

@@ -7,15 +7,17 @@ timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smok
 timeout 600 python bench.py > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err; echo "default rc=$?"; tail -3 gpurun_out/bench_default.err; cat gpurun_out/bench_default.json
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err; echo "reference rc=$?"; cat gpurun_out/bench_reference.json
 timeout 600 python bench.py --workload c1b > gpurun_out/bench_c1b.json 2> gpurun_out/bench_c1b.err; echo "c1b rc=$?"; tail -3 gpurun_out/bench_c1b.err; cat gpurun_out/bench_c1b.json
-for wl in c1 c3 c4; do
+for wl in c1 c3 c4 c5; do
   timeout 300 python bench.py --workload $wl --steps 5 --warmup 3 --no-e2e --cpu-budget 3 > gpurun_out/bench_$wl.json 2> gpurun_out/bench_$wl.err; echo "$wl rc=$?"
 done
 if [ "$1" == "ncu" ]; then
-  for wl in c2 c1b; do
+  for wl in c2 c1b c3 c5; do
     timeout 300 python bench.py --workload $wl --steps 2 --warmup 3 --no-e2e --cpu-budget 1 > gpurun_out/plain_$wl.log 2>&1 && \
     timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_$wl.csv \
       python bench.py --workload $wl --steps 2 --warmup 3 --no-e2e --cpu-budget 1 > gpurun_out/ncu_launch_$wl.log 2>&1; echo "launch list $wl rc=$?"
-    timeout 900 ncu --set full --clock-control none --import-source on -k regex:"sweep_kernel|einv_|forward_kernel" -s 3 -c 3 -f -o gpurun_out/full_$wl \
+    timeout 900 ncu --set full --clock-control none --import-source on -k regex:"sweep_|einv_|forward_" -s 3 -c 3 -f -o gpurun_out/full_$wl \
       python bench.py --workload $wl --steps 1 --warmup 1 --no-e2e --cpu-budget 1 > gpurun_out/ncu_full_$wl.log 2>&1; echo "set full $wl rc=$?"
+    # the .ncu-rep files (with source) exceed what gpurun copies back: keep the raw-page CSV only
+    ncu -i gpurun_out/full_$wl.ncu-rep --page raw --csv > gpurun_out/full_$wl.raw.csv 2>/dev/null; rm -f gpurun_out/full_$wl.ncu-rep
   done
 fi

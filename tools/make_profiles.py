@@ -26,9 +26,13 @@ WANT = ["Kernel Name", "Grid Size", "Block Size", "gpu__time_duration.sum", "dra
 
 def ncu_full(wl):
     rep = os.path.join(GO, f"full_{wl}.ncu-rep")
-    if not os.path.exists(rep):
+    rawcsv = os.path.join(GO, f"full_{wl}.raw.csv")
+    if os.path.exists(rawcsv) and os.path.getsize(rawcsv):
+        raw = open(rawcsv).read()
+    elif os.path.exists(rep):
+        raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    else:
         return None
-    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(raw.splitlines()))
     hdr, units, data = rows[0], rows[1], rows[2:]
     out = os.path.join(PR, f"{RR}_ncu_full_{wl}.csv")
@@ -70,13 +74,13 @@ def launch_list(wl):
 
 
 summary = {"round": RR, "bench": {}, "ncu": {}}
-for name in ("default", "reference", "c1b", "c1", "c3", "c4"):
+for name in ("default", "reference", "c1b", "c1", "c3", "c4", "c5"):
     p = os.path.join(GO, f"bench_{name}.json")
     if os.path.exists(p) and os.path.getsize(p):
         line = open(p).read().strip().splitlines()[-1]
         open(os.path.join(PR, f"{RR}_bench_{name}.json"), "w").write(line + "\n")
         summary["bench"][name] = json.loads(line)
-for wl in ("c2", "c1b"):
+for wl in ("c2", "c1b", "c3", "c5"):
     summary["ncu"][wl] = {"full": ncu_full(wl), "launches": launch_list(wl)}
 for f in ("pytest_gpu.log", "smoke.log"):
     if os.path.exists(os.path.join(GO, f)):
