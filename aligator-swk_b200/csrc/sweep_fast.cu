@@ -59,8 +59,10 @@ __global__ void __launch_bounds__(32 * WPB, 3) einv_dmma_kernel(const DevParams 
 }
 
 // ---- shared-memory plan of the sweep (doubles) ---------------------------------------------
-template <int NX, int NU, int NC, int NTH = 0> struct FastPlan {
-  static constexpr int n = NX, m = NU, c = NC, s = NU + NC, h = NTH;
+// HREC: parameter dimension of the knot RECORD (leg mode: the record has no theta blocks, the
+// leg-end knot supplies Gx = A^T, Gu = B^T, Gth = -mu I, gamma = f as views; parallel-solver.hpp:43-51)
+template <int NX, int NU, int NC, int NTH = 0, int HREC = NTH> struct FastPlan {
+  static constexpr int n = NX, m = NU, c = NC, s = NU + NC, h = NTH, hr = HREC;
   static constexpr int NA = 1 + h;                      // augmented columns: the vector + the theta block
   static constexpr int na = n + NA;
   static constexpr int sp = (s + 3) & ~3;               // KKT block padded to a multiple of 4 (blocked LDL^T)
@@ -69,8 +71,8 @@ template <int NX, int NU, int NC, int NTH = 0> struct FastPlan {
   static constexpr int oQ = 0, oS = r2(oQ + n * n), oR = r2(oS + n * m), oq = r2(oR + m * m),
                        orr = r2(oq + n), oA = r2(orr + m), oB = r2(oA + n * n), oE = r2(oB + n * m),
                        of = r2(oE + n * n), oC = r2(of + n), oD = r2(oC + c * n), od = r2(oD + c * m),
-                       oGth = r2(od + c), oGx = r2(oGth + h * h), oGu = r2(oGx + n * h),
-                       ogam = r2(oGu + m * h), kstride = r2(ogam + h);
+                       oGth = r2(od + c), oGx = r2(oGth + hr * hr), oGu = r2(oGx + n * hr),
+                       ogam = r2(oGu + m * hr), kstride = r2(ogam + hr);
   static_assert(oS == oQ + n * n && oB == oA + n * n, "[Q|S] and [A|B] must be contiguous (even n*n)");
   static constexpr int nrows = m + c + 2 * n;
   static constexpr int gff = 0, gfb = r2(nrows), gfth = r2(gfb + nrows * n), gstride = r2(gfth + nrows * h);
@@ -100,18 +102,28 @@ template <int NX, int NU, int NC, int NTH = 0> struct FastPlan {
   static constexpr int total = bar + 2;
 };
 
-template <int NX, int NU, int NC, int NTH, int NW, bool PROF>
-__global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : (NW == 5 && NC == 0 && NTH == 0) ? 3 : NW == 5 ? 2 : NW == 1 ? 24 : 1))
+// LEG: one CTA per leg of the parallel-in-time solver (parallel-solver.hxx:111-143): knots [beg, end),
+// NTH = NX for the legs that end on a co-state cut (the leg-end knot is a terminal solve with nu > 0
+// and the coupling blocks as its parameter block), NTH = 0 for the last leg; the value function of
+// the leg's first knot goes to value slot `leg`, there is no initial stage.
+template <int NX, int NU, int NC, int NTH, int NW, bool PROF, bool LEG = false>
+__global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : (NW == 5 && NC == 0 && NTH == 0) ? 3 : (NW == 5 && NTH <= 4) ? 2 : NW == 1 ? 24 : 1))
 sweep_kernel(const DevParams p) {
   extern __shared__ __align__(16) double sm[];
-  using PL = FastPlan<NX, NU, NC, NTH>;
+  using PL = FastPlan<NX, NU, NC, NTH, LEG ? 0 : NTH>;
+  static_assert(!LEG || NC == 0, "leg mode: nc = 0");
   constexpr int n = NX, m = NU, c = NC, s = NU + NC, h = NTH, NT = 32 * NW;
   constexpr int NA = PL::NA, na = PL::na, sp = PL::sp;
   constexpr int hh = h > 0 ? h : 1;        // divisor-safe
   constexpr int rK = 0, rZ = m, rL = m + c, rA = m + c + n;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int b = blockIdx.x;
   const int T = p.T;
+  const int nlegs = LEG ? p.num_legs : 1;
+  const int leg = LEG ? (NTH > 0 ? (int)(blockIdx.x % (unsigned)(nlegs - 1)) : nlegs - 1) : 0;
+  const int b = (LEG && NTH > 0) ? (int)(blockIdx.x / (unsigned)(nlegs - 1)) : (int)blockIdx.x;
+  int beg = 0, end = T + 1;
+  if constexpr (LEG) get_work(T, leg, nlegs, beg, end);
+  const int tl = end - 1;                  // last knot of this sweep (T unless a coupled leg)
   const double mudyn = p.mudyn, mueq = p.mueq;
   double *rec = sm + PL::rec;
   double *Q = rec + PL::oQ, *S = rec + PL::oS, *R = rec + PL::oR, *qv = rec + PL::oq, *rv = rec + PL::orr;
@@ -156,7 +168,7 @@ sweep_kernel(const DevParams p) {
     const int pt = phys_t(p, t);
     const double *src = p.knots + (pbase + pt) * PL::kstride;
     fence_proxy_async();
-    if (t == T) {
+    if (t == tl) {                      // terminal / leg-end knot: E is not used
       mbar_expect_tx(bar, (uint32_t)PL::kstride * 8u);
       tma_load_1d(rec, src, (uint32_t)PL::kstride * 8u, bar);
     } else {
@@ -177,7 +189,7 @@ sweep_kernel(const DevParams p) {
     }
   };
   auto store_value = [&](int t) {     // [P | pv] is the value function of knot t
-    const int slot = p.store_all_values ? t : (t == 0 ? 0 : -1);
+    const int slot = p.store_all_values ? t : (LEG ? (t == beg ? leg : -1) : (t == 0 ? 0 : -1));
     if (slot < 0) return;
     double *v = p.values + ((size_t)b * p.nslots + slot) * p.VL.stride;
     for (int e = tid; e < n * n; e += NT) v[p.VL.Pmat + e] = P[e];
@@ -187,36 +199,104 @@ sweep_kernel(const DevParams p) {
       for (int e = tid; e < h * h; e += NT) v[p.VL.Vtt + e] = Vtt[e];
       for (int i = tid; i < h; i += NT) v[p.VL.vt + i] = vt[i];
     }
-    if (t == 0 && p.store_all_values) {                       // proximal-riccati.hxx:39-42
+    if (!LEG && t == 0 && p.store_all_values) {               // proximal-riccati.hxx:39-42
       for (int e = tid; e < n * n; e += NT) v[p.VL.Vxx + e] = P[e];
       for (int i = tid; i < n; i += NT) v[p.VL.vx + i] = pv[i];
     }
   };
+  // leg mode, last leg: the gains records carry an (unused) fth block of the coupled legs' width
+  auto zero_fth_tail = [&](int t) {
+    if constexpr (LEG && h == 0) {
+      double *g = p.gains + (pbase + phys_t(p, t)) * p.GL.stride;
+      for (int e = PL::gfth + tid; e < p.GL.stride; e += NT) g[e] = 0.0;
+    }
+  };
 
   // ---- terminal knot (nu = nc = 0): Pmat = Q, pvec = q, empty gains  (riccati-kernel.hxx:90-150)
-  if (tid == 0) issue_load(T);
+  if (tid == 0) issue_load(tl);
   mbar_wait(bar, phase); phase ^= 1;
-  for (int e = tid; e < n * n; e += NT) P[e] = Q[e];
-  for (int i = tid; i < n; i += NT) pv[i] = qv[i];
-  if constexpr (h > 0) {                                  // Vxt = Gx, Vtt = Gth, vt = gamma  (:142-149, nu = 0)
-    for (int e = tid; e < n * h; e += NT) Pth[e] = Gx[e];
-    for (int e = tid; e < h * h; e += NT) Vtt[e] = Gth[e];
-    for (int i = tid; i < h; i += NT) vt[i] = gam[i];
+  if constexpr (LEG && h > 0) {
+    // ---- leg-end knot of a coupled leg: terminalSolve with nu > 0 and the parameter block
+    //      Gx = A^T, Gu = B^T, Gth = -mudyn I, gamma = f     (riccati-kernel.hxx:110-149, parallel-solver.hpp:43-51)
+    auto build_term = [&]() {
+      for (int e = tid; e < m * m; e += NT) { const int i = e % m, j = e / m; kkt[i + j * sp] = R[i + j * m]; }
+      if constexpr (sp > s) {
+        constexpr int pr = sp - s > 0 ? sp - s : 1;
+        for (int e = tid; e < (sp - s) * sp; e += NT) { const int i = s + e % pr, j = e / pr; kkt[i + j * sp] = (i == j) ? -1.0 : 0.0; }
+      }
+      for (int i = tid; i < m; i += NT) ff[rK + i] = -rv[i];
+      for (int e = tid; e < m * n; e += NT) { const int i = e / n, j = e % n; fb[(rK + i) * n + j] = -S[j + i * n]; }
+      for (int e = tid; e < m * h; e += NT) { const int i = e / hh, j = e % hh; fth[(rK + i) * h + j] = -B[j + i * n]; }   // -Gu = -B^T
+    };
+    build_term();
+    cta_sync<NT>();
+    if (!ldlt_solve_blocked<sp, na, NT, m>(tid, kkt, RhsGainsTh<n, h, s>{ff, fb, fth}, P, P + 4 * sp)) {
+      build_term();
+      cta_sync<NT>();
+      if (warp == 0) {
+        if (!bk_factor_warp(lane, s, kkt, sp, kpiv, ksub)) flags |= GARB200_FLAG_BK_SINGULAR;
+      }
+      cta_sync<NT>();
+      for (int col = tid; col < na; col += NT) {
+        if (col == 0) bk_solve_column(s, kkt, sp, kpiv, ksub, ff, 1);
+        else if (col <= n) bk_solve_column(s, kkt, sp, kpiv, ksub, fb + (col - 1), n);
+        else bk_solve_column(s, kkt, sp, kpiv, ksub, fth + (col - n - 1), h);
+      }
+      cta_sync<NT>();
+    }
+    // [Pmat | pvec] = [Q | q] + S [K | kff]                                              (:134-140)
+    mma_gemm<n, n + 1, s, NW>(warp, lane,
+        [&](int i, int k) { return S[i + k * n]; },
+        [&](int k, int j) { return j < n ? fb[k * n + j] : ff[k]; },
+        [&](int i, int j) { return j < n ? Q[i + j * n] : qv[i]; },
+        [&](int i, int j, double v) { P[i + j * n] = v; });
+    // Vxt = A^T + K^T B^T ; Vtt = -mudyn I + B Kth ; vt = f + B kff                       (:142-149)
+    for (int e = tid; e < n * h; e += NT) {
+      const int i = e % n, j = e / n;
+      double v = A[j + i * n];
+#pragma unroll
+      for (int k = 0; k < m; k++) v = fma(fb[(rK + k) * n + i], B[j + k * n], v);
+      Pth[e] = v;
+    }
+    for (int e = tid; e < h * h + h; e += NT) {
+      if (e < h * h) {
+        const int a = e % hh, bcol = e / hh;
+        double v = (a == bcol) ? -mudyn : 0.0;
+#pragma unroll
+        for (int k = 0; k < m; k++) v = fma(B[a + k * n], fth[(rK + k) * h + bcol], v);
+        Vtt[e] = v;
+      } else {
+        const int a = e - h * h;
+        double v = f[a];
+#pragma unroll
+        for (int k = 0; k < m; k++) v = fma(B[a + k * n], ff[rK + k], v);
+        vt[a] = v;
+      }
+    }
+  } else {
+    for (int e = tid; e < n * n; e += NT) P[e] = Q[e];
+    for (int i = tid; i < n; i += NT) pv[i] = qv[i];
+    if constexpr (h > 0) {                                  // Vxt = Gx, Vtt = Gth, vt = gamma  (:142-149, nu = 0)
+      for (int e = tid; e < n * h; e += NT) Pth[e] = Gx[e];
+      for (int e = tid; e < h * h; e += NT) Vtt[e] = Gth[e];
+      for (int i = tid; i < h; i += NT) vt[i] = gam[i];
+    }
   }
-  store_gains(T);
+  store_gains(tl);
   {
-    double *gT = p.gains + (pbase + phys_t(p, T)) * p.GL.stride;
+    double *gT = p.gains + (pbase + phys_t(p, tl)) * p.GL.stride;
     for (int e = PL::gpart + tid; e < PL::gfth; e += NT) gT[e] = 0.0;
   }
-  store_value(T);
+  zero_fth_tail(tl);
+  store_value(tl);
   fence_proxy_async();
   cta_sync<NT>();
 
 #pragma unroll 1
-  for (int t = T - 1; t >= 0; t--) {
+  for (int t = tl - 1; t >= beg; t--) {
     if (tid == 0) {
       issue_load(t);
-      if (t > 0) {          // next knot's record and E^{-1} towards L2 while this one is solved
+      if (t > beg) {          // next knot's record and E^{-1} towards L2 while this one is solved
         const int pn = phys_t(p, t - 1);
         l2_prefetch(p.knots + (pbase + pn) * PL::kstride, (uint32_t)PL::kstride * 8u);
         l2_prefetch(p.einv + ((size_t)b * T + pn) * (size_t)(n * n), (uint32_t)(n * n) * 8u);
@@ -338,7 +418,7 @@ sweep_kernel(const DevParams p) {
         }
       }
       if constexpr (h > 0) {         // [-Guhat ; 0],  Guhat = Gu + B^T Lth0                  (:264-272)
-        for (int e = tid; e < m * h; e += NT) { const int i = e / hh, j = e % hh; fth[(rK + i) * h + j] = -(Gu[i + j * m] + BtVth[i + j * m]); }
+        for (int e = tid; e < m * h; e += NT) { const int i = e / hh, j = e % hh; fth[(rK + i) * h + j] = -((LEG ? 0.0 : Gu[i + j * m]) + BtVth[i + j * m]); }
         for (int e = tid; e < c * h; e += NT) fth[rZ * h + e] = 0.0;
       }
     };
@@ -523,29 +603,39 @@ sweep_kernel(const DevParams p) {
       // Vtt += Gth + Gu^T Kth + Vxt+^T Yth                                                (:286-298)
       for (int e = tid; e < n * h; e += NT) {
         const int i = e % n, j = e / n;
-        double v = Gx[e] + Vxn[e];
+        double v = Vxn[e];
+        if constexpr (!LEG) {
+          v += Gx[e];
 #pragma unroll
-        for (int k = 0; k < m; k++) v = fma(fb[(rK + k) * n + i], Gu[k + j * m], v);
+          for (int k = 0; k < m; k++) v = fma(fb[(rK + k) * n + i], Gu[k + j * m], v);
+        }
         Pth[e] = v;
       }
       for (int e = tid; e < h * h + h; e += NT) {
         if (e < h * h) {
           const int a = e % hh, bcol = e / hh;
-          double v = Vtt[e] + Gth[e] + Vttp[e];
+          double v = Vtt[e] + Vttp[e];
+          if constexpr (!LEG) {
+            v += Gth[e];
 #pragma unroll
-          for (int k = 0; k < m; k++) v = fma(Gu[k + a * m], fth[(rK + k) * h + bcol], v);
+            for (int k = 0; k < m; k++) v = fma(Gu[k + a * m], fth[(rK + k) * h + bcol], v);
+          }
           Vtt[e] = v;
         } else {
           const int a = e - h * h;
-          double v = vt[a] + gam[a] + vtp[a];
+          double v = vt[a] + vtp[a];
+          if constexpr (!LEG) {
+            v += gam[a];
 #pragma unroll
-          for (int k = 0; k < m; k++) v = fma(Gu[k + a * m], ff[rK + k], v);
+            for (int k = 0; k < m; k++) v = fma(Gu[k + a * m], ff[rK + k], v);
+          }
           vt[a] = v;
         }
       }
     }
     PH(12);
     store_gains(t);
+    zero_fth_tail(t);
     store_value(t);
     fence_proxy_async();
     cta_sync<NT>();
@@ -554,7 +644,7 @@ sweep_kernel(const DevParams p) {
   PH(14);
 
   // ---- initial stage: BK of [Pmat0 G0^T; G0 -mudyn I]        (proximal-riccati.hxx:44-62) ----
-  {
+  if constexpr (!LEG) {
     if (tid == 0) tma_store_wait_read();
     cta_sync<NT>();
     const int c0 = p.nc0, s0 = n + c0;
@@ -730,13 +820,45 @@ static int launch_fast_t(const DevParams &p, cudaStream_t st) {
   return launched + 1;
 }
 
+// Leg mode (ParallelRiccatiSolver::backward, parallel-solver.hxx:111-143): the E^{-1} pre-pass, then the
+// coupled legs (theta = co-state of the next leg, NTH = NX) and the last leg (NTH = 0).
+template <int NX, int NU, int NW>
+static int launch_fast_legs(const DevParams &p, cudaStream_t st) {
+  using PLc = FastPlan<NX, NU, 0, NX, 0>;
+  using PLl = FastPlan<NX, NU, 0, 0, 0>;
+  if (p.KL.stride != PLc::kstride || p.GL.stride != PLc::gstride || p.KL.E != PLc::oE || p.KL.f != PLc::of) return -3;
+  if ((size_t)PLc::total * sizeof(double) > 227u * 1024u) return -3;
+  constexpr int WPB = 4;
+  const long long total = (long long)p.batch * p.T;
+  constexpr size_t esm = (size_t)WPB * (GjDmma<NX>::SMEM * sizeof(double) + GjDmma<NX>::SINTS * sizeof(int));
+  if (cudaFuncSetAttribute(einv_dmma_kernel<NX, WPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)esm) != cudaSuccess) return -2;
+  einv_dmma_kernel<NX, WPB><<<(unsigned)((total + WPB - 1) / WPB), 32 * WPB, esm, st>>>(p);
+  if (cudaGetLastError() != cudaSuccess) return -2;
+  auto kc = sweep_kernel<NX, NU, 0, NX, NW, false, true>;
+  auto kl = sweep_kernel<NX, NU, 0, 0, NW, false, true>;
+  const size_t smc = (size_t)PLc::total * sizeof(double), sml = (size_t)PLl::total * sizeof(double);
+  if (cudaFuncSetAttribute(kc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smc) != cudaSuccess) return -2;
+  if (cudaFuncSetAttribute(kl, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sml) != cudaSuccess) return -2;
+  kc<<<p.batch * (p.num_legs - 1), 32 * NW, smc, st>>>(p);
+  if (cudaGetLastError() != cudaSuccess) return -2;
+  kl<<<p.batch, 32 * NW, sml, st>>>(p);
+  if (cudaGetLastError() != cudaSuccess) return -2;
+  return 3;
+}
+
 /// Returns the number of kernels launched, -3 if no specialisation matches (caller falls back
 /// to the generic kernel), < 0 otherwise on error.
 int launch_backward_fast(const DevParams &p, const int *h_nu_t, const int *h_nc_t, cudaStream_t st) {
-  if (p.num_legs >= 2 || p.einv == nullptr || p.T < 1) return -3;
+  if (p.einv == nullptr || p.T < 1) return -3;
   if (h_nu_t[p.T] != 0 || h_nc_t[p.T] != 0) return -3;
   for (int t = 0; t < p.T; t++)
     if (h_nu_t[t] != p.nu || h_nc_t[t] != p.nc) return -3;
+  if (p.num_legs >= 2) {
+    static const bool generic_legs = [] { const char *e = getenv("GARB200_LEGS"); return e && e[0] == 'g'; }();
+    if (generic_legs || p.store_all_values) return -3;
+    if (p.nx == 36 && p.nu == 12 && p.nc == 0 && p.nth == 0) return launch_fast_legs<36, 12, 5>(p, st);
+    return -3;
+  }
   if (p.nx == 12 && p.nu == 4 && p.nc == 0 && p.nth == 0) return launch_fast_t<12, 4, 0, 0, 1>(p, st);
   if (p.nx == 36 && p.nu == 12 && p.nc == 0 && p.nth == 0) {
     static const int nw = getenv("GARB200_NW36") ? atoi(getenv("GARB200_NW36")) : 5;   // tuning knob
@@ -748,7 +870,7 @@ int launch_backward_fast(const DevParams &p, const int *h_nu_t, const int *h_nc_
 }
 
 bool fast_path_available(int nx, int nu, int nc, int nth, int num_legs) {
-  if (num_legs >= 2) return false;
+  if (num_legs >= 2) return nx == 36 && nu == 12 && nc == 0 && nth == 0;
   return (nx == 12 && nu == 4 && nc == 0 && nth == 0) || (nx == 36 && nu == 12 && nc == 0 && nth == 0) ||
          (nx == 36 && nu == 12 && nc == 6 && nth == 4) || big_path_available(nx, nu, nc, nth);
 }

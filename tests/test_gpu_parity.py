@@ -254,7 +254,10 @@ LEG_CASES = [
     (32, 12, 0, 50, 6, 2, 1e-9),      # parallel_solver_class (tests/gar/parallel.cpp:199-271)
     (4, 2, 0, 11, 2, 3, 1e-9),
     (12, 4, 0, 50, 5, 4, 1e-10),
-    (36, 12, 0, 127, 8, 1, 1e-9),
+    (36, 12, 0, 127, 8, 1, 1e-9),     # specialised leg sweep + specialised condensed solve
+    (36, 12, 0, 50, 6, 3, 1e-9),
+    (36, 12, 0, 21, 2, 2, 1e-11),
+    (36, 12, 0, 9, 9, 2, 1e-8),       # one- and two-knot legs on the specialised path
     (8, 3, 2, 20, 3, 2, 1e-8),
     (6, 2, 0, 7, 8, 2, 1e-9),         # one-knot legs
 ]
@@ -281,10 +284,11 @@ def test_parallel_in_time_parity(capi, oracle, case):
     s.close()
 
 
-def test_collapse_feedback(capi, oracle):
+@pytest.mark.parametrize("dims", [(4, 2, 5, 3), (36, 12, 5, 3)], ids=lambda d: "nx%d_nu%d_T%d_J%d" % d)
+def test_collapse_feedback(capi, oracle, dims):
     """collapseFeedback (parallel-solver.hpp:55-66): K0 -= Kth0 * subdiagonal[1].  Explicit
     dynamics and two-knot legs so that the correction is not vanishingly small."""
-    nx, nu, T, J, mu = 4, 2, 5, 3, 1e-8
+    (nx, nu, T, J), mu = dims, 1e-8
     pp = generate_problems(2, T, nx, nu, 0, 0, seed=11, dist="explicit")
     s, xs, us, vs, lb = solve_gpu(capi, pp, mu, num_legs=J)
     G = GainLayout(nx, nu, 0, nx)
