@@ -61,8 +61,11 @@ __global__ void __launch_bounds__(32 * WPB, 3) einv_dmma_kernel(const DevParams 
 // ---- shared-memory plan of the sweep (doubles) ---------------------------------------------
 // HREC: parameter dimension of the knot RECORD (leg mode: the record has no theta blocks, the
 // leg-end knot supplies Gx = A^T, Gu = B^T, Gth = -mu I, gamma = f as views; parallel-solver.hpp:43-51)
-template <int NX, int NU, int NC, int NTH = 0, int HREC = NTH> struct FastPlan {
+// EG: E^{-1} is NOT staged in shared memory (it enters its three products as the strip-side operand
+// straight from L2, see strip_gemm); the shared-memory copy of the record then has no E block.
+template <int NX, int NU, int NC, int NTH = 0, int HREC = NTH, bool EG = false> struct FastPlan {
   static constexpr int n = NX, m = NU, c = NC, s = NU + NC, h = NTH, hr = HREC;
+  static constexpr int esh = EG ? NX * NX : 0;      // shift of the record blocks behind E in shared memory
   static constexpr int NA = 1 + h;                      // augmented columns: the vector + the theta block
   static constexpr int na = n + NA;
   static constexpr int sp = (s + 3) & ~3;               // KKT block padded to a multiple of 4 (blocked LDL^T)
@@ -83,13 +86,13 @@ template <int NX, int NU, int NC, int NTH = 0, int HREC = NTH> struct FastPlan {
   static_assert(n % 2 == 0, "row-major fb rows are written as 16-byte pairs");
   // smem
   static constexpr int rec = 0;
-  static constexpr int X1 = r2(rec + kstride);          // n x na
+  static constexpr int X1 = r2(rec + kstride - esh);    // n x na
   static constexpr int P = r2(X1 + n * na);             // n x na: [P | pvec | Vxt] / [Vxx | vx | Lth0] / [A_pre | tv | Yth_pre]
   static constexpr int BtV = r2(P + n * na);            // m x na
   static constexpr int kkt = r2(BtV + m * na);          // sp x sp
   static constexpr int ksub = r2(kkt + sp * sp);        // max(s, 2n) + 2
   static constexpr int KS = (sp > 2 * n ? sp : 2 * n) + 2;
-  static constexpr int dinv = r2(ksub + KS);            // n
+  static constexpr int dinv = EG ? ksub : r2(ksub + KS); // n   (EG: ksub is aliased, see sweep_kernel)
   static constexpr int rhat = r2(dinv + n);             // 16 doubles of reduction scratch
   static constexpr int atvx = r2(rhat + 16);            // n + m
   static constexpr int G = r2(atvx + n + m);            // gains staging: [ff | fb rows K,Z] then fth
@@ -97,8 +100,8 @@ template <int NX, int NU, int NC, int NTH = 0, int HREC = NTH> struct FastPlan {
   static constexpr int Pxt = r2(Gth_s + gthsz);         // Pxttilde = -Einv^T Vxt (n x h)
   static constexpr int Vxn = r2(Pxt + n * h);           // Vxt^T Afb (h x n, transposed: n x h col-major)
   static constexpr int Vtt = r2(Vxn + n * h);           // h x h | vt h | parts h*h + h
-  static constexpr int ints = r2(Vtt + 2 * (h * h + h)); // pivots: KS ints
-  static constexpr int bar = r2(ints + (KS + 1) / 2);
+  static constexpr int ints = r2(Vtt + 2 * (h * h + h)); // pivots: KS ints (EG: aliased, see sweep_kernel)
+  static constexpr int bar = EG ? ints : r2(ints + (KS + 1) / 2);
   static constexpr int total = bar + 2;
 };
 
@@ -106,12 +109,13 @@ template <int NX, int NU, int NC, int NTH = 0, int HREC = NTH> struct FastPlan {
 // NTH = NX for the legs that end on a co-state cut (the leg-end knot is a terminal solve with nu > 0
 // and the coupling blocks as its parameter block), NTH = 0 for the last leg; the value function of
 // the leg's first knot goes to value slot `leg`, there is no initial stage.
-template <int NX, int NU, int NC, int NTH, int NW, bool PROF, bool LEG = false>
-__global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : (NW == 5 && NC == 0 && NTH == 0) ? 3 : (NW == 5 && NTH <= 4) ? 2 : NW == 1 ? 24 : 1))
+template <int NX, int NU, int NC, int NTH, int NW, bool PROF, bool LEG = false, bool EG = false>
+__global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : (NW == 5 && NTH <= 4) ? 3 : NW == 1 ? 24 : 1))
 sweep_kernel(const DevParams p) {
   extern __shared__ __align__(16) double sm[];
-  using PL = FastPlan<NX, NU, NC, NTH, LEG ? 0 : NTH>;
+  using PL = FastPlan<NX, NU, NC, NTH, LEG ? 0 : NTH, EG>;
   static_assert(!LEG || NC == 0, "leg mode: nc = 0");
+  static_assert(!EG || !LEG, "EG is not combined with leg mode");
   constexpr int n = NX, m = NU, c = NC, s = NU + NC, h = NTH, NT = 32 * NW;
   constexpr int NA = PL::NA, na = PL::na, sp = PL::sp;
   constexpr int hh = h > 0 ? h : 1;        // divisor-safe
@@ -127,21 +131,27 @@ sweep_kernel(const DevParams p) {
   const double mudyn = p.mudyn, mueq = p.mueq;
   double *rec = sm + PL::rec;
   double *Q = rec + PL::oQ, *S = rec + PL::oS, *R = rec + PL::oR, *qv = rec + PL::oq, *rv = rec + PL::orr;
-  double *A = rec + PL::oA, *B = rec + PL::oB, *Einv = rec + PL::oE, *f = rec + PL::of;
-  double *C = rec + PL::oC, *D = rec + PL::oD, *d = rec + PL::od;
-  double *Gth = rec + PL::oGth, *Gx = rec + PL::oGx, *Gu = rec + PL::oGu, *gam = rec + PL::ogam;
+  double *A = rec + PL::oA, *B = rec + PL::oB, *Einv = rec + PL::oE, *f = rec + PL::of - PL::esh;
+  double *C = rec + PL::oC - PL::esh, *D = rec + PL::oD - PL::esh, *d = rec + PL::od - PL::esh;
+  double *Gth = rec + PL::oGth - PL::esh, *Gx = rec + PL::oGx - PL::esh, *Gu = rec + PL::oGu - PL::esh, *gam = rec + PL::ogam - PL::esh;
+  const double *gE = nullptr;                // EG: E^{-1} of the current knot in global memory
   double *fth = sm + PL::Gth_s;          // fth staging, nrows x h row-major
   double *Pxt = sm + PL::Pxt, *Vxn = sm + PL::Vxn;
   double *Vtt = sm + PL::Vtt, *vt = Vtt + h * h, *Vttp = vt + h, *vtp = Vttp + h * h;
   double *X1 = sm + PL::X1, *P = sm + PL::P, *BtV = sm + PL::BtV, *kkt = sm + PL::kkt;
-  double *ksub = sm + PL::ksub, *dinv = sm + PL::dinv, *atvx = sm + PL::atvx, *Gs = sm + PL::G;
+  // EG: the Bunch-Kaufman scratch (used only by the fallback paths) aliases dead blocks: P + 128.. in
+  // the stage fallback (Vxx is consumed by then, the LDL^T attempt used P[0, 5 sp) itself), BtV in the
+  // initial stage
+  double *ksub = EG ? sm + PL::P + 128 : sm + PL::ksub;
+  double *dinv = sm + PL::dinv, *atvx = sm + PL::atvx, *Gs = sm + PL::G;
   double *pv = P + n * n;         // column n of the augmented P block
   double *x1v = X1 + n * n;       // column n of the augmented X1 block
   double *btvx = BtV + m * n;     // column n of BtV: B^T vx
   double *Pth = P + n * (n + 1);  // theta columns of the P block: Vxt / Lth0 / Yth_pre
   double *BtVth = BtV + m * (n + 1);
   double *ff = Gs + PL::gff, *fb = Gs + PL::gfb;
-  int *kpiv = reinterpret_cast<int *>(sm + PL::ints);
+  int *kpiv = reinterpret_cast<int *>(EG ? sm + PL::P + 128 + PL::KS : sm + PL::ints);
+  static_assert(!EG || 128 + PL::KS + (PL::KS + 1) / 2 <= NX * NX, "aliased BK scratch must stay inside the dead Vxx block");
   double *red = sm + PL::rhat;    // NW doubles: cross-warp reduction scratch
   uint64_t *bar = reinterpret_cast<uint64_t *>(sm + PL::bar);
   int flags = 0;
@@ -168,6 +178,12 @@ sweep_kernel(const DevParams p) {
     const int pt = phys_t(p, t);
     const double *src = p.knots + (pbase + pt) * PL::kstride;
     fence_proxy_async();
+    if constexpr (EG) {                 // [Q..B] and [f..], the E block is never staged
+      mbar_expect_tx(bar, (uint32_t)(PL::kstride - PL::esh) * 8u);
+      tma_load_1d(rec, src, (uint32_t)PL::oE * 8u, bar);
+      tma_load_1d(rec + PL::oE, src + PL::of, (uint32_t)(PL::kstride - PL::of) * 8u, bar);
+      return;
+    }
     if (t == tl) {                      // terminal / leg-end knot: E is not used
       mbar_expect_tx(bar, (uint32_t)PL::kstride * 8u);
       tma_load_1d(rec, src, (uint32_t)PL::kstride * 8u, bar);
@@ -303,11 +319,19 @@ sweep_kernel(const DevParams p) {
       }
       tma_store_wait_read();
     }
+    if constexpr (EG) gE = p.einv + ((size_t)b * T + phys_t(p, t)) * (size_t)(n * n);
     mbar_wait(bar, phase); phase ^= 1;
     cta_sync<NT>();
     PH(0);
     // (1) [X1 | x1v] = Einv^T [P | pvec]          EinvP, -ptilde      (:175-178)
     //     theta columns: Pxttilde = -Einv^T Vxt -> Pxt                                   (:261-262)
+    if constexpr (EG)
+      strip_gemm<n, na, n, NW, true, false>(warp, lane,
+          [&](int i, int k) { return __ldg(gE + k + i * n); },
+          [&](int k, int j) { return P[k + j * n]; },
+          [](int, int) { return 0.0; },
+          [&](int i, int j, double v) { if (j <= n) X1[i + j * n] = v; else Pxt[i + (j - n - 1) * n] = -v; });
+    else
     mma_gemm<n, na, n, NW>(warp, lane,
         [&](int i, int k) { return Einv[k + i * n]; },
         [&](int k, int j) { return P[k + j * n]; },
@@ -317,6 +341,15 @@ sweep_kernel(const DevParams p) {
     PH(1);
     // (2) Ptilde = X1 * Einv (lower triangle kept, mirrored); ||Ptilde||_F^2 on the fly  (:179-180)
     double fro = 0.0;
+    if constexpr (EG)      // transposed: Ptilde^T = Einv^T X1^T, whose upper triangle is the reference's lower one
+      strip_gemm<n, n, n, NW, true, false>(warp, lane,
+          [&](int i, int k) { return __ldg(gE + k + i * n); },
+          [&](int k, int j) { return X1[j + k * n]; },
+          [](int, int) { return 0.0; },
+          [&](int i, int j, double v) {
+            if (i <= j) { P[j + i * n] = v; P[i + j * n] = v; fro = fma(i == j ? v : 2.0 * v, v, fro); }
+          });
+    else
     mma_gemm_lower<n, n, NW>(warp, lane,
         [&](int i, int k) { return X1[i + k * n]; },
         [&](int k, int j) { return Einv[k + j * n]; },
@@ -574,6 +607,24 @@ sweep_kernel(const DevParams p) {
     // (10) [Afb | yff] = -Einv [A_pre | tv]                                              (:243-245)
     //      rows n..n+h-1 of the same product: Pxttilde^T [A_pre | tv | Yth_pre] = Vxt^T [Afb | yff | Yth]
     //      (Vxt^T Einv^{-1}... = Pxttilde^T exactly), the three Vxt-contractions of :286-298
+    if constexpr (EG)
+      strip_gemm<n + h, na, n, NW, true, false>(warp, lane,
+        [&](int i, int k) { return i < n ? -__ldg(gE + i + k * n) : Pxt[k + (i - n) * n]; },
+        [&](int k, int j) { return P[k + j * n]; },
+        [](int, int) { return 0.0; },
+        [&](int i, int j, double v) {
+          if (i < n) {
+            if (j < n) gfbg[(rA + i) * n + j] = v;
+            else if (j == n) ff[rA + i] = v;
+            else fth[(rA + i) * h + (j - n - 1)] = v;
+          } else {
+            const int a = i - n;
+            if (j < n) Vxn[j + a * n] = v;
+            else if (j == n) vtp[a] = v;
+            else Vttp[a + (j - n - 1) * h] = v;
+          }
+        });
+    else
     mma_gemm<n + h, na, n, NW>(warp, lane,
         [&](int i, int k) { return i < n ? -Einv[i + k * n] : Pxt[k + (i - n) * n]; },
         [&](int k, int j) { return P[k + j * n]; },
@@ -644,6 +695,7 @@ sweep_kernel(const DevParams p) {
   PH(14);
 
   // ---- initial stage: BK of [Pmat0 G0^T; G0 -mudyn I]        (proximal-riccati.hxx:44-62) ----
+  if constexpr (EG) { ksub = BtV; kpiv = reinterpret_cast<int *>(BtV + PL::KS); }   // P is live here, BtV is dead
   if constexpr (!LEG) {
     if (tid == 0) tma_store_wait_read();
     cta_sync<NT>();
@@ -784,9 +836,10 @@ sweep_kernel(const DevParams p) {
 }
 
 // ---- host side -----------------------------------------------------------------------------
-template <int NX, int NU, int NC, int NTH, int NW>
+template <int NX, int NU, int NC, int NTH, int NW, bool EG = false>
 static int launch_fast_t(const DevParams &p, cudaStream_t st) {
-  using PL = FastPlan<NX, NU, NC, NTH>;
+  using PL = FastPlan<NX, NU, NC, NTH, NTH, EG>;
+  static_assert(!EG || PL::BtV + PL::KS + (PL::KS + 1) / 2 + 2 <= PL::kkt, "EG: BK scratch of the initial stage must fit in BtV");
   static_assert(PL::kstride >= 0, "");
   if (p.KL.stride != PL::kstride || p.GL.stride != PL::gstride || p.KL.E != PL::oE || p.KL.f != PL::of)
     return -3;   // layout mismatch: never expected, fall back to the generic kernel
@@ -813,7 +866,7 @@ static int launch_fast_t(const DevParams &p, cudaStream_t st) {
     launched++;
   }
   const size_t smem = (size_t)PL::total * sizeof(double);
-  auto ks = p.phase_cycles ? sweep_kernel<NX, NU, NC, NTH, NW, true> : sweep_kernel<NX, NU, NC, NTH, NW, false>;
+  auto ks = p.phase_cycles ? sweep_kernel<NX, NU, NC, NTH, NW, true, false, EG> : sweep_kernel<NX, NU, NC, NTH, NW, false, false, EG>;
   if (cudaFuncSetAttribute(ks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -2;
   ks<<<p.batch, 32 * NW, smem, st>>>(p);
   if (cudaGetLastError() != cudaSuccess) return -2;
@@ -864,7 +917,10 @@ int launch_backward_fast(const DevParams &p, const int *h_nu_t, const int *h_nc_
     static const int nw = getenv("GARB200_NW36") ? atoi(getenv("GARB200_NW36")) : 5;   // tuning knob
     return nw == 4 ? launch_fast_t<36, 12, 0, 0, 4>(p, st) : launch_fast_t<36, 12, 0, 0, 5>(p, st);
   }
-  if (p.nx == 36 && p.nu == 12 && p.nc == 6 && p.nth == 4) return launch_fast_t<36, 12, 6, 4, 5>(p, st);   // C3
+  if (p.nx == 36 && p.nu == 12 && p.nc == 6 && p.nth == 4) {   // C3: E^{-1} from L2 -> 75 KB of shared memory, 3 CTAs per SM
+    static const bool eg = [] { const char *e = getenv("GARB200_C3_EG"); return !(e && e[0] == '0'); }();
+    return eg ? launch_fast_t<36, 12, 6, 4, 5, true>(p, st) : launch_fast_t<36, 12, 6, 4, 5, false>(p, st);
+  }
   if (big_path_available(p.nx, p.nu, p.nc, p.nth)) return launch_backward_big(p, st);                     // C5
   return -3;
 }
