@@ -66,6 +66,7 @@ bool fast_path_available(int nx, int nu, int nc, int nth, int num_legs);
 // streaming variant for records larger than shared memory (sweep_big.cu): -3 = no instantiation
 int launch_backward_big(const DevParams &p, cudaStream_t st);
 bool big_path_available(int nx, int nu, int nc, int nth);
+int launch_big_sweep_36(const DevParams &p, cudaStream_t st);
 int launch_forward(const DevParams &p, const double *d_theta, double *xs, double *us, double *vs,
                    double *lbdas, cudaStream_t st);
 int launch_condensed(const DevParams &p, cudaStream_t st);

@@ -74,7 +74,8 @@ template <int NX, int NU> struct BigPlan {
   static constexpr int Rqr = r2(kkt + sp * sp);         // [R | q | r] of the knot record
   static constexpr int fv = r2(Rqr + (oA - oR));        // f
   static constexpr int P = r2(fv + n);                  // n x na
-  static constexpr int G = r2(P + n * na);              // gains staging
+  static constexpr int K0max = (2 * n) * ((2 * n) | 1);  // overlay extent of the initial-stage KKT matrix
+  static constexpr int G = r2(P + n * na) > K0max ? r2(P + n * na) : r2(K0max);   // gains staging, behind the overlay
   static constexpr int KS = 2 * n + 8;
   static constexpr int ksub = r2(G + gpart);
   static constexpr int dinv = r2(ksub + KS);
@@ -83,15 +84,14 @@ template <int NX, int NU> struct BigPlan {
   static constexpr int ints = r2(atvx + n + m);
   static constexpr int bar = r2(ints + (KS + 1) / 2);
   static constexpr int total = bar + 2;
-  static constexpr int K0max = (2 * n) * ((2 * n) | 1);  // overlay extent of the initial-stage KKT matrix
   static_assert(K0max <= G, "initial-stage KKT overlay must end before the gains staging block");
   static_assert(n * ((2 * n) | 1) <= P, "columns < n of the overlay must end before the P block");
   static_assert(gpart >= r2(2 * n) + 4 * n + 4, "gains staging doubles as BK scratch");
   static_assert(total * 8 <= 227 * 1024, "shared-memory plan exceeds 227 KB");
 };
 
-template <int NX, int NU, int NW>
-__global__ void __launch_bounds__(32 * NW, 1) sweep_big_kernel(const DevParams p) {
+template <int NX, int NU, int NW, int MINB>
+__global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParams p) {
   extern __shared__ __align__(16) double sm[];
   using PL = BigPlan<NX, NU>;
   constexpr int n = NX, m = NU, s = NU, NT = 32 * NW, na = PL::na, sp = PL::sp;
@@ -472,11 +472,25 @@ static int launch_big_t(const DevParams &p, cudaStream_t st) {
     launched++;
   }
   const size_t smem = (size_t)PL::total * sizeof(double);
-  auto ks = sweep_big_kernel<NX, NU, NW>;
+  auto ks = sweep_big_kernel<NX, NU, NW, 1>;
   if (cudaFuncSetAttribute(ks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -2;
   ks<<<p.batch, 32 * NW, smem, st>>>(p);
   if (cudaGetLastError() != cudaSuccess) return -2;
   return launched + 1;
+}
+
+// The same streaming plan for nx = 36, nu = 12 (47.9 KB of shared memory, 4 CTAs x 5 warps per SM at 102
+// registers) — sweep only, the caller has run the E^{-1} pre-pass.
+int launch_big_sweep_36(const DevParams &p, cudaStream_t st) {
+  using PL = BigPlan<36, 12>;
+  if (p.KL.stride != PL::kstride || p.GL.stride != PL::gstride || p.KL.E != PL::oE || p.KL.f != PL::of ||
+      p.KL.A != PL::oA || p.KL.R != PL::oR || p.GL.fb != PL::gfb)
+    return -3;
+  const size_t smem = (size_t)PL::total * sizeof(double);
+  auto ks = sweep_big_kernel<36, 12, 5, 4>;
+  if (cudaFuncSetAttribute(ks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -2;
+  ks<<<p.batch, 32 * 5, smem, st>>>(p);
+  return cudaGetLastError() == cudaSuccess ? 1 : -2;
 }
 
 bool big_path_available(int nx, int nu, int nc, int nth) { return nx == 76 && nu == 32 && nc == 0 && nth == 0; }

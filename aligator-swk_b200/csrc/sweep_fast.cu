@@ -865,6 +865,13 @@ static int launch_fast_t(const DevParams &p, cudaStream_t st) {
     if (cudaGetLastError() != cudaSuccess) return -2;
     launched++;
   }
+  if constexpr (NX == 36 && NU == 12 && NC == 0 && NTH == 0) {
+    static const bool streamed = [] { const char *e = getenv("GARB200_C1_STREAM"); return e && e[0] == '1'; }();
+    if (streamed && !p.phase_cycles) {
+      const int rc = launch_big_sweep_36(p, st);
+      return rc < 0 ? rc : launched + rc;
+    }
+  }
   const size_t smem = (size_t)PL::total * sizeof(double);
   auto ks = p.phase_cycles ? sweep_kernel<NX, NU, NC, NTH, NW, true, false, EG> : sweep_kernel<NX, NU, NC, NTH, NW, false, false, EG>;
   if (cudaFuncSetAttribute(ks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -2;
@@ -892,10 +899,32 @@ static int launch_fast_legs(const DevParams &p, cudaStream_t st) {
   const size_t smc = (size_t)PLc::total * sizeof(double), sml = (size_t)PLl::total * sizeof(double);
   if (cudaFuncSetAttribute(kc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smc) != cudaSuccess) return -2;
   if (cudaFuncSetAttribute(kl, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sml) != cudaSuccess) return -2;
+  // The last leg is independent of the coupled legs (disjoint knots, gains and value slots): it runs on
+  // a side stream (one per device, created on first use) between two events, beside the coupled legs.
+  struct Side { cudaStream_t s = nullptr; cudaEvent_t e0 = nullptr, e1 = nullptr; bool ok = false; };
+  static Side side[16];
+  int dev = 0;
+  cudaGetDevice(&dev);
+  Side *sd = (dev >= 0 && dev < 16) ? &side[dev] : nullptr;
+  if (sd && !sd->s) {
+    sd->ok = cudaStreamCreateWithFlags(&sd->s, cudaStreamNonBlocking) == cudaSuccess &&
+             cudaEventCreateWithFlags(&sd->e0, cudaEventDisableTiming) == cudaSuccess &&
+             cudaEventCreateWithFlags(&sd->e1, cudaEventDisableTiming) == cudaSuccess;
+  }
+  const bool fork = sd && sd->ok && p.batch * (p.num_legs - 1) < 4 * 148;   // only worth it while the GPU is not full
+  if (fork) {
+    if (cudaEventRecord(sd->e0, st) != cudaSuccess || cudaStreamWaitEvent(sd->s, sd->e0, 0) != cudaSuccess) return -2;
+    kl<<<p.batch, 32 * NW, sml, sd->s>>>(p);
+    if (cudaGetLastError() != cudaSuccess || cudaEventRecord(sd->e1, sd->s) != cudaSuccess) return -2;
+  }
   kc<<<p.batch * (p.num_legs - 1), 32 * NW, smc, st>>>(p);
   if (cudaGetLastError() != cudaSuccess) return -2;
-  kl<<<p.batch, 32 * NW, sml, st>>>(p);
-  if (cudaGetLastError() != cudaSuccess) return -2;
+  if (fork) {
+    if (cudaStreamWaitEvent(st, sd->e1, 0) != cudaSuccess) return -2;
+  } else {
+    kl<<<p.batch, 32 * NW, sml, st>>>(p);
+    if (cudaGetLastError() != cudaSuccess) return -2;
+  }
   return 3;
 }
 

@@ -70,6 +70,11 @@ CASES = [
     (76, 32, 0, 0, 12, 3, 1e-11, "ref"),     # C5 shape (Talos walk): streaming sweep, sweep_big.cu
     (76, 32, 0, 0, 6, 2, 1e-8, "explicit"),
     (76, 32, 0, 0, 5, 2, 1e-2, "explicit_psd"),   # C5 shape, LDL^T (non-Neumann) path
+    (12, 4, 0, 0, 1, 3, 1e-11, "ref"),       # horizon 1 on every specialised sweep: one stage knot + terminal
+    (36, 12, 0, 0, 1, 2, 1e-11, "ref"),
+    (36, 12, 6, 4, 1, 2, 1e-9, "ref"),
+    (76, 32, 0, 0, 1, 2, 1e-11, "ref"),
+    (12, 4, 0, 0, 0, 2, 1e-11, "ref"),       # horizon 0 with a specialised shape: generic kernel (no stage knot)
 ]
 
 FAST_DIMS = ((12, 4, 0, 0), (36, 12, 0, 0), (36, 12, 6, 4), (76, 32, 0, 0))
