@@ -830,7 +830,15 @@ __device__ __forceinline__ bool gj_inverse_cta(int tid, const double *__restrict
   for (int e = tid; e < NP * LD; e += NT) M[e] = 0.0;
   for (int e = tid; e < 16 * (2 * NTL - NB); e += NT) sbinv[16 * NB + e] = 0.0;
   __syncthreads();
-  for (int e = tid; e < N * N; e += NT) M[(e % N) * LD + (e / N)] = Eg[e];
+  {   // transposing fill: a warp moves 4 rows x 8 columns at a time (32-byte runs of a column-major
+      // column in global memory, a 2-way instead of a 16-way bank conflict on the row-major store)
+    constexpr int RB = N / 4, CB = (N + 7) / 8;
+    const int r4 = lane & 3, c8 = lane >> 2;
+    for (int blk = warp; blk < RB * CB; blk += NWARP) {
+      const int row = (blk % RB) * 4 + r4, col = (blk / RB) * 8 + c8;
+      if (col < N) M[row * LD + col] = Eg[row + col * N];
+    }
+  }
   bool act[RPL];
 #pragma unroll
   for (int s = 0; s < RPL; s++) act[s] = lane + 32 * s < N;
