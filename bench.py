@@ -216,29 +216,39 @@ def gpu_arm(args, w, rank, world, local_rank):
     # trajectory gather to rank 0 (north_star: a single NCCL gather, no collective inside the
     # sweep): the forward kernel writes straight into the send buffer.
     send = recv = None
-    out_ptrs = {}
+    out_ptrs = [{}, {}]
     if dist is not None:
         sizes = sharding.trajectory_sizes(B, T, nx, nu, nc)
-        send = torch.empty(sum(sizes), dtype=torch.float64, device="cuda")
-        recv = [torch.empty_like(send) for _ in range(world)] if rank == 0 else None
-        for name, view in zip(("d_xs", "d_us", "d_vs", "d_lbdas"), sharding.carve(send, sizes)):
-            out_ptrs[name] = view.data_ptr()
+        # two send buffers: the forward rollout of step i+1 writes the other one while step i's is in flight
+        send = [torch.empty(sum(sizes), dtype=torch.float64, device="cuda") for _ in range(2)]
+        recv = [torch.empty_like(send[0]) for _ in range(world)] if rank == 0 else None
+        for k in range(2):
+            for name, view in zip(("d_xs", "d_us", "d_vs", "d_lbdas"), sharding.carve(send[k], sizes)):
+                out_ptrs[k][name] = view.data_ptr()
 
-    # The gather of step i runs on a side stream and overlaps the backward sweep of step i+1;
-    # the next forward (which overwrites the send buffer) waits for it.
+    # The gather of step i runs on a side stream and overlaps the backward sweep AND the forward rollout
+    # of step i+1 (double-buffered send buffer); a forward only waits for the gather that last read its buffer.
     side = torch.cuda.Stream() if dist is not None else None
+    gathered = [None, None]
+    stepno = [0]
 
     def step_device():
+        k = stepno[0] & 1
         s.backward(MU, MU)
-        if side is not None:
-            torch.cuda.current_stream().wait_stream(side)
-        s.forward_device(d_theta=theta_d, **out_ptrs)
+        if side is not None and gathered[k] is not None:
+            torch.cuda.current_stream().wait_event(gathered[k])
+        s.forward_device(d_theta=theta_d, **out_ptrs[k])
 
     def gather():
+        k = stepno[0] & 1
+        stepno[0] += 1
         if dist is not None:
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
-                sharding.gather_to_root(dist, send, rank, world, recv)
+                sharding.gather_to_root(dist, send[k], rank, world, recv)
+                ev = torch.cuda.Event()
+                ev.record(side)
+                gathered[k] = ev
 
     def drain():
         if side is not None:
