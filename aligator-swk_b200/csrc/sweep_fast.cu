@@ -19,8 +19,8 @@ namespace garb200 {
 // ---- pre-pass: batched inverse of E ------------------------------------------------------
 // One matrix per LPM lanes (two 12x12 matrices or one 36x36 matrix per warp), the whole matrix
 // in registers; E is read once from HBM and Einv written once (2 n^2 doubles of traffic).
-template <int N, int WPB>
-__global__ void __launch_bounds__(32 * WPB) einv_kernel(const DevParams p) {
+template <int N, int WPB, int MINB = 1>
+__global__ void __launch_bounds__(32 * WPB, MINB) einv_kernel(const DevParams p) {
   using GS = GjShape<N>;
   constexpr int MPW = GS::MPW, LPM = GS::LPM, NP = (N + 1) & ~1;
   __shared__ __align__(16) double s_row[WPB * MPW][NP];
@@ -860,7 +860,12 @@ static int launch_fast_t(const DevParams &p, cudaStream_t st) {
       }
       else einv_kernel<NX, WPB><<<(unsigned)((total + MPB - 1) / MPB), 32 * WPB, 0, st>>>(p);
     } else {
-      einv_kernel<NX, WPB><<<(unsigned)((total + MPB - 1) / MPB), 32 * WPB, 0, st>>>(p);
+      // small matrices: the register cap trades a few spilled bytes for 24 / 32 resident warps per SM
+      static const int minb = [] { const char *e = getenv("GARB200_EINV_MINB"); return e ? atoi(e) : 6; }();
+      const unsigned grid = (unsigned)((total + MPB - 1) / MPB);
+      if (minb >= 8) einv_kernel<NX, WPB, 8><<<grid, 32 * WPB, 0, st>>>(p);
+      else if (minb >= 6) einv_kernel<NX, WPB, 6><<<grid, 32 * WPB, 0, st>>>(p);
+      else einv_kernel<NX, WPB, 1><<<grid, 32 * WPB, 0, st>>>(p);
     }
     if (cudaGetLastError() != cudaSuccess) return -2;
     launched++;
