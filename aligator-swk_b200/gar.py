@@ -238,6 +238,22 @@ class ProximalRiccatiSolver(_GpuSolver):
         return self._solver.get_initial(0)[3]
 
 
+class RiccatiSolverDense(ProximalRiccatiSolver):
+    """dense-riccati.hpp:28-58 — same constructor and virtuals.  The reference's dense solver factors
+    the (nu + nc + 2 nx)^2 stage KKT matrix per knot (dense-kernel.hpp:56-212) and returns the solution
+    the proximal sweep returns; on the GPU both names run the same sweep.  One documented difference:
+    only the reference's DENSE kernel reads Gv (dense-kernel.hpp:76,134; the proximal kernel zeroes
+    that right-hand side, riccati-kernel.hxx:128,272), so a problem with a non-zero Gv is refused here
+    instead of being solved with the proximal semantics."""
+
+    def __init__(self, problem: LqrProblem, device=0):
+        for t, k in enumerate(problem.stages):
+            if np.any(np.asarray(k.Gv) != 0.0):
+                raise ValueError(f"RiccatiSolverDense (GPU): knot {t} has a non-zero Gv, which the proximal "
+                                 "sweep does not read (riccati-kernel.hxx:128,272)")
+        super().__init__(problem, device)
+
+
 class ParallelRiccatiSolver(_GpuSolver):
     """parallel-solver.hpp:24-108, GPU-backed: legs are CTAs instead of OpenMP threads."""
 

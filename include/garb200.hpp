@@ -228,6 +228,22 @@ public:
   Vec thHess() { Vec H((size_t)nth_ * nth_); detail::check(garb200_get_initial(h_, 0, nullptr, nullptr, nullptr, H.data()), "garb200_get_initial"); return H; }
 };
 
+/// dense-riccati.hpp:28-58 — same constructor and virtuals; on the GPU it runs the proximal sweep (the two
+/// reference solvers return the same solution).  Only the reference's dense kernel reads Gv
+/// (dense-kernel.hpp:76,134 vs riccati-kernel.hxx:128,272): a non-zero Gv is refused.
+class RiccatiSolverDense : public ProximalRiccatiSolver {
+public:
+  explicit RiccatiSolverDense(const LqrProblem &problem, int device = 0) : ProximalRiccatiSolver(check_gv(problem), device) {}
+
+private:
+  static const LqrProblem &check_gv(const LqrProblem &p) {
+    for (const auto &k : p.stages)
+      for (double v : k.Gv.v)
+        if (v != 0.0) throw std::domain_error("RiccatiSolverDense (GPU): non-zero Gv is not read by the proximal sweep");
+    return p;
+  }
+};
+
 /// parallel-solver.hpp:24-108 — legs are CTAs instead of OpenMP threads.
 class ParallelRiccatiSolver : public detail::GpuSolver {
 public:

@@ -118,6 +118,24 @@ int main() {
     try { ParallelRiccatiSolver bad(prob, 1); } catch (const std::runtime_error &) { threw = true; }
     CHECK(threw, "num_threads < 2 must throw (parallel-solver.hxx:25-29)");
   }
+  { // random_long_problem, dense solver (riccati.cpp:143-157): same API, KKT <= 1e-9, same solution as the proximal one
+    Vec x0(36); for (auto &x : x0) x = nrm(rng);
+    LqrProblem prob = generate_problem(x0, 100, 36, 12);
+    ProximalRiccatiSolver prox(prob);
+    RiccatiSolverDense dense(prob);
+    prox.backward(1e-14, 1e-14); dense.backward(1e-14, 1e-14);
+    auto [xs, us, vs, lbdas] = lqrInitializeSolution(prob);
+    auto [xd, ud, vd, ld] = lqrInitializeSolution(prob);
+    prox.forward(xs, us, vs, lbdas); dense.forward(xd, ud, vd, ld);
+    CHECK(maxabs(lqrComputeKktError(prob, xd, ud, vd, ld, 0.0, 0.0)) <= 1e-9, "dense KKT");
+    CHECK(infdiff(xs, xd) <= 1e-10 && infdiff(us, ud) <= 1e-10, "dense != proximal");
+    Vec x4(4, 1.0);
+    LqrProblem pg = generate_problem(x4, 3, 4, 2, 1);
+    bool threw = false;
+    pg.stages[0].Gv = Mat(1, 1); pg.stages[0].Gv(0, 0) = 1.0;
+    try { RiccatiSolverDense bad(pg); } catch (const std::domain_error &) { threw = true; }
+    CHECK(threw, "non-zero Gv must be refused by the GPU dense solver");
+  }
   printf(fails ? "%d FAILURES\n" : "all C++ mirror tests passed\n", fails);
   return fails ? 1 : 0;
 }

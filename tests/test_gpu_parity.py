@@ -199,6 +199,26 @@ def test_gar_mirror_api(capi, oracle):
     assert relerr(np.array(xs2), ref["xs"]) < RTOL
 
 
+def test_gar_mirror_dense_solver(capi, oracle):
+    """RiccatiSolverDense (dense-riccati.hpp:28-58) through the host mirror: same API, same solution as
+    the proximal solver (tests/gar/riccati.cpp:143-157), non-zero Gv refused."""
+    from aligator_swk_b200 import gar
+    from test_oracle import short_horz_pb
+    prob = short_horz_pb()
+    dense = gar.RiccatiSolverDense(prob)
+    assert dense.backward(1e-14, 1e-14)
+    xs, us, vs, lbdas = gar.lqrInitializeSolution(prob)
+    assert dense.forward(xs, us, vs, lbdas)
+    assert gar.lqrComputeKktError(prob, xs, us, vs, lbdas, 0.0, 0.0).max() <= 1e-9
+    ref = oracle.prox_solve(prob.pack(), 1e-14, 1e-14)
+    assert relerr(np.array(xs), ref["xs"]) < RTOL
+    prob.stages[0].addParameterization(1)
+    if prob.stages[0].nc:
+        prob.stages[0].Gv[:] = 1.0
+        with pytest.raises(ValueError):
+            gar.RiccatiSolverDense(prob)
+
+
 def test_error_conventions(capi):
     with pytest.raises(capi.GarB200Error):
         capi.Solver(4, 2, horizon=5, nc0=6)          # nc0 > nx
