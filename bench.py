@@ -438,6 +438,63 @@ def e2e_run(torch, capi, s_dev, w, K, W, dist, world, theta):
     return r
 
 
+def horizon_sweep(args):
+    """The reference's own benchmark (bench/gar-riccati.cpp:18-31,62-68): ONE random problem nx=36 nu=12,
+    horizons 16 ... 1024 (+ T = 100, tests/gar/riccati.cpp:113), backward + forward latency.  GPU: the serial
+    sweep and the parallel-in-time solver (legs ~ 0.83 sqrt(T), the latency optimum of leg time vs condensed solve), CUDA events, mean over repetitions;
+    CPU: the oracle port, serial (1 thread) and parallel legs (all host cores), next to it."""
+    import torch
+    import garb200_pkg
+    garb200_pkg.load()
+    from aligator_swk_b200 import capi
+    from aligator_swk_b200.synth import generate_problems
+    import pyoracle as po
+    po.build()
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except AttributeError:
+        cores = os.cpu_count() or 1
+    nx, nu = 36, 12
+    rows = []
+    # leg time ~ 2 x 13 us x T / J, condensed solve ~ 2 J x 19 us  ->  J* ~ 0.83 sqrt(T)
+    gpu_legs = lambda T: int(min(64, max(2, round(0.83 * T ** 0.5))))
+    for T in (16, 32, 64, 100, 128, 256, 512, 1024):
+        pp = generate_problems(1, T, nx, nu, 0, 0, seed=42)
+        row = {"horizon": T}
+        for name, legs in (("gpu_serial_ms", 0), ("gpu_legs_ms", gpu_legs(T))):
+            s = capi.Solver.for_problems(pp, num_legs=legs)
+            s.upload(pp)
+            for _ in range(3):
+                s.backward(MU, MU); s.forward_device()
+            torch.cuda.synchronize()
+            reps = 20
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                s.backward(MU, MU); s.forward_device()
+            e1.record(); torch.cuda.synchronize()
+            s.synchronize()
+            row[name] = e0.elapsed_time(e1) / reps
+            if legs:
+                row["legs"] = legs
+            row[name.replace("_ms", "_kkt")] = float(s.kkt_error(MU, MU).max())
+            s.close()
+        for name, legs, nthreads in (("cpu_serial_ms", 0, 1), ("cpu_legs_ms", min(cores, max(2, T // 4)), cores)):
+            secs, _ = po.bench(pp, MU, MU, num_legs=legs, reps=1, nthreads=nthreads)
+            reps = int(max(3, min(50, 2.0 / max(secs, 1e-6))))
+            secs, used = po.bench(pp, MU, MU, num_legs=legs, reps=reps, nthreads=nthreads)
+            row[name] = secs / reps * 1e3
+            if legs:
+                row["cpu_legs"], row["cpu_threads"] = legs, used
+        rows.append(row)
+        print("T=%4d  gpu serial %.3f ms  gpu %d legs %.3f ms | cpu serial %.2f ms  cpu %d legs %.2f ms" % (
+            T, row["gpu_serial_ms"], row["legs"], row["gpu_legs_ms"], row["cpu_serial_ms"], row["cpu_legs"], row["cpu_legs_ms"]),
+            file=sys.stderr, flush=True)
+    print(json.dumps({"metric": "single-problem backward+forward latency over horizons (bench/gar-riccati.cpp)", "unit": "ms",
+                      "higher_is_better": False, "nx": nx, "nu": nu, "mu": MU, "cpu_kind": "port", "cpu_cores": cores,
+                      "rows": rows}), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -448,7 +505,11 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="override the per-GPU batch")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU-port timing")
+    ap.add_argument("--horizons", action="store_true", help="the reference's own latency sweep over horizons (one GPU)")
     args = ap.parse_args()
+    if args.horizons:
+        horizon_sweep(args)
+        return
     w = dict(WORKLOADS[args.workload])
     if args.batch > 0:
         w["batch"] = args.batch
