@@ -90,7 +90,7 @@ template <int NX, int NU> struct BigPlan {
   static_assert(total * 8 <= 227 * 1024, "shared-memory plan exceeds 227 KB");
 };
 
-template <int NX, int NU, int NW, int MINB>
+template <int NX, int NU, int NW, int MINB, bool PROF = false>
 __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParams p) {
   extern __shared__ __align__(16) double sm[];
   using PL = BigPlan<NX, NU>;
@@ -109,6 +109,19 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
   int *kpiv = reinterpret_cast<int *>(sm + PL::ints);
   uint64_t *bar = reinterpret_cast<uint64_t *>(sm + PL::bar);
   int flags = 0;
+  // optional phase timers (GARB200_PHASE_TIMERS=1), same slots as sweep_fast.cu / tools/phase_timers.py;
+  // thread 0's view, and the instrumented build spills more: read the shares, not the absolute cycles
+  long long ph_acc[16], ph_last = 0;
+  if constexpr (PROF) {
+#pragma unroll
+    for (int i = 0; i < 16; i++) ph_acc[i] = 0;
+    ph_last = clock64();
+  }
+  auto PH = [&](int i) {
+    if constexpr (PROF) {
+      if (tid == 0) { const long long now = clock64(); ph_acc[i] += now - ph_last; ph_last = now; }
+    }
+  };
 
   if (tid == 0) { mbar_init(bar, 1); fence_mbar_init(); }
   for (int e = tid; e < PL::gpart; e += NT) Gs[e] = 0.0;
@@ -181,6 +194,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
       if (t > 0) prefetch_knot(t - 1);
       tma_store_wait_read();
     }
+    PH(0);
     // (1) [X1 | x1v] = Einv^T [P | pvec]          EinvP, -ptilde      (:175-178)
     strip_gemm<n, na, n, NW, true, false>(warp, lane,
         [&](int i, int k) { return __ldg(gE + k + i * n); },
@@ -188,6 +202,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
         [](int, int) { return 0.0; },
         [&](int i, int j, double v) { X1[i + j * n] = v; });
     cta_sync<NT>();
+    PH(1);
     // (2) Ptilde^T = Einv^T X1^T; the upper triangle of the transposed product IS the reference's
     //     lower triangle of Ptilde = X1 Einv, mirrored; ||Ptilde||_F^2 on the fly      (:179-180)
     double fro = 0.0;
@@ -207,6 +222,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
 #pragma unroll
     for (int w = 0; w < NW; w++) fro += red[w];
     const bool neumann = mudyn * sqrt(fro) <= 1e-9;     // see sweep_fast.cu
+    PH(2);
     // (3) w = ptilde + Ptilde f -> pv                                                   (:182-187)
     gemv4<n, n, NT>(tid, [&](int i, int j) { return P[i + j * n]; }, [&](int j) { return f[j]; },
                     [&](int i) { return -x1v[i]; }, [&](int i, double v) { pv[i] = v; });
@@ -217,6 +233,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
       }
     }
     cta_sync<NT>();
+    PH(3);
     // (4) [Vxx | vx] = Lambda^{-1} [Ptilde | w]                                      (:185-190)
     if (neumann) {
       strip_gemm<n, na, n, NW, false, false>(warp, lane,
@@ -239,6 +256,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
       for (int e = tid; e < n * n; e += NT) v[p.VL.Vxx + e] = P[e];
       for (int i = tid; i < n; i += NT) v[p.VL.vx + i] = pv[i];
     }
+    PH(5);
     // (5) [AtV ; BtV] = [A | B]^T [Vxx | vx]: rows < n -> X1 (+ A^T vx), rows >= n -> BtV (+ B^T vx)
     strip_gemm<n + m, na, n, NW, true, false>(warp, lane,
         [&](int i, int k) { return __ldg(gAB + k + i * n); },
@@ -249,6 +267,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
           else BtV[(i - n) + j * m] = v;
         });
     cta_sync<NT>();
+    PH(6);
     // (6) [Qhat | Shat]^T = [Q | S]^T + [A | B]^T (Vxx A),  Vxx A = AtV^T                (:195-199)
     //     (mirrored strip assignment: the warps that took two strips in (5) take one here)
     strip_gemm<n + m, n, n, NW, true, true>(warp, lane,
@@ -280,6 +299,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
     for (int i = tid; i < n; i += NT) qv[i] += atvx[i];                           // qhat
     build_rhs_K();
     cta_sync<NT>();
+    PH(7);
     // (7) reduced KKT system Rhat [K kff] = rhs: blocked LDL^T with inertia check, Bunch-Kaufman
     //     (bunchkaufman.hpp:20-167, 447-516) as the fallback                             (:202-228)
     {
@@ -299,6 +319,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
         cta_sync<NT>();
       }
     }
+    PH(9);
     // (8) lff = vx + BtV^T kff ; tv = f + B kff - mudyn lff -> pv slot                  (:231-236)
     for (int i = tid; i < n; i += NT) {
       double l = pv[i], tb = f[i];
@@ -355,6 +376,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
       }
     }
     cta_sync<NT>();
+    PH(10);
     // (10) [Afb | yff] = -Einv [A_pre | tv]                                              (:243-245)
     strip_gemm<n, na, n, NW, true, false>(warp, lane,
         [&](int i, int k) { return -__ldg(gE + i + k * n); },
@@ -365,17 +387,21 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
           else ff[rA + i] = v;
         });
     cta_sync<NT>();
+    PH(11);
     // (11) [Pmat | pvec] = [Qhat | qhat] + Shat [K | kff]                                 (:249-250)
     strip_gemm<n, na, s, NW, false, false>(warp, lane,
         [&](int i, int k) { return Sh[i + k * n]; },
         [&](int k, int j) { return j < n ? fb[k * n + j] : ff[k]; },
         [&](int i, int j) { return j < n ? Qh[i + j * n] : qv[i]; },
         [&](int i, int j, double v) { P[i + j * n] = v; });
+    PH(12);
     store_gains(t);
     store_value(t);
     fence_proxy_async();
     cta_sync<NT>();
+    PH(13);
   }
+  PH(14);
 
   // ---- initial stage: BK of [Pmat0 G0^T; G0 -mudyn I]        (proximal-riccati.hxx:44-62) ----
   {
@@ -445,6 +471,12 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
   }
   if (flags) atomicOr(reinterpret_cast<int *>(p.flags) + b, flags);
   if (tid == 0) tma_store_wait_all();
+  PH(15);
+  if constexpr (PROF) {
+    if (tid == 0 && p.phase_cycles)
+#pragma unroll
+      for (int i = 0; i < 16; i++) atomicAdd(reinterpret_cast<unsigned long long *>(p.phase_cycles) + i, (unsigned long long)ph_acc[i]);
+  }
 }
 
 template <int NX, int NU, int NW>
@@ -472,7 +504,7 @@ static int launch_big_t(const DevParams &p, cudaStream_t st) {
     launched++;
   }
   const size_t smem = (size_t)PL::total * sizeof(double);
-  auto ks = sweep_big_kernel<NX, NU, NW, 1>;
+  auto ks = p.phase_cycles ? sweep_big_kernel<NX, NU, NW, 1, true> : sweep_big_kernel<NX, NU, NW, 1, false>;
   if (cudaFuncSetAttribute(ks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -2;
   ks<<<p.batch, 32 * NW, smem, st>>>(p);
   if (cudaGetLastError() != cudaSuccess) return -2;
