@@ -389,13 +389,15 @@ sweep_kernel(const DevParams p) {
           [&](int i, int k) { return -mudyn * P[i + k * n]; },
           [&](int k, int j) { return P[k + j * n]; },
           [&](int i, int j) { return P[i + j * n]; },
-          [&](int i, int j, double v) { X1[i + j * n] = v; });
+          [&](int i, int j, double v) {                       // lower triangle kept and mirrored in the epilogue
+            if (j >= n || i >= j) X1[i + j * n] = v;
+            if (j < n && i > j) X1[j + i * n] = v;
+          });
       cta_sync<NT>();
       PH(4);
-      for (int e = tid; e < n * na; e += NT) {                // back into P, mirrored from the lower triangle
-        const int i = e % n, j = e / n;
-        P[e] = (j < n && i < j) ? X1[j + i * n] : X1[e];
-      }
+      static_assert((n * na) % 2 == 0, "vector copy");
+      for (int e = tid; e < n * na / 2; e += NT)              // back into P
+        reinterpret_cast<double2 *>(P)[e] = reinterpret_cast<const double2 *>(X1)[e];
     } else {
       if (!ldlt_solve_blocked<n, na, NT>(tid, X1, RhsColMajor<n>{P}, Gs, dinv)) flags |= GARB200_FLAG_LLT_NOT_PD;
       PH(4);
