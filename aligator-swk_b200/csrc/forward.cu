@@ -12,6 +12,7 @@
 // loads of knots t+1.. are in flight while knot t is applied; 4 threads share one row of
 // the row-major gain matrix (bank-conflict free for nx = 4 mod 16, e.g. 12, 36, 76).
 #include "device_linalg.cuh"
+#include <cstdlib>
 #include "kernels.cuh"
 
 namespace garb200 {
@@ -228,7 +229,9 @@ int launch_forward(const DevParams &p, const double *d_theta, double *xs, double
     if (rc != -3) return rc;
   }
   if (p.GL.stride * 8 <= 4096) return launch_forward_t<32, 4>(p, d_theta, xs, us, vs, lbdas, st);
-  if (forward_smem(p, 3) <= 100u * 1024u) return launch_forward_t<128, 3>(p, d_theta, xs, us, vs, lbdas, st);
+  static const int stages = [] { const char *e = getenv("GARB200_FWD_STAGES"); return e ? atoi(e) : 2; }();   // 2: more CTAs per SM beats a deeper ring (c1b 5.7 -> 6.6 TB/s, c3 4.1 -> 5.5 TB/s)
+  if (stages == 4 && forward_smem(p, 4) <= 110u * 1024u) return launch_forward_t<128, 4>(p, d_theta, xs, us, vs, lbdas, st);
+  if (stages >= 3 && forward_smem(p, 3) <= 100u * 1024u) return launch_forward_t<128, 3>(p, d_theta, xs, us, vs, lbdas, st);
   return launch_forward_t<128, 2>(p, d_theta, xs, us, vs, lbdas, st);
 }
 
