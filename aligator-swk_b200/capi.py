@@ -17,6 +17,7 @@ _LIB = None
 OK, ERR_INVALID, ERR_CUDA, ERR_NUMERIC, ERR_STATE = 0, 1, 2, 3, 4
 STORE_ALL_VALUES = 1
 FORCE_GENERIC = 2
+PHASE_TIMERS = 4
 
 _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int)
@@ -53,7 +54,7 @@ SYMBOLS = [
     "garb200_get_refinement_steps", "garb200_collapse_feedback", "garb200_cycle_append",
     "garb200_kkt_error", "garb200_upload_trajectory", "garb200_kernel_launches", "garb200_last_timings",
     "garb200_fp64_peak", "garb200_timing_log_start", "garb200_timing_log_read",
-    "garb200_used_fast_path", "garb200_phase_cycles",
+    "garb200_used_fast_path", "garb200_phase_cycles", "garb200_set_tuning",
 ]
 
 
@@ -77,6 +78,7 @@ def lib():
             getattr(L, name).argtypes = [C.c_void_p] * 6 if name == "garb200_forward_device" else [C.c_void_p] * 6
         L.garb200_upload_packed.argtypes = [C.c_void_p] * 4
         L.garb200_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+        L.garb200_set_tuning.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
         L.garb200_synchronize.argtypes = [C.c_void_p]
         L.garb200_destroy.argtypes = [C.c_void_p]
         L.garb200_get_gains.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -180,6 +182,11 @@ class Solver:
             pass
 
     # ---- plumbing
+    def set_tuning(self, **knobs):
+        """diagnostic launcher knobs (garb200_set_tuning), e.g. ``set_tuning(group=1)``"""
+        for k, v in knobs.items():
+            check(lib().garb200_set_tuning(self._h, k.encode(), int(v)))
+
     def set_stream(self, stream_ptr):
         check(lib().garb200_set_stream(self._h, C.c_void_p(int(stream_ptr))))
 

@@ -5,7 +5,6 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
-#include <cstdlib>
 #include <string>
 #include <vector>
 #include "kernels.cuh"
@@ -40,11 +39,33 @@ struct garb200_solver {
   std::vector<cudaEvent_t> tlog;   // timing log: 4 events per logged solve (bwd begin/end, fwd begin/end)
   int tlog_cap = 0, tlog_bwd = 0, tlog_fwd = 0;
   size_t knots_doubles = 0;
+  // staging bookkeeping: only knots staged since the last commit are uploaded (a knot installed
+  // another way — upload_packed, generate, device producers, cycle_append — is never overwritten)
+  std::vector<uint8_t> dirty;    // [batch][T+1] physical knot slots staged since the last commit
+  std::vector<uint8_t> dirty0;   // [batch] initial condition staged since the last commit
+  bool any_dirty = false;
+  cudaEvent_t ev_h2d = nullptr;  // recorded after every async H2D that reads a pinned staging buffer
+  bool h2d_pending = false;
+  double *h_gains = nullptr;     // pinned mirror of the gains records (getFeedback/getFeedforward cache)
+  bool gains_fresh = false;
+  cudaStream_t side = nullptr;   // leg mode: the last leg runs beside the coupled legs
+  cudaEvent_t side_e0 = nullptr, side_e1 = nullptr;
   int nblk = 0;                  // blocks of the condensed system (2 * legs)
   size_t csys_len = 0;           // nc0 + (nblk-1) nx
 };
 
 static const size_t kMaxPinnedStage = (size_t)1 << 30;  // 1 GiB
+static const size_t kMaxPinnedGains = (size_t)256 << 20; // 256 MiB
+
+// The pinned staging buffers may still be the source of an in-flight H2D copy (commit / cycle_append
+// are asynchronous): wait for it before the host overwrites them.
+static int wait_staging(garb200_solver *s) {
+  if (s->h2d_pending) {
+    if (cudaEventSynchronize(s->ev_h2d) != cudaSuccess) { g_err = "cudaEventSynchronize (staging) failed"; return GARB200_ERR_CUDA; }
+    s->h2d_pending = false;
+  }
+  return GARB200_OK;
+}
 
 template <class T> static int dmalloc(garb200_solver *s, T **ptr, size_t count) {
   *ptr = nullptr;
@@ -84,6 +105,11 @@ void garb200_destroy(garb200_solver *s) {
   if (s->h_g0) cudaFreeHost(s->h_g0);
   if (s->h_scratch) cudaFreeHost(s->h_scratch);
   if (s->h_cycle) cudaFreeHost(s->h_cycle);
+  if (s->h_gains) cudaFreeHost(s->h_gains);
+  if (s->ev_h2d) cudaEventDestroy(s->ev_h2d);
+  if (s->side) cudaStreamDestroy(s->side);
+  if (s->side_e0) cudaEventDestroy(s->side_e0);
+  if (s->side_e1) cudaEventDestroy(s->side_e1);
   for (auto &e : s->ev) if (e) cudaEventDestroy(e);
   for (auto &e : s->tlog) if (e) cudaEventDestroy(e);
   delete s;
@@ -176,7 +202,7 @@ int garb200_create(const garb200_config *cfg, garb200_solver **out) {
   TRYB(dmalloc(s, &p.refine_steps, B));
   TRYB(dmalloc(s, &s->d_kkt_out, B * 3));
   p.phase_cycles = nullptr;
-  if (getenv("GARB200_PHASE_TIMERS")) { TRYB(dmalloc(s, &p.phase_cycles, 16)); cudaMemset(p.phase_cycles, 0, 16 * sizeof(long long)); }
+  if (c.flags & GARB200_PHASE_TIMERS) { TRYB(dmalloc(s, &p.phase_cycles, 16)); cudaMemset(p.phase_cycles, 0, 16 * sizeof(long long)); }
   cudaMemset(p.flags, 0, B * sizeof(int32_t));
   cudaMemset(p.refine_steps, 0, B * sizeof(int32_t));
   cudaMemset(p.values, 0, B * p.nslots * p.VL.stride * sizeof(double));
@@ -212,8 +238,39 @@ int garb200_create(const garb200_config *cfg, garb200_solver **out) {
       return bail(fail(GARB200_ERR_CUDA, "cudaMallocHost (cycle) failed"));
   for (auto &e : s->ev)
     if (cudaEventCreate(&e) != cudaSuccess) return bail(fail(GARB200_ERR_CUDA, "cudaEventCreate failed"));
+  if (cudaEventCreateWithFlags(&s->ev_h2d, cudaEventDisableTiming) != cudaSuccess)
+    return bail(fail(GARB200_ERR_CUDA, "cudaEventCreate failed"));
+  if (s->h_stage) { s->dirty.assign(B * (T + 1), 0); s->dirty0.assign(B, 0); }
+  {
+    const size_t gbytes = B * (T + 1) * p.GL.stride * sizeof(double);
+    if (gbytes <= kMaxPinnedGains && cudaMallocHost(&s->h_gains, gbytes) != cudaSuccess)
+      return bail(fail(GARB200_ERR_CUDA, "cudaMallocHost (gains mirror) failed"));
+  }
+  if (legs) {   // side stream of the last leg: created here, never lazily (no allocation after create)
+    if (cudaStreamCreateWithFlags(&s->side, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&s->side_e0, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&s->side_e1, cudaEventDisableTiming) != cudaSuccess)
+      return bail(fail(GARB200_ERR_CUDA, "side stream creation failed"));
+    p.side_stream = s->side; p.side_e0 = s->side_e0; p.side_e1 = s->side_e1;
+  }
 #undef TRYB
   *out = s;
+  return GARB200_OK;
+}
+
+int garb200_set_tuning(garb200_solver *s, const char *name, int value) {
+  if (!s || !name) return fail(GARB200_ERR_INVALID, "null argument");
+  Tune &t = s->p.tune;
+  const std::string k(name);
+  if (k == "group") t.group = value;
+  else if (k == "einv_mode") t.einv_mode = value;
+  else if (k == "einv_minb") t.einv_minb = value;
+  else if (k == "fwd_stages") t.fwd_stages = value;
+  else if (k == "condensed") t.condensed = value;
+  else if (k == "c3_eg") t.c3_eg = value;
+  else if (k == "legs_generic") t.legs_generic = value;
+  else if (k == "explicit_dyn") t.explicit_dyn = value;
+  else return fail(GARB200_ERR_INVALID, "unknown tuning knob: " + k);
   return GARB200_OK;
 }
 
@@ -313,7 +370,10 @@ int garb200_stage_knot(garb200_solver *s, int problem, int t, const garb200_knot
   if (!s->h_stage) return fail(GARB200_ERR_STATE, "batch too large for pinned staging: use garb200_upload_packed");
   if (problem < 0 || problem >= p.batch || t < 0 || t > p.T) return fail(GARB200_ERR_INVALID, "index out of range");
   if (k->nu != s->nu_t[t] || k->nc != s->nc_t[t]) return fail(GARB200_ERR_INVALID, "knot dims differ from the solver's");
-  pack_knot(p.KL, *k, s->h_stage + ((size_t)problem * (p.T + 1) + phys_t(p, t)) * p.KL.stride);
+  TRY(wait_staging(s));
+  const size_t slot = (size_t)problem * (p.T + 1) + phys_t(p, t);
+  pack_knot(p.KL, *k, s->h_stage + slot * p.KL.stride);
+  s->dirty[slot] = 1; s->any_dirty = true;
   return GARB200_OK;
 }
 
@@ -322,8 +382,10 @@ int garb200_stage_initial(garb200_solver *s, int problem, const double *G0, cons
   const DevParams &p = s->p;
   if (!s->h_stage) return fail(GARB200_ERR_STATE, "batch too large for pinned staging");
   if (problem < 0 || problem >= p.batch) return fail(GARB200_ERR_INVALID, "index out of range");
+  TRY(wait_staging(s));
   pack_block(s->h_G0 + (size_t)problem * p.nc0 * p.nx, G0, p.nc0 * p.nx);
   pack_block(s->h_g0 + (size_t)problem * p.nc0, g0, p.nc0);
+  s->dirty0[problem] = 1; s->any_dirty = true;
   return GARB200_OK;
 }
 
@@ -332,10 +394,30 @@ int garb200_commit(garb200_solver *s) {
   if (!s->h_stage) return fail(GARB200_ERR_STATE, "batch too large for pinned staging");
   CK(cudaSetDevice(s->cfg.device));
   const DevParams &p = s->p;
-  const size_t B = p.batch, n = p.nx;
-  CK(cudaMemcpyAsync(p.knots, s->h_stage, s->knots_doubles * sizeof(double), cudaMemcpyHostToDevice, s->stream));
-  CK(cudaMemcpyAsync(p.G0, s->h_G0, B * p.nc0 * n * sizeof(double), cudaMemcpyHostToDevice, s->stream));
-  CK(cudaMemcpyAsync(p.g0, s->h_g0, B * p.nc0 * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  const size_t B = p.batch, n = p.nx, ks = p.KL.stride, total = B * (p.T + 1);
+  if (s->any_dirty) {
+    // contiguous runs of staged knot slots -> one copy each (a fully staged batch is ONE copy)
+    for (size_t i = 0; i < total;) {
+      if (!s->dirty[i]) { i++; continue; }
+      size_t j = i;
+      while (j < total && s->dirty[j]) s->dirty[j++] = 0;
+      CK(cudaMemcpyAsync(p.knots + i * ks, s->h_stage + i * ks, (j - i) * ks * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+      i = j;
+    }
+    for (size_t i = 0; i < B;) {
+      if (!s->dirty0[i]) { i++; continue; }
+      size_t j = i;
+      while (j < B && s->dirty0[j]) s->dirty0[j++] = 0;
+      if (p.nc0 > 0) {
+        CK(cudaMemcpyAsync(p.G0 + i * p.nc0 * n, s->h_G0 + i * p.nc0 * n, (j - i) * p.nc0 * n * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+        CK(cudaMemcpyAsync(p.g0 + i * p.nc0, s->h_g0 + i * p.nc0, (j - i) * p.nc0 * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+      }
+      i = j;
+    }
+    CK(cudaEventRecord(s->ev_h2d, s->stream));
+    s->h2d_pending = true;
+    s->any_dirty = false;
+  }
   s->has_problem = true;
   return GARB200_OK;
 }
@@ -399,6 +481,7 @@ int garb200_backward(garb200_solver *s, double mudyn, double mueq) {
   if (logb) { CK(cudaEventRecord(s->tlog[4 * s->tlog_bwd + 1], s->stream)); s->tlog_bwd++; }
   s->did_backward = true;
   s->did_forward = false;
+  s->gains_fresh = false;
   return GARB200_OK;
 }
 
@@ -466,12 +549,24 @@ int garb200_get_gains(garb200_solver *s, int problem, int t, double *ff, double 
   if (!s->did_backward) return fail(GARB200_ERR_STATE, "no factorization yet");
   if (problem < 0 || problem >= p.batch || t < 0 || t > p.T) return fail(GARB200_ERR_INVALID, "index out of range");
   CK(cudaSetDevice(s->cfg.device));
-  const double *rec = p.gains + ((size_t)problem * (p.T + 1) + phys_t(p, t)) * p.GL.stride;
-  TRY(fetch(s, s->h_scratch, rec, p.GL.stride));
+  // updateGains() reads every knot of a problem right after backward (solver-proxddp.hxx:316-334): the
+  // first read after a factorization mirrors ALL gains records in one bulk D2H, the others are memcpys
+  const size_t slot = (size_t)problem * (p.T + 1) + phys_t(p, t);
+  const double *rec_h;
+  if (s->h_gains) {
+    if (!s->gains_fresh) {
+      TRY(fetch(s, s->h_gains, p.gains, (size_t)p.batch * (p.T + 1) * p.GL.stride));
+      s->gains_fresh = true;
+    }
+    rec_h = s->h_gains + slot * p.GL.stride;
+  } else {
+    TRY(fetch(s, s->h_scratch, p.gains + slot * p.GL.stride, p.GL.stride));
+    rec_h = s->h_scratch;
+  }
   const int nr = s->nu_t[t] + s->nc_t[t] + 2 * p.nx;
-  if (ff) memcpy(ff, s->h_scratch + p.GL.ff, nr * sizeof(double));
-  if (fb) memcpy(fb, s->h_scratch + p.GL.fb, (size_t)nr * p.nx * sizeof(double));
-  if (fth && p.GL.nth) memcpy(fth, s->h_scratch + p.GL.fth, (size_t)nr * p.GL.nth * sizeof(double));
+  if (ff) memcpy(ff, rec_h + p.GL.ff, nr * sizeof(double));
+  if (fb) memcpy(fb, rec_h + p.GL.fb, (size_t)nr * p.nx * sizeof(double));
+  if (fth && p.GL.nth) memcpy(fth, rec_h + p.GL.fth, (size_t)nr * p.GL.nth * sizeof(double));
   return GARB200_OK;
 }
 
@@ -549,6 +644,7 @@ int garb200_collapse_feedback(garb200_solver *s) {
   const int rc = launch_collapse(s->p, s->stream);
   if (rc < 0) return fail(GARB200_ERR_CUDA, "collapse launch failed");
   s->launches += rc;
+  s->gains_fresh = false;
   return GARB200_OK;
 }
 
@@ -565,15 +661,26 @@ int garb200_cycle_append(garb200_solver *s, const garb200_knot_view *knots, int 
   for (int b = 0; b < p.batch; b++) {
     const garb200_knot_view &k = shared ? knots[0] : knots[b];
     if (k.nu != s->nu_t[0] || k.nc != s->nc_t[0]) return fail(GARB200_ERR_INVALID, "knot dims differ from the solver's");
-    pack_knot(p.KL, k, s->h_cycle + (size_t)b * p.KL.stride);
   }
-  CK(cudaStreamSynchronize(s->stream));         // nothing in flight still reads the old offset
+  CK(cudaStreamSynchronize(s->stream));         // nothing in flight still reads the old offset or h_cycle
+  s->h2d_pending = false;
   p.shift = (p.shift + 1) % p.T;                // rotate_vec_left(datas, 0, 1)  (mpc-util.hpp:17-22)
   const int slot = phys_t(p, p.T - 1);
+  for (int b = 0; b < p.batch; b++) {
+    const garb200_knot_view &k = shared ? knots[0] : knots[b];
+    pack_knot(p.KL, k, s->h_cycle + (size_t)b * p.KL.stride);
+    if (s->h_stage) {   // keep the staging mirror coherent: the appended knot is already on the device
+      const size_t gs = (size_t)b * (p.T + 1) + slot;
+      memcpy(s->h_stage + gs * p.KL.stride, s->h_cycle + (size_t)b * p.KL.stride, p.KL.stride * sizeof(double));
+      s->dirty[gs] = 0;
+    }
+  }
   const size_t pitch_k = (size_t)(p.T + 1) * p.KL.stride * sizeof(double);
   CK(cudaMemcpy2DAsync(p.knots + (size_t)slot * p.KL.stride, pitch_k, s->h_cycle,
                        p.KL.stride * sizeof(double), p.KL.stride * sizeof(double), p.batch,
                        cudaMemcpyHostToDevice, s->stream));
+  CK(cudaEventRecord(s->ev_h2d, s->stream));
+  s->h2d_pending = true;
   // fresh StageFactor at N-1, kkt0 / thGrad / thHess reset (proximal-riccati.hxx:83-87)
   const size_t pitch_g = (size_t)(p.T + 1) * p.GL.stride * sizeof(double);
   CK(cudaMemset2DAsync(p.gains + (size_t)slot * p.GL.stride, pitch_g, 0, p.GL.stride * sizeof(double), p.batch, s->stream));
@@ -582,6 +689,7 @@ int garb200_cycle_append(garb200_solver *s, const garb200_knot_view *knots, int 
   CK(cudaMemsetAsync(p.thGrad, 0, std::max<size_t>(B * p.nth, 1) * sizeof(double), s->stream));
   CK(cudaMemsetAsync(p.thHess, 0, std::max<size_t>(B * p.nth * p.nth, 1) * sizeof(double), s->stream));
   s->did_forward = false;
+  s->gains_fresh = false;
   return GARB200_OK;
 }
 
@@ -634,7 +742,7 @@ int garb200_used_fast_path(const garb200_solver *s) { return s && s->used_fast ?
 
 int garb200_phase_cycles(garb200_solver *s, long long *out16) {
   if (!s || !out16) return fail(GARB200_ERR_INVALID, "null argument");
-  if (!s->p.phase_cycles) return fail(GARB200_ERR_STATE, "create the solver with GARB200_PHASE_TIMERS=1 in the environment");
+  if (!s->p.phase_cycles) return fail(GARB200_ERR_STATE, "create the solver with GARB200_PHASE_TIMERS in garb200_config.flags");
   CK(cudaSetDevice(s->cfg.device));
   CK(cudaStreamSynchronize(s->stream));
   CK(cudaMemcpy(out16, s->p.phase_cycles, 16 * sizeof(long long), cudaMemcpyDeviceToHost));

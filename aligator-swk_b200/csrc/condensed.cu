@@ -449,7 +449,7 @@ int launch_condensed(const DevParams &p, cudaStream_t st) {
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
     return -2;
   int launched = 0, only_marked = 0;
-  static const bool force_bk = [] { const char *e = getenv("GARB200_CONDENSED"); return e && e[0] == 'b'; }();
+  const bool force_bk = p.tune.condensed == 1;
   if (n == 36 && p.nc0 == 36 && !force_bk) {
     constexpr int N = 36, NW = 5;
     const size_t vlen = (size_t)2 * p.num_legs * N;
@@ -463,7 +463,7 @@ int launch_condensed(const DevParams &p, cudaStream_t st) {
       only_marked = 1;
     }
   }
-  static const bool fast_only = [] { const char *e = getenv("GARB200_CONDENSED"); return e && e[0] == 'f'; }();   // debugging
+  const bool fast_only = p.tune.condensed == 2;   // debugging
   if (fast_only && only_marked) return launched;
   kern<<<p.batch, NT, smem, st>>>(p, only_marked);
   return cudaGetLastError() == cudaSuccess ? launched + 1 : -2;

@@ -33,6 +33,26 @@ template <int NT_> struct Group {
   __device__ __forceinline__ int warp() const { return tid >> 5; }
 };
 
+// Barrier over the NT threads that cooperate on ONE problem.  GRP > 1: the CTA holds GRP problems
+// (threads [g NT, (g+1) NT) own problem g) and each group has its own hardware named barrier
+// 1 + g; barrier 0 (__syncthreads) stays free for aligning the groups with each other.
+template <int NT, int GRP = 1> __device__ __forceinline__ void cta_sync() {
+  if constexpr (NT == 32) __syncwarp();
+  else if constexpr (GRP == 1) __syncthreads();
+  else asm volatile("bar.sync %0, %1;" ::"r"(1 + (int)(threadIdx.x / NT)), "r"(NT) : "memory");
+}
+// group-wide AND of a predicate (the __syncthreads_and of one group)
+template <int NT, int GRP = 1> __device__ __forceinline__ int cta_all(int pred) {
+  if constexpr (NT == 32) return __all_sync(0xffffffffu, pred);
+  else if constexpr (GRP == 1) return __syncthreads_and(pred);
+  else {
+    int out;
+    asm volatile("{\n\t.reg .pred p, q;\n\tsetp.ne.b32 q, %1, 0;\n\tbar.red.and.pred p, %2, %3, q;\n\tselp.b32 %0, 1, 0, p;\n\t}"
+                 : "=r"(out) : "r"(pred), "r"(1 + (int)(threadIdx.x / NT)), "r"(NT) : "memory");
+    return out;
+  }
+}
+
 __device__ __forceinline__ int imin(int a, int b) { return a < b ? a : b; }
 __device__ __forceinline__ int imax(int a, int b) { return a > b ? a : b; }
 
@@ -405,13 +425,13 @@ __device__ __forceinline__ bool bk_factor_warp(int lane, int n, double *a, int l
 // snapshots the pivot column(s) into wk; one barrier; every thread updates its share of the
 // trailing lower triangle; one barrier.   wk: 2n + 4 doubles, ctl: 4 ints of scratch.
 // ------------------------------------------------------------------------------------------
-template <int NT>
+template <int NT, int GRP = 1>
 __device__ __forceinline__ bool bk_factor_cta(int tid, int n, double *a, int ld, int *piv, double *sub,
                                               double *wk, int *ctl) {
   const double alpha = 0.6403882032022076;   // (1 + sqrt(17)) / 8
   const int lane = tid & 31, warp = tid >> 5;
   constexpr int TY = NT / 32;
-  auto gsync = [&]() { if constexpr (NT == 32) __syncwarp(); else __syncthreads(); };
+  auto gsync = [&]() { cta_sync<NT, GRP>(); };
   if (n == 0) return true;
   int k = 0;
   bool ok = true;

@@ -258,10 +258,6 @@ __device__ __forceinline__ void gemv4(int tid, FA a, FX x, FI yin, FO yout) {
   }
 }
 
-template <int NT> __device__ __forceinline__ void cta_sync() {
-  if constexpr (NT == 32) __syncwarp();
-  else __syncthreads();
-}
 
 // A(j,i) = A(i,j), i > j (col-major, ld = N): selfadjointView<Lower>
 template <int N, int NT> __device__ __forceinline__ void mirror_lower_ct(int tid, double *A) {
@@ -346,7 +342,7 @@ template <int NXc, int H, int S> struct RhsGainsTh {
 // not have that inertia (SPD: NPOS = N; quasi-definite KKT block: NPOS = nu).
 // Scratch: Wp 4 (N - 4) doubles, dinv N doubles.  Needs NT >= round32(N - 4) + NR threads.
 // ------------------------------------------------------------------------------------------
-template <int N, int NR, int NT, int NPOS = N, class RH>
+template <int N, int NR, int NT, int NPOS = N, int GRP = 1, class RH>
 __device__ __forceinline__ bool ldlt_solve_blocked(int tid, double *S, RH R, double *Wp, double *dinv) {
   static_assert(N % 4 == 0, "blocked LDL^T needs N % 4 == 0");
   constexpr int NW = NT / 32;
@@ -410,7 +406,7 @@ __device__ __forceinline__ bool ldlt_solve_blocked(int tid, double *S, RH R, dou
       const double y3 = fma(-l32, y2, fma(-l31, y1, fma(-l30, y0, R.get(r0 + 3, j))));
       R.set(r0 + 1, j, y1); R.set(r0 + 2, j, y2); R.set(r0 + 3, j, y3);
     }
-    cta_sync<NT>();
+    cta_sync<NT, GRP>();
     if (tid == NT - 1) {   // after the barrier: every thread has read the unscaled diagonal block
       double *Dw = S + r0 + r0 * N;
       Dw[1] = l10; Dw[2] = l20; Dw[3] = l30; Dw[2 + N] = l21; Dw[3 + N] = l31; Dw[3 + 2 * N] = l32;
@@ -431,13 +427,13 @@ __device__ __forceinline__ bool ldlt_solve_blocked(int tid, double *S, RH R, dou
                  [&](int k, int j) { return Wp[4 * j + k]; },
                  [&](int i, int j) { return S1[i + j * N]; },
                  [&](int i, int j, double v) { S1[i + j * N] = v; });
-      cta_sync<NT>();
+      cta_sync<NT, GRP>();
     }
   }
-  cta_sync<NT>();
+  cta_sync<NT, GRP>();
   // z = D^{-1} y
   for (int e = tid; e < N * NR; e += NT) { const int i = e % N, j = e / N; R.set(i, j, R.get(i, j) * dinv[i]); }
-  cta_sync<NT>();
+  cta_sync<NT, GRP>();
 #pragma unroll 1
   for (int r0 = N - 4; r0 >= 0; r0 -= 4) {
     // ---- phase C: x rows r0..r0+3 of every column
@@ -451,7 +447,7 @@ __device__ __forceinline__ bool ldlt_solve_blocked(int tid, double *S, RH R, dou
       R.set(r0 + 2, tid, x2); R.set(r0 + 1, tid, x1); R.set(r0, tid, x0);
     }
     if (r0 == 0) break;
-    cta_sync<NT>();
+    cta_sync<NT, GRP>();
     // ---- phase D: rows above: R(i, j) -= sum_k L(r0+k, i) x(r0+k, j)
     const double *Lr = S + r0;                     // (r0+k, i) at Lr[k + i*N]
     mma_k4<NW, (NR + 7) / 8>(warp, lane, r0, NR, false,
@@ -459,9 +455,9 @@ __device__ __forceinline__ bool ldlt_solve_blocked(int tid, double *S, RH R, dou
                [&](int k, int j) { return R.get(r0 + k, j); },
                [&](int i, int j) { return R.get(i, j); },
                [&](int i, int j, double v) { R.set(i, j, v); });
-    cta_sync<NT>();
+    cta_sync<NT, GRP>();
   }
-  cta_sync<NT>();
+  cta_sync<NT, GRP>();
   return ok;
 }
 

@@ -229,7 +229,7 @@ int launch_forward(const DevParams &p, const double *d_theta, double *xs, double
     if (rc != -3) return rc;
   }
   if (p.GL.stride * 8 <= 4096) return launch_forward_t<32, 4>(p, d_theta, xs, us, vs, lbdas, st);
-  static const int stages = [] { const char *e = getenv("GARB200_FWD_STAGES"); return e ? atoi(e) : 2; }();   // 2: more CTAs per SM beats a deeper ring (c1b 5.7 -> 6.6 TB/s, c3 4.1 -> 5.5 TB/s)
+  const int stages = p.tune.fwd_stages;   // 2: more CTAs per SM beats a deeper ring (c1b 5.7 -> 6.6 TB/s, c3 4.1 -> 5.5 TB/s)
   if (stages == 1 || (stages == 2 && forward_smem(p, 2) > 114u * 1024u && forward_smem(p, 1) <= 113u * 1024u + 512u))   // two 1-deep CTAs per SM
     return launch_forward_t<128, 1>(p, d_theta, xs, us, vs, lbdas, st);
   if (stages == 4 && forward_smem(p, 4) <= 110u * 1024u) return launch_forward_t<128, 4>(p, d_theta, xs, us, vs, lbdas, st);

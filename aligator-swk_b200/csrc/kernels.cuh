@@ -12,6 +12,18 @@ __host__ __device__ inline void get_work(int horz, int tid, int nthreads, int &b
   end = (int)((long long)(tid + 1) * (horz + 1) / nthreads);
 }
 
+/// Diagnostic tuning knobs (garb200_set_tuning): read by the LAUNCHERS only, fixed per solver.
+struct Tune {
+  int group = 0;          // problems per CTA of the nx = 36 sweep (0: default = 3 in lockstep, 1: one CTA per problem)
+  int einv_mode = 0;      // 0: default pre-pass, 1: register Gauss-Jordan, 2: LU in shared memory (nx = 76)
+  int einv_minb = 6;      // min CTAs/SM hint of the small-matrix pre-pass
+  int fwd_stages = 2;     // TMA ring depth of the forward rollout
+  int condensed = 0;      // 0: default, 1: Bunch-Kaufman kernel only, 2: specialised kernel only
+  int c3_eg = 1;          // (36,12,6,4): E^{-1} read from L2 instead of staged
+  int legs_generic = 0;   // leg mode on the generic kernel
+  int explicit_dyn = 1;   // use the E = -I fast path when every knot qualifies
+};
+
 /// Everything a kernel needs to know about one solver (passed by value).
 struct DevParams {
   int nx, nu, nc, nth;  // layout dims (nth: user parameter dim; 0 in leg mode)
@@ -37,6 +49,8 @@ struct DevParams {
   int32_t *flags, *refine_steps;
   long long *phase_cycles;        // [16] accumulated phase timers of the specialised sweep, or nullptr
   double mudyn, mueq;
+  Tune tune;
+  void *side_stream = nullptr, *side_e0 = nullptr, *side_e1 = nullptr;   // leg mode (host side only)
   garb200_knot_layout KL;
   garb200_gain_layout GL;   // built with nth_eff = (leg mode ? nx : nth)
   garb200_value_layout VL;  // same
@@ -66,7 +80,6 @@ bool fast_path_available(int nx, int nu, int nc, int nth, int num_legs);
 // streaming variant for records larger than shared memory (sweep_big.cu): -3 = no instantiation
 int launch_backward_big(const DevParams &p, cudaStream_t st);
 bool big_path_available(int nx, int nu, int nc, int nth);
-int launch_big_sweep_36(const DevParams &p, cudaStream_t st);
 int launch_forward(const DevParams &p, const double *d_theta, double *xs, double *us, double *vs,
                    double *lbdas, cudaStream_t st);
 int launch_condensed(const DevParams &p, cudaStream_t st);

@@ -487,7 +487,7 @@ static int launch_big_t(const DevParams &p, cudaStream_t st) {
     return -3;
   const long long total = (long long)p.batch * p.T;
   int launched = 0;
-  static const bool lu_prepass = [] { const char *e = getenv("GARB200_EINV"); return e && e[0] == 'l'; }();
+  const bool lu_prepass = p.tune.einv_mode == 2;
   if (total > 0 && !lu_prepass) {
     constexpr int EW = 5;
     constexpr size_t esm = (size_t)GjCta<NX>::SMEM * sizeof(double) + (size_t)GjCta<NX>::SINTS * sizeof(int);
@@ -509,20 +509,6 @@ static int launch_big_t(const DevParams &p, cudaStream_t st) {
   ks<<<p.batch, 32 * NW, smem, st>>>(p);
   if (cudaGetLastError() != cudaSuccess) return -2;
   return launched + 1;
-}
-
-// The same streaming plan for nx = 36, nu = 12 (47.9 KB of shared memory, 4 CTAs x 5 warps per SM at 102
-// registers) — sweep only, the caller has run the E^{-1} pre-pass.
-int launch_big_sweep_36(const DevParams &p, cudaStream_t st) {
-  using PL = BigPlan<36, 12>;
-  if (p.KL.stride != PL::kstride || p.GL.stride != PL::gstride || p.KL.E != PL::oE || p.KL.f != PL::of ||
-      p.KL.A != PL::oA || p.KL.R != PL::oR || p.GL.fb != PL::gfb)
-    return -3;
-  const size_t smem = (size_t)PL::total * sizeof(double);
-  auto ks = sweep_big_kernel<36, 12, 5, 4>;
-  if (cudaFuncSetAttribute(ks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -2;
-  ks<<<p.batch, 32 * 5, smem, st>>>(p);
-  return cudaGetLastError() == cudaSuccess ? 1 : -2;
 }
 
 bool big_path_available(int nx, int nu, int nc, int nth) { return nx == 76 && nu == 32 && nc == 0 && nth == 0; }

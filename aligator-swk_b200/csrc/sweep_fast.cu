@@ -10,7 +10,6 @@
 //                  (NW warps) per problem, knot record + Einv staged by 1-D TMA bulk copies,
 //                  all n^3 contractions on the FP64 tensor pipe (DMMA), GEMVs riding along
 //                  as an extra column of the GEMM they belong to.
-#include <cstdlib>
 #include "fast.cuh"
 #include "kernels.cuh"
 
@@ -109,22 +108,34 @@ template <int NX, int NU, int NC, int NTH = 0, int HREC = NTH, bool EG = false> 
 // NTH = NX for the legs that end on a co-state cut (the leg-end knot is a terminal solve with nu > 0
 // and the coupling blocks as its parameter block), NTH = 0 for the last leg; the value function of
 // the leg's first knot goes to value slot `leg`, there is no initial stage.
-template <int NX, int NU, int NC, int NTH, int NW, bool PROF, bool LEG = false, bool EG = false>
-__global__ void __launch_bounds__(32 * NW, (NW >= 8 ? 2 : (NW == 5 && NTH <= 4) ? 3 : NW == 1 ? 24 : 1))
+// GRP > 1: GRP problems per CTA in LOCKSTEP.  Threads [g NT, (g+1) NT) solve problem blockIdx.x GRP + g
+// in their own slice of shared memory with their own named barrier; once per knot all groups meet at
+// barrier 0 right before the reduced-KKT solve, so that the latency-bound dependent FP64 chains of the
+// factorizations run while NO group feeds the tensor pipe (a dependent DFMA queued behind the other
+// CTAs' DMMAs waits ~100 cycles; alone it takes ~10), and the GEMM phases of all groups saturate the pipe
+// together.  Independent CTAs (GRP = 1, 3 per SM) drift apart and pay that queueing in every chain.
+template <int NX, int NU, int NC, int NTH, int NW, bool PROF, bool LEG = false, bool EG = false, int GRP = 1>
+__global__ void __launch_bounds__(32 * NW * GRP, GRP > 1 ? 1 : (NW >= 8 ? 2 : (NW == 5 && NTH <= 4) ? 3 : NW == 1 ? 24 : 1))
 sweep_kernel(const DevParams p) {
-  extern __shared__ __align__(16) double sm[];
+  extern __shared__ __align__(16) double sm_cta[];
   using PL = FastPlan<NX, NU, NC, NTH, LEG ? 0 : NTH, EG>;
+  static_assert(GRP == 1 || !LEG, "lockstep groups are not combined with leg mode");
+  static_assert(PL::total % 2 == 0, "group slices must stay 16-byte aligned");
+  const int grp = GRP > 1 ? (int)threadIdx.x / (32 * NW) : 0;
+  double *sm = sm_cta + (size_t)grp * PL::total;
   static_assert(!LEG || NC == 0, "leg mode: nc = 0");
   static_assert(!EG || !LEG, "EG is not combined with leg mode");
   constexpr int n = NX, m = NU, c = NC, s = NU + NC, h = NTH, NT = 32 * NW;
   constexpr int NA = PL::NA, na = PL::na, sp = PL::sp;
   constexpr int hh = h > 0 ? h : 1;        // divisor-safe
   constexpr int rK = 0, rZ = m, rL = m + c, rA = m + c + n;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = (int)threadIdx.x - grp * NT, warp = tid >> 5, lane = tid & 31;
   const int T = p.T;
   const int nlegs = LEG ? p.num_legs : 1;
   const int leg = LEG ? (NTH > 0 ? (int)(blockIdx.x % (unsigned)(nlegs - 1)) : nlegs - 1) : 0;
-  const int b = (LEG && NTH > 0) ? (int)(blockIdx.x / (unsigned)(nlegs - 1)) : (int)blockIdx.x;
+  // (a group past the end of the batch re-solves the last problem: same bytes to the same addresses)
+  const int b = (LEG && NTH > 0) ? (int)(blockIdx.x / (unsigned)(nlegs - 1))
+                                 : (GRP > 1 ? min((int)blockIdx.x * GRP + grp, p.batch - 1) : (int)blockIdx.x);
   int beg = 0, end = T + 1;
   if constexpr (LEG) get_work(T, leg, nlegs, beg, end);
   const int tl = end - 1;                  // last knot of this sweep (T unless a coupled leg)
@@ -171,7 +182,7 @@ sweep_kernel(const DevParams p) {
   if (tid == 0) { mbar_init(bar, 1); fence_mbar_init(); }
   for (int e = tid; e < PL::gpart; e += NT) Gs[e] = 0.0;
   for (int e = tid; e < PL::gthsz; e += NT) fth[e] = 0.0;
-  cta_sync<NT>();
+  cta_sync<NT, GRP>();
   uint32_t phase = 0;
   const size_t pbase = (size_t)b * (T + 1);
   auto issue_load = [&](int t) {      // thread 0 only
@@ -196,7 +207,7 @@ sweep_kernel(const DevParams p) {
   };
   auto store_gains = [&](int t) {     // all threads; Gs complete
     fence_proxy_async();
-    cta_sync<NT>();
+    cta_sync<NT, GRP>();
     if (tid == 0) {
       double *gdst = p.gains + (pbase + phys_t(p, t)) * p.GL.stride;
       tma_store_1d(gdst, Gs, (uint32_t)PL::gpart * 8u);
@@ -245,20 +256,20 @@ sweep_kernel(const DevParams p) {
       for (int e = tid; e < m * h; e += NT) { const int i = e / hh, j = e % hh; fth[(rK + i) * h + j] = -B[j + i * n]; }   // -Gu = -B^T
     };
     build_term();
-    cta_sync<NT>();
-    if (!ldlt_solve_blocked<sp, na, NT, m>(tid, kkt, RhsGainsTh<n, h, s>{ff, fb, fth}, P, P + 4 * sp)) {
+    cta_sync<NT, GRP>();
+    if (!ldlt_solve_blocked<sp, na, NT, m, GRP>(tid, kkt, RhsGainsTh<n, h, s>{ff, fb, fth}, P, P + 4 * sp)) {
       build_term();
-      cta_sync<NT>();
+      cta_sync<NT, GRP>();
       if (warp == 0) {
         if (!bk_factor_warp(lane, s, kkt, sp, kpiv, ksub)) flags |= GARB200_FLAG_BK_SINGULAR;
       }
-      cta_sync<NT>();
+      cta_sync<NT, GRP>();
       for (int col = tid; col < na; col += NT) {
         if (col == 0) bk_solve_column(s, kkt, sp, kpiv, ksub, ff, 1);
         else if (col <= n) bk_solve_column(s, kkt, sp, kpiv, ksub, fb + (col - 1), n);
         else bk_solve_column(s, kkt, sp, kpiv, ksub, fth + (col - n - 1), h);
       }
-      cta_sync<NT>();
+      cta_sync<NT, GRP>();
     }
     // [Pmat | pvec] = [Q | q] + S [K | kff]                                              (:134-140)
     mma_gemm<n, n + 1, s, NW>(warp, lane,
@@ -306,7 +317,7 @@ sweep_kernel(const DevParams p) {
   zero_fth_tail(tl);
   store_value(tl);
   fence_proxy_async();
-  cta_sync<NT>();
+  cta_sync<NT, GRP>();
 
 #pragma unroll 1
   for (int t = tl - 1; t >= beg; t--) {
@@ -321,7 +332,7 @@ sweep_kernel(const DevParams p) {
     }
     if constexpr (EG) gE = p.einv + ((size_t)b * T + phys_t(p, t)) * (size_t)(n * n);
     mbar_wait(bar, phase); phase ^= 1;
-    cta_sync<NT>();
+    cta_sync<NT, GRP>();
     PH(0);
     // (1) [X1 | x1v] = Einv^T [P | pvec]          EinvP, -ptilde      (:175-178)
     //     theta columns: Pxttilde = -Einv^T Vxt -> Pxt                                   (:261-262)
@@ -337,7 +348,7 @@ sweep_kernel(const DevParams p) {
         [&](int k, int j) { return P[k + j * n]; },
         [](int, int) { return 0.0; },
         [&](int i, int j, double v) { if (j <= n) X1[i + j * n] = v; else Pxt[i + (j - n - 1) * n] = -v; });
-    cta_sync<NT>();
+    cta_sync<NT, GRP>();
     PH(1);
     // (2) Ptilde = X1 * Einv (lower triangle kept, mirrored); ||Ptilde||_F^2 on the fly  (:179-180)
     double fro = 0.0;
@@ -360,7 +371,7 @@ sweep_kernel(const DevParams p) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) fro += __shfl_xor_sync(0xffffffffu, fro, o);
     if (lane == 0) red[warp] = fro;
-    cta_sync<NT>();
+    cta_sync<NT, GRP>();
     PH(2);
     fro = 0.0;
 #pragma unroll
@@ -381,7 +392,7 @@ sweep_kernel(const DevParams p) {
         if (i >= j) X1[e] = (i == j ? 1.0 : 0.0) + mudyn * P[e];
       }
     }
-    cta_sync<NT>();
+    cta_sync<NT, GRP>();
     PH(3);
     // (4) [Vxx | vx] = Lambda^{-1} [Ptilde | w]                                      (:185-190)
     if (neumann) {
@@ -393,17 +404,17 @@ sweep_kernel(const DevParams p) {
             if (j >= n || i >= j) X1[i + j * n] = v;
             if (j < n && i > j) X1[j + i * n] = v;
           });
-      cta_sync<NT>();
+      cta_sync<NT, GRP>();
       PH(4);
       static_assert((n * na) % 2 == 0, "vector copy");
       for (int e = tid; e < n * na / 2; e += NT)              // back into P
         reinterpret_cast<double2 *>(P)[e] = reinterpret_cast<const double2 *>(X1)[e];
     } else {
-      if (!ldlt_solve_blocked<n, na, NT>(tid, X1, RhsColMajor<n>{P}, Gs, dinv)) flags |= GARB200_FLAG_LLT_NOT_PD;
+      if (!ldlt_solve_blocked<n, na, NT, n, GRP>(tid, X1, RhsColMajor<n>{P}, Gs, dinv)) flags |= GARB200_FLAG_LLT_NOT_PD;
       PH(4);
       mirror_lower_ct<n, NT>(tid, P);
     }
-    cta_sync<NT>();
+    cta_sync<NT, GRP>();
     PH(5);
     if (p.store_all_values) {
       double *v = p.values + ((size_t)b * p.nslots + (t + 1)) * p.VL.stride;
@@ -419,7 +430,7 @@ sweep_kernel(const DevParams p) {
           if (i < n) { if (j < n) X1[i + j * n] = v; else if (j == n) atvx[i] = v; }   // A^T Lth0 is not needed
           else BtV[(i - n) + j * m] = v;                                             // B^T [Vxx | vx | Lth0]
         });
-    cta_sync<NT>();
+    cta_sync<NT, GRP>();
     PH(6);
     // (6) [Qhat | Shat] = [Q | S] + AtV [A | B] (in place) ; Rhat = R + BtV B -> kkt   (:195-199)
     mma_gemm<n, n + m, n, NW>(warp, lane,
@@ -462,7 +473,7 @@ sweep_kernel(const DevParams p) {
     };
     build_kkt();
     for (int i = tid; i < n; i += NT) qv[i] += atvx[i];                           // qhat
-    cta_sync<NT>();
+    cta_sync<NT, GRP>();
     build_rhs_K();
     // (7) reduced KKT system [Rhat D^T; D -mueq I] [K kff; Z zff] = rhs                  (:202-228)
     // The matrix is quasi-definite whenever Rhat > 0 (any convex stage): LDL^T in the natural
@@ -470,26 +481,27 @@ sweep_kernel(const DevParams p) {
     // knot that fails the check is rebuilt and factorised with the reference's Bunch-Kaufman
     // pivoting instead (bunchkaufman.hpp:20-167, 447-516).
     PH(7);
-    cta_sync<NT>();
+    if constexpr (GRP > 1) __syncthreads();     // all groups enter the KKT chains together (see the kernel comment)
+    else cta_sync<NT, GRP>();
     PH(8);
     {
       // blocked LDL^T solve (backward stable; an explicit inverse of Rhat was measurably less
       // accurate on the ill-conditioned knots of the reference distribution)
-      const bool okk = ldlt_solve_blocked<sp, na, NT, m>(tid, kkt, RhsGainsTh<n, h, s>{ff, fb, fth}, P, P + 4 * sp);
+      const bool okk = ldlt_solve_blocked<sp, na, NT, m, GRP>(tid, kkt, RhsGainsTh<n, h, s>{ff, fb, fth}, P, P + 4 * sp);
       if (!okk) {                     // uniform: every thread computed the same pivots
         build_kkt();
         build_rhs_K();
-        cta_sync<NT>();
+        cta_sync<NT, GRP>();
         if (warp == 0) {
           if (!bk_factor_warp(lane, s, kkt, sp, kpiv, ksub)) flags |= GARB200_FLAG_BK_SINGULAR;
         }
-        cta_sync<NT>();
+        cta_sync<NT, GRP>();
         for (int col = tid; col < na; col += NT) {
           if (col == 0) bk_solve_column(s, kkt, sp, kpiv, ksub, ff, 1);
           else if (col <= n) bk_solve_column(s, kkt, sp, kpiv, ksub, fb + (col - 1), n);
           else bk_solve_column(s, kkt, sp, kpiv, ksub, fth + (col - n - 1), h);
         }
-        cta_sync<NT>();
+        cta_sync<NT, GRP>();
       }
     }
     PH(9);
@@ -604,7 +616,7 @@ sweep_kernel(const DevParams p) {
       }
       }
     }
-    cta_sync<NT>();
+    cta_sync<NT, GRP>();
     PH(10);
     // (10) [Afb | yff] = -Einv [A_pre | tv]                                              (:243-245)
     //      rows n..n+h-1 of the same product: Pxttilde^T [A_pre | tv | Yth_pre] = Vxt^T [Afb | yff | Yth]
@@ -643,7 +655,7 @@ sweep_kernel(const DevParams p) {
             else Vttp[a + (j - n - 1) * h] = v;
           }
         });
-    cta_sync<NT>();
+    cta_sync<NT, GRP>();
     PH(11);
     // (11) [Pmat | pvec] = [Qhat | qhat] + Shat [K | kff] + C^T [Z | zff]                  (:249-250)
     mma_gemm<n, n + 1, s, NW>(warp, lane,
@@ -691,7 +703,7 @@ sweep_kernel(const DevParams p) {
     zero_fth_tail(t);
     store_value(t);
     fence_proxy_async();
-    cta_sync<NT>();
+    cta_sync<NT, GRP>();
     PH(13);
   }
   PH(14);
@@ -700,7 +712,7 @@ sweep_kernel(const DevParams p) {
   if constexpr (EG) { ksub = BtV; kpiv = reinterpret_cast<int *>(BtV + PL::KS); }   // P is live here, BtV is dead
   if constexpr (!LEG) {
     if (tid == 0) tma_store_wait_read();
-    cta_sync<NT>();
+    cta_sync<NT, GRP>();
     const int c0 = p.nc0, s0 = n + c0;
     const double *G0 = p.G0 + (size_t)b * c0 * n, *g0 = p.g0 + (size_t)b * c0;
     double *off = p.kkt0_ff + (size_t)b * s0;
@@ -716,7 +728,7 @@ sweep_kernel(const DevParams p) {
         const int i = e % n, j = e / n;
         if (G0[e] != (i == j ? 1.0 : 0.0)) isI = 0;
       }
-    if constexpr (NT == 32) isI = __all_sync(0xffffffffu, isI); else isI = __syncthreads_and(isI);
+    isI = cta_all<NT, GRP>(isI);
     if (isI) {
       double fro = 0.0;
       for (int e = tid; e < n * n; e += NT) fro = fma(P[e], P[e], fro);
@@ -727,7 +739,7 @@ sweep_kernel(const DevParams p) {
                       [&](int i) { return -pv[i]; }, [&](int i, double v) { x1v[i] = v; });
       if constexpr (h > 0)
         for (int e = tid; e < n * h; e += NT) x1th[e] = -Pth[e];      // (I + mudyn P0) lbd0_th = -Vxt0
-      cta_sync<NT>();
+      cta_sync<NT, GRP>();
       fro = 0.0;
 #pragma unroll
       for (int w = 0; w < NW; w++) fro += red[w];
@@ -741,7 +753,7 @@ sweep_kernel(const DevParams p) {
           for (int j = 0; j < h; j++)
             gemv4<n, n, NT>(tid, [&](int i, int k) { return -mudyn * P[i + k * n]; }, [&](int k) { return x1th[k + j * n]; },
                             [&](int i) { return x1th[i + j * n]; }, [&](int i, double v) { Pxt[i + j * n] = v; });
-          cta_sync<NT>();
+          cta_sync<NT, GRP>();
           for (int e = tid; e < n * h; e += NT) x1th[e] = Pxt[e];
         }
       } else {
@@ -749,10 +761,10 @@ sweep_kernel(const DevParams p) {
           const int i = e % n, j = e / n;
           if (i >= j) X1[e] = (i == j ? 1.0 : 0.0) + mudyn * P[e];
         }
-        cta_sync<NT>();
-        if (!ldlt_solve_blocked<n, NA, NT>(tid, X1, RhsColMajor<n>{x1v}, Gs, dinv)) flags |= GARB200_FLAG_LLT_NOT_PD;
+        cta_sync<NT, GRP>();
+        if (!ldlt_solve_blocked<n, NA, NT, n, GRP>(tid, X1, RhsColMajor<n>{x1v}, Gs, dinv)) flags |= GARB200_FLAG_LLT_NOT_PD;
       }
-      cta_sync<NT>();
+      cta_sync<NT, GRP>();
       for (int i = tid; i < n; i += NT) { off[i] = fma(mudyn, lam[i], -g0[i]); off[n + i] = lam[i]; }
       if constexpr (h > 0) {
         // x0_th = mudyn lbd0_th ; thGrad = vt + Vxt^T x0 ; thHess = Vtt + Vxt^T x0_th         (:59-61)
@@ -789,10 +801,10 @@ sweep_kernel(const DevParams p) {
         K0[i + j * ld0] = v;
       }
       for (int i = tid; i < s0; i += NT) ff0[i] = (i < n) ? -pv[i] : -g0[i - n];
-      cta_sync<NT>();
-      if (!bk_factor_cta<NT>(tid, s0, K0, ld0, kpiv, ksub, wk0, kpiv + s0)) flags |= GARB200_FLAG_BK_SINGULAR;
+      cta_sync<NT, GRP>();
+      if (!bk_factor_cta<NT, GRP>(tid, s0, K0, ld0, kpiv, ksub, wk0, kpiv + s0)) flags |= GARB200_FLAG_BK_SINGULAR;
       if (warp == 0) bk_solve_vec_warp<(2 * n + 31) / 32>(lane, s0, K0, ld0, kpiv, ksub, ff0, reinterpret_cast<int *>(wk0));
-      cta_sync<NT>();
+      cta_sync<NT, GRP>();
       for (int i = tid; i < s0; i += NT) off[i] = ff0[i];
       if constexpr (h > 0) {
         // theta columns one after the other through the same warp solve; X1 (free here? no: K0
@@ -801,14 +813,14 @@ sweep_kernel(const DevParams p) {
         static_assert(PL::Vxn == PL::Pxt + n * h, "Pxt and Vxn must be adjacent");
 #pragma unroll 1
         for (int j = 0; j < h; j++) {
-          cta_sync<NT>();
+          cta_sync<NT, GRP>();
           for (int i = tid; i < s0; i += NT) ff0[i] = (i < n) ? -Pth[i + j * n] : 0.0;
-          cta_sync<NT>();
+          cta_sync<NT, GRP>();
           if (warp == 0) bk_solve_vec_warp<(2 * n + 31) / 32>(lane, s0, K0, ld0, kpiv, ksub, ff0, reinterpret_cast<int *>(wk0));
-          cta_sync<NT>();
+          cta_sync<NT, GRP>();
           for (int i = tid; i < s0; i += NT) { ofth[i * h + j] = ff0[i]; if (i < n) fth0[i + j * n] = ff0[i]; }
         }
-        cta_sync<NT>();
+        cta_sync<NT, GRP>();
         for (int e = tid; e < h * h + h; e += NT) {
           if (e < h * h) {
             const int a = e % hh, bb = e / hh;
@@ -838,7 +850,7 @@ sweep_kernel(const DevParams p) {
 }
 
 // ---- host side -----------------------------------------------------------------------------
-template <int NX, int NU, int NC, int NTH, int NW, bool EG = false>
+template <int NX, int NU, int NC, int NTH, int NW, bool EG = false, int GRP = 1>
 static int launch_fast_t(const DevParams &p, cudaStream_t st) {
   using PL = FastPlan<NX, NU, NC, NTH, NTH, EG>;
   static_assert(!EG || PL::BtV + PL::KS + (PL::KS + 1) / 2 + 2 <= PL::kkt, "EG: BK scratch of the initial stage must fit in BtV");
@@ -853,7 +865,7 @@ static int launch_fast_t(const DevParams &p, cudaStream_t st) {
   const long long total = (long long)p.batch * p.T;
   int launched = 0;
   if (total > 0) {
-    static const bool force_regs = [] { const char *e = getenv("GARB200_EINV"); return e && e[0] == 'r'; }();
+    const bool force_regs = p.tune.einv_mode == 1;
     if constexpr (NX % 4 == 0 && NX > 16) {
       if (!force_regs) {
         constexpr size_t esm = (size_t)WPB * (GjDmma<NX>::SMEM * sizeof(double) + GjDmma<NX>::SINTS * sizeof(int));
@@ -863,7 +875,7 @@ static int launch_fast_t(const DevParams &p, cudaStream_t st) {
       else einv_kernel<NX, WPB><<<(unsigned)((total + MPB - 1) / MPB), 32 * WPB, 0, st>>>(p);
     } else {
       // small matrices: the register cap trades a few spilled bytes for 24 / 32 resident warps per SM
-      static const int minb = [] { const char *e = getenv("GARB200_EINV_MINB"); return e ? atoi(e) : 6; }();
+      const int minb = p.tune.einv_minb;
       const unsigned grid = (unsigned)((total + MPB - 1) / MPB);
       if (minb >= 8) einv_kernel<NX, WPB, 8><<<grid, 32 * WPB, 0, st>>>(p);
       else if (minb >= 6) einv_kernel<NX, WPB, 6><<<grid, 32 * WPB, 0, st>>>(p);
@@ -872,17 +884,11 @@ static int launch_fast_t(const DevParams &p, cudaStream_t st) {
     if (cudaGetLastError() != cudaSuccess) return -2;
     launched++;
   }
-  if constexpr (NX == 36 && NU == 12 && NC == 0 && NTH == 0) {
-    static const bool streamed = [] { const char *e = getenv("GARB200_C1_STREAM"); return e && e[0] == '1'; }();
-    if (streamed && !p.phase_cycles) {
-      const int rc = launch_big_sweep_36(p, st);
-      return rc < 0 ? rc : launched + rc;
-    }
-  }
-  const size_t smem = (size_t)PL::total * sizeof(double);
-  auto ks = p.phase_cycles ? sweep_kernel<NX, NU, NC, NTH, NW, true, false, EG> : sweep_kernel<NX, NU, NC, NTH, NW, false, false, EG>;
+  const size_t smem = (size_t)GRP * PL::total * sizeof(double);
+  static_assert((size_t)GRP * PL::total * sizeof(double) <= 227u * 1024u, "lockstep groups exceed the shared memory of one SM");
+  auto ks = p.phase_cycles ? sweep_kernel<NX, NU, NC, NTH, NW, true, false, EG, GRP> : sweep_kernel<NX, NU, NC, NTH, NW, false, false, EG, GRP>;
   if (cudaFuncSetAttribute(ks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -2;
-  ks<<<p.batch, 32 * NW, smem, st>>>(p);
+  ks<<<(p.batch + GRP - 1) / GRP, 32 * NW * GRP, smem, st>>>(p);
   if (cudaGetLastError() != cudaSuccess) return -2;
   return launched + 1;
 }
@@ -907,17 +913,10 @@ static int launch_fast_legs(const DevParams &p, cudaStream_t st) {
   if (cudaFuncSetAttribute(kc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smc) != cudaSuccess) return -2;
   if (cudaFuncSetAttribute(kl, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sml) != cudaSuccess) return -2;
   // The last leg is independent of the coupled legs (disjoint knots, gains and value slots): it runs on
-  // a side stream (one per device, created on first use) between two events, beside the coupled legs.
-  struct Side { cudaStream_t s = nullptr; cudaEvent_t e0 = nullptr, e1 = nullptr; bool ok = false; };
-  static Side side[16];
-  int dev = 0;
-  cudaGetDevice(&dev);
-  Side *sd = (dev >= 0 && dev < 16) ? &side[dev] : nullptr;
-  if (sd && !sd->s) {
-    sd->ok = cudaStreamCreateWithFlags(&sd->s, cudaStreamNonBlocking) == cudaSuccess &&
-             cudaEventCreateWithFlags(&sd->e0, cudaEventDisableTiming) == cudaSuccess &&
-             cudaEventCreateWithFlags(&sd->e1, cudaEventDisableTiming) == cudaSuccess;
-  }
+  // the solver's side stream (created in garb200_create) between two events, beside the coupled legs.
+  struct Side { cudaStream_t s; cudaEvent_t e0, e1; bool ok; };
+  Side side_{static_cast<cudaStream_t>(p.side_stream), static_cast<cudaEvent_t>(p.side_e0), static_cast<cudaEvent_t>(p.side_e1), p.side_stream != nullptr};
+  Side *sd = &side_;
   const bool fork = sd && sd->ok && p.batch * (p.num_legs - 1) < 4 * 148;   // only worth it while the GPU is not full
   if (fork) {
     if (cudaEventRecord(sd->e0, st) != cudaSuccess || cudaStreamWaitEvent(sd->s, sd->e0, 0) != cudaSuccess) return -2;
@@ -943,19 +942,16 @@ int launch_backward_fast(const DevParams &p, const int *h_nu_t, const int *h_nc_
   for (int t = 0; t < p.T; t++)
     if (h_nu_t[t] != p.nu || h_nc_t[t] != p.nc) return -3;
   if (p.num_legs >= 2) {
-    static const bool generic_legs = [] { const char *e = getenv("GARB200_LEGS"); return e && e[0] == 'g'; }();
-    if (generic_legs || p.store_all_values) return -3;
+    if (p.tune.legs_generic || p.store_all_values) return -3;
     if (p.nx == 36 && p.nu == 12 && p.nc == 0 && p.nth == 0) return launch_fast_legs<36, 12, 5>(p, st);
     return -3;
   }
   if (p.nx == 12 && p.nu == 4 && p.nc == 0 && p.nth == 0) return launch_fast_t<12, 4, 0, 0, 1>(p, st);
   if (p.nx == 36 && p.nu == 12 && p.nc == 0 && p.nth == 0) {
-    static const int nw = getenv("GARB200_NW36") ? atoi(getenv("GARB200_NW36")) : 5;   // tuning knob
-    return nw == 4 ? launch_fast_t<36, 12, 0, 0, 4>(p, st) : launch_fast_t<36, 12, 0, 0, 5>(p, st);
+    return p.tune.group == 1 ? launch_fast_t<36, 12, 0, 0, 5>(p, st) : launch_fast_t<36, 12, 0, 0, 5, false, 3>(p, st);
   }
   if (p.nx == 36 && p.nu == 12 && p.nc == 6 && p.nth == 4) {   // C3: E^{-1} from L2 -> 75 KB of shared memory, 3 CTAs per SM
-    static const bool eg = [] { const char *e = getenv("GARB200_C3_EG"); return !(e && e[0] == '0'); }();
-    return eg ? launch_fast_t<36, 12, 6, 4, 5, true>(p, st) : launch_fast_t<36, 12, 6, 4, 5, false>(p, st);
+    return p.tune.c3_eg ? launch_fast_t<36, 12, 6, 4, 5, true>(p, st) : launch_fast_t<36, 12, 6, 4, 5, false>(p, st);
   }
   if (big_path_available(p.nx, p.nu, p.nc, p.nth)) return launch_backward_big(p, st);                     // C5
   return -3;

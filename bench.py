@@ -199,6 +199,7 @@ def gpu_arm(args, w, rank, world, local_rank):
     nx, nu, nc, nth, T, B, legs = w["nx"], w["nu"], w["nc"], w["nth"], w["T"], w["batch"], w["legs"]
     K, W = args.steps, args.warmup
     s = capi.Solver(nx, nu, nc, nth, horizon=T, batch=B, num_legs=legs, device=local_rank)
+    s.set_tuning(**args.tune_knobs)
     s.generate(seed=42 + rank, dist=0)
     s.synchronize_stream_only()
     theta_d = None
@@ -505,8 +506,10 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="override the per-GPU batch")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU-port timing")
+    ap.add_argument("--tune", action="append", default=[], help="diagnostic launcher knob key=value (garb200_set_tuning)")
     ap.add_argument("--horizons", action="store_true", help="the reference's own latency sweep over horizons (one GPU)")
     args = ap.parse_args()
+    args.tune_knobs = {kv.split("=")[0]: int(kv.split("=")[1]) for kv in args.tune}
     if args.horizons:
         horizon_sweep(args)
         return

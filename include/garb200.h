@@ -53,6 +53,8 @@ extern "C" {
                                         leg heads only — what the algorithm itself consumes)  */
 
 #define GARB200_FORCE_GENERIC 2      /* never use the dimension-specialised kernels (testing)  */
+#define GARB200_PHASE_TIMERS 4       /* diagnostic: per-phase clock64 timers in the specialised
+                                        sweep (garb200_phase_cycles); slower instrumented kernel */
 
 typedef struct garb200_solver garb200_solver; /* opaque */
 
@@ -94,6 +96,11 @@ void garb200_destroy(garb200_solver *s);
 const char *garb200_last_error(void);
 const char *garb200_version(void);
 
+/* Diagnostic tuning knobs, read by the kernel launchers of this solver only (no environment
+ * variables anywhere in the library).  Names: "group" (problems per CTA of the nx = 36 sweep:
+ * 0 default, 1 one CTA per problem), "einv_mode", "einv_minb", "fwd_stages", "condensed",
+ * "c3_eg", "legs_generic", "explicit_dyn" (0: never take the E = -I path). */
+int garb200_set_tuning(garb200_solver *s, const char *name, int value);
 /* Run subsequent kernels/copies on this CUDA stream (a cudaStream_t, passed as void*). */
 int garb200_set_stream(garb200_solver *s, void *cuda_stream);
 /* Block until everything queued by this solver has finished. */
@@ -188,7 +195,7 @@ int garb200_last_timings(garb200_solver *s, float *backward_ms, float *forward_m
 /* 1 if the last backward ran the dimension-specialised (DMMA) sweep, 0 for the generic kernel */
 int garb200_used_fast_path(const garb200_solver *s);
 /* Diagnostic: accumulated clock64() cycles of thread 0 of every CTA per phase of the specialised
- * sweep since the last call (solver created with GARB200_PHASE_TIMERS=1 in the environment). */
+ * sweep since the last call (solver created with GARB200_PHASE_TIMERS in config.flags). */
 int garb200_phase_cycles(garb200_solver *s, long long *out16);
 /* Per-call device timing log (bench / roofline): after _start, every backward and forward
  * brackets its kernels with CUDA events on the solver stream (up to `capacity` of each);

@@ -1,13 +1,13 @@
 """Per-phase cycle breakdown of the specialised sweep (diagnostic; run on the GPU box):
-   GARB200_PHASE_TIMERS=1 python tools/phase_timers.py c1b 296"""
+   python tools/phase_timers.py c1b 296 [group=1 ...]"""
 import os, sys
-os.environ["GARB200_PHASE_TIMERS"] = "1"
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import bench, garb200_pkg
 garb200_pkg.load()
 from aligator_swk_b200 import capi
 w = dict(bench.WORKLOADS[sys.argv[1]]); B = int(sys.argv[2]) if len(sys.argv) > 2 else w["batch"]
-s = capi.Solver(w["nx"], w["nu"], w["nc"], w["nth"], horizon=w["T"], batch=B)
+s = capi.Solver(w["nx"], w["nu"], w["nc"], w["nth"], horizon=w["T"], batch=B, flags=capi.PHASE_TIMERS)
+s.set_tuning(**{kv.split("=")[0]: int(kv.split("=")[1]) for kv in sys.argv[3:]})
 s.generate(42, 0)
 for _ in range(2):
     s.backward(bench.MU, bench.MU)
