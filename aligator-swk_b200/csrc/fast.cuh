@@ -462,6 +462,125 @@ __device__ __forceinline__ bool ldlt_solve_blocked(int tid, double *S, RH R, dou
 }
 
 // ------------------------------------------------------------------------------------------
+// The same blocked LDL^T split into its two halves so that the FACTORIZATION (a dependent FP64
+// chain: ~30 levels per 4 pivots, no parallelism to speak of) runs on ONE warp beside a GEMM of
+// the other warps, and the SUBSTITUTIONS run one right-hand-side column per thread with the
+// column in registers (depth 2 N FMAs, no barrier, L read as shared-memory broadcasts).
+//
+// ldlt_factor_warp: S (N x N col-major, lower triangle) -> unit-lower L in place, dinv[N].
+//   One warp, __syncwarp only.  Wp: 4 (N - 4) doubles of scratch.
+//   Returns false when the pivots do not have the inertia (+)^NPOS (-)^(N-NPOS), or when a pivot
+//   of the leading (positive) block is numerically zero relative to the largest diagonal entry
+//   (|d_k| <= 1e-13 max_i |S_ii|: a rank-deficient Rhat whose controls are fixed by the constraint
+//   rows only — the unpivoted order would divide by rounding noise; the caller then re-factorises
+//   with the reference's Bunch-Kaufman pivoting, bunchkaufman.hpp:20-167).
+// ------------------------------------------------------------------------------------------
+template <int N, int NPOS = N>
+__device__ __forceinline__ bool ldlt_factor_warp(int lane, double *S, double *Wp, double *dinv) {
+  static_assert(N % 4 == 0 && N - 4 <= 32, "in-warp blocked LDL^T: N % 4 == 0, N <= 36");
+  bool ok = true;
+  double amax = 0.0;
+#pragma unroll
+  for (int i = 0; i < NPOS; i++) amax = fmax(amax, fabs(S[i + i * N]));
+  const double tiny = 1e-13 * amax;
+#pragma unroll 1
+  for (int r0 = 0; r0 < N; r0 += 4) {
+    const double *Dg = S + r0 + r0 * N;
+    const double a00 = Dg[0], a10 = Dg[1], a20 = Dg[2], a30 = Dg[3];
+    const double a11 = Dg[1 + N], a21 = Dg[2 + N], a31 = Dg[3 + N];
+    const double a22 = Dg[2 + 2 * N], a32 = Dg[3 + 2 * N], a33 = Dg[3 + 3 * N];
+    // reciprocal pivots in pairs (2x2 leading minors), see ldlt_solve_blocked
+    const double i0 = __drcp_rn(a00);
+    const double det01 = fma(a00, a11, -a10 * a10);
+    const double i1 = a00 * __drcp_rn(det01);
+    const double l10 = a10 * i0, l20 = a20 * i0, l30 = a30 * i0;
+    const double d1 = det01 * i0;
+    const double w21 = fma(-l20, a10, a21), w31 = fma(-l30, a10, a31);
+    const double l21 = w21 * i1, l31 = w31 * i1;
+    const double d2 = fma(-l21, w21, fma(-l20, a20, a22));
+    const double w32 = fma(-l31, w21, fma(-l30, a20, a32));
+    const double s33 = fma(-l31, w31, fma(-l30, a30, a33));
+    const double i2 = __drcp_rn(d2);
+    const double det23 = fma(d2, s33, -w32 * w32);
+    const double i3 = d2 * __drcp_rn(det23);
+    const double l32 = w32 * i2;
+    const double d3 = det23 * i2;
+    {
+      const double dd[4] = {a00, d1, d2, d3};
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const bool pos = r0 + k < NPOS;
+        const double sk = pos ? dd[k] : -dd[k];
+        if (!(sk > 0.0) || (pos && !(sk > tiny))) ok = false;
+      }
+    }
+    const int nbelow = N - r0 - 4;
+    if (lane < nbelow) {
+      const int i = r0 + 4 + lane;
+      double *row = S + i + r0 * N;
+      const double w0 = row[0];
+      const double l0 = w0 * i0;
+      const double w1 = fma(-l0, a10, row[N]);
+      const double l1 = w1 * i1;
+      const double w2 = fma(-l1, w21, fma(-l0, a20, row[2 * N]));
+      const double l2 = w2 * i2;
+      const double w3 = fma(-l2, w32, fma(-l1, w31, fma(-l0, a30, row[3 * N])));
+      const double l3 = w3 * i3;
+      row[0] = l0; row[N] = l1; row[2 * N] = l2; row[3 * N] = l3;
+      double *wp = Wp + 4 * lane;
+      wp[0] = w0; wp[1] = w1; wp[2] = w2; wp[3] = w3;
+    }
+    __syncwarp();
+    if (lane == 31) {   // every lane has read the unscaled diagonal block
+      double *Dw = S + r0 + r0 * N;
+      Dw[1] = l10; Dw[2] = l20; Dw[3] = l30; Dw[2 + N] = l21; Dw[3 + N] = l31; Dw[3 + 2 * N] = l32;
+      dinv[r0] = i0; dinv[r0 + 1] = i1; dinv[r0 + 2] = i2; dinv[r0 + 3] = i3;
+    }
+    if (nbelow > 0) {
+      const int r1 = r0 + 4;
+      const double *Lp = S + r1 + r0 * N;
+      double *S1 = S + r1 + r1 * N;
+      mma_k4<1, ((N + 3) / 8 < 1 ? 1 : (N + 3) / 8)>(0, lane, nbelow, nbelow, true,
+                 [&](int i, int k) { return -Lp[i + k * N]; },
+                 [&](int k, int j) { return Wp[4 * j + k]; },
+                 [&](int i, int j) { return S1[i + j * N]; },
+                 [&](int i, int j, double v) { S1[i + j * N] = v; });
+    }
+    __syncwarp();
+  }
+  return ok;
+}
+
+// ldlt_solve_cols: X <- (L D L^T)^{-1} X for the NR columns of the accessor R, one column per
+// thread (threads tid < NR), the column held in registers.  Column-oriented (axpy) substitutions:
+// dependent depth 2 N, every L entry is one shared-memory broadcast.  No barrier inside; the
+// caller synchronises before (factor + right-hand sides complete) and after.
+template <int N, int NR, class RH>
+__device__ __forceinline__ void ldlt_solve_cols(int tid, const double *S, const double *dinv, RH R) {
+  if (tid >= NR) return;
+  // (volatile: the L entries are consumed in program order — left free, the scheduler of the fully
+  //  unrolled N = 32 form hoists all 496 loads and spills 4 KB per thread)
+  const volatile double *L = S;
+  double x[N];
+#pragma unroll
+  for (int i = 0; i < N; i++) x[i] = R.get(i, tid);
+#pragma unroll
+  for (int k = 0; k < N - 1; k++) {
+#pragma unroll
+    for (int i = k + 1; i < N; i++) x[i] = fma(-L[i + k * N], x[k], x[i]);
+  }
+#pragma unroll
+  for (int i = 0; i < N; i++) x[i] *= dinv[i];
+#pragma unroll
+  for (int k = N - 1; k > 0; k--) {
+#pragma unroll
+    for (int i = 0; i < k; i++) x[i] = fma(-L[k + i * N], x[k], x[i]);
+  }
+#pragma unroll
+  for (int i = 0; i < N; i++) R.set(i, tid, x[i]);
+}
+
+// ------------------------------------------------------------------------------------------
 // X = E^{-1} entirely in REGISTERS: in-place Gauss-Jordan elimination with row partial
 // pivoting (same pivot rule as PartialPivLU: largest |entry| of the column among the rows not
 // yet used).  LPM lanes own one matrix (8 for N <= 16: four matrices per warp), lane `sub`

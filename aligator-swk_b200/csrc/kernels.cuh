@@ -14,7 +14,7 @@ __host__ __device__ inline void get_work(int horz, int tid, int nthreads, int &b
 
 /// Diagnostic tuning knobs (garb200_set_tuning): read by the LAUNCHERS only, fixed per solver.
 struct Tune {
-  int group = 0;          // problems per CTA of the nx = 36 sweep (0: default = 3 in lockstep, 1: one CTA per problem)
+  int group = 0;          // problems per CTA of the nx = 36 sweep (0/1: one CTA per problem, default; >= 2: 3 in lockstep)
   int einv_mode = 0;      // 0: default pre-pass, 1: register Gauss-Jordan, 2: LU in shared memory (nx = 76)
   int einv_minb = 6;      // min CTAs/SM hint of the small-matrix pre-pass
   int fwd_stages = 2;     // TMA ring depth of the forward rollout

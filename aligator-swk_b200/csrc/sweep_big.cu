@@ -268,14 +268,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
         });
     cta_sync<NT>();
     PH(6);
-    // (6) [Qhat | Shat]^T = [Q | S]^T + [A | B]^T (Vxx A),  Vxx A = AtV^T                (:195-199)
-    //     (mirrored strip assignment: the warps that took two strips in (5) take one here)
-    strip_gemm<n + m, n, n, NW, true, true>(warp, lane,
-        [&](int i, int k) { return __ldg(gAB + k + i * n); },
-        [&](int k, int j) { return X1[j + k * n]; },
-        [&](int i, int j) { return __ldg(gQS + j + i * n); },
-        [&](int i, int j, double v) { Qh[j + i * n] = v; });
-    // Rhat = R + BtV B -> kkt; right-hand sides [-rhat | -Shat^T] in the gains record   (:202-226)
+    // (6a) Rhat = R + BtV B -> kkt (all warps), right-hand side -rhat                       (:199-226)
     auto build_kkt = [&]() {
       mma_gemm<m, m, n, NW>(warp, lane,
           [&](int i, int k) { return BtV[i + k * m]; },
@@ -291,20 +284,39 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
         }
       }
     };
-    auto build_rhs_K = [&]() {   // needs Shat complete: fb(k, j) = -Shat(j, k), the same linear index
+    auto build_rhs_K = [&]() {   // needs Shat complete: fb(k, j) = -Shat(j, k), the same linear index (fallback path)
       for (int e = tid; e < m * n; e += NT) fb[rK * n + e] = -Sh[e];
     };
     build_kkt();
     cta_sync<NT>();
-    for (int i = tid; i < n; i += NT) qv[i] += atvx[i];                           // qhat
-    build_rhs_K();
+    // (6b) [Qhat | Shat]^T = [Q | S]^T + [A | B]^T (Vxx A),  Vxx A = AtV^T  on warps 1..NW-1   (:195-199)
+    //      (-Shat^T goes straight into the K rows of the right-hand side), while
+    // (7a) warp 0 factorises Rhat: blocked LDL^T, a dependent FP64 chain that needs nothing else  (:202-208)
+    int *kkt_ok = reinterpret_cast<int *>(red + NW);
+    if (warp == 0) {
+      const bool okf = ldlt_factor_warp<sp, m>(lane, kkt, P, dinv);     // P[0, 4 sp): Vxx is consumed
+      if (lane == 0) *kkt_ok = okf ? 1 : 0;
+    } else {
+      strip_gemm<n + m, n, n, NW - 1, true, true>(warp - 1, lane,
+          [&](int i, int k) { return __ldg(gAB + k + i * n); },
+          [&](int k, int j) { return X1[j + k * n]; },
+          [&](int i, int j) { return __ldg(gQS + j + i * n); },
+          [&](int i, int j, double v) {
+            Qh[j + i * n] = v;
+            if (i >= n) fb[rK * n + j + (i - n) * n] = -v;
+          });
+      for (int i = tid - 32; i < n; i += NT - 32) qv[i] += atvx[i];                 // qhat
+    }
     cta_sync<NT>();
     PH(7);
-    // (7) reduced KKT system Rhat [K kff] = rhs: blocked LDL^T with inertia check, Bunch-Kaufman
-    //     (bunchkaufman.hpp:20-167, 447-516) as the fallback                             (:202-228)
+    // (7b) [K kff] = Rhat^{-1} rhs, one right-hand-side column per thread; Bunch-Kaufman
+    //      (bunchkaufman.hpp:20-167, 447-516) when the factorization failed its checks      (:210-228)
     {
-      const bool okk = ldlt_solve_blocked<sp, na, NT, m>(tid, kkt, RhsGainsTh<n, 0, s>{ff, fb, nullptr}, P, P + 4 * sp);
-      if (!okk) {
+      const bool okk = *kkt_ok != 0;
+      if (okk) {
+        ldlt_solve_cols<sp, na>(tid, kkt, dinv, RhsGainsTh<n, 0, s>{ff, fb, nullptr});
+        cta_sync<NT>();
+      } else {
         build_kkt();
         build_rhs_K();
         cta_sync<NT>();

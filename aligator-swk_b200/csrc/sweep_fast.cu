@@ -10,6 +10,7 @@
 //                  (NW warps) per problem, knot record + Einv staged by 1-D TMA bulk copies,
 //                  all n^3 contractions on the FP64 tensor pipe (DMMA), GEMVs riding along
 //                  as an extra column of the GEMM they belong to.
+#include <type_traits>
 #include "fast.cuh"
 #include "kernels.cuh"
 
@@ -432,64 +433,81 @@ sweep_kernel(const DevParams p) {
         });
     cta_sync<NT, GRP>();
     PH(6);
-    // (6) [Qhat | Shat] = [Q | S] + AtV [A | B] (in place) ; Rhat = R + BtV B -> kkt   (:195-199)
-    mma_gemm<n, n + m, n, NW>(warp, lane,
-        [&](int i, int k) { return X1[i + k * n]; },
-        [&](int k, int j) { return A[k + j * n]; },
-        [&](int i, int j) { return Q[i + j * n]; },           // [Q | S] contiguous as well
-        [&](int i, int j, double v) { Q[i + j * n] = v; });
-    // Rhat = R + BtV B -> kkt, the constraint rows [D  -mueq I], and the right-hand sides
-    // [-rhat | -Shat^T ; -d | -C] in the gains record                              (:202-226)
-    auto build_kkt = [&]() {
-      mma_gemm<m, m, n, NW>(warp, lane,
+    // (6) [Qhat | Shat] = [Q | S] + AtV [A | B] (in place)                                  (:195-199)
+    //     on the first NWG warps, with -Shat^T going straight into the K rows of the right-hand side;
+    // (7a) meanwhile the LAST warp builds the reduced KKT matrix [Rhat D^T; D -mueq I] (Rhat = R + BtV B)
+    //     and factorises it (blocked LDL^T in natural order, inertia + rank check) — a dependent FP64
+    //     chain that needs only BtV, so it runs beside the big GEMM instead of after it.       (:202-208)
+    constexpr int NWG = NW > 1 ? NW - 1 : 1;          // GEMM warps
+    constexpr int FW = NW - 1;                         // factor warp (NW == 1: the one warp does both in turn)
+    int *kkt_ok = reinterpret_cast<int *>(red + NW);   // red has 16 doubles, NW <= 8
+    auto kkt_matrix = [&](auto nwc, int w, int t0, int nt) {   // by decltype(nwc)::value warps (this one is w) = nt threads (this one is t0)
+      mma_gemm<m, m, n, decltype(nwc)::value>(w, lane,
           [&](int i, int k) { return BtV[i + k * m]; },
           [&](int k, int j) { return B[k + j * n]; },
           [&](int i, int j) { return R[i + j * m]; },
           [&](int i, int j, double v) { kkt[i + j * sp] = v; });
-      for (int i = tid; i < m; i += NT) ff[rK + i] = -(rv[i] + btvx[i]);          // -rhat
       if constexpr (c > 0) {
         constexpr int cc = c > 0 ? c : 1;
-        for (int i = tid; i < c; i += NT) ff[rZ + i] = -d[i];
-        for (int e = tid; e < c * s; e += NT) {
+        for (int e = t0; e < c * s; e += nt) {
           const int i = e % cc, j = e / cc;
           kkt[(m + i) + j * sp] = (j < m) ? D[i + j * c] : ((j - m == i) ? -mueq : 0.0);
         }
-        for (int e = tid; e < c * n; e += NT) { const int i = e % cc, j = e / cc; fb[(rZ + i) * n + j] = -C[i + j * c]; }
       }
       if constexpr (sp > s) {        // padding rows of the blocked LDL^T: -I, decoupled
         constexpr int pr = sp - s > 0 ? sp - s : 1;
-        for (int e = tid; e < (sp - s) * sp; e += NT) {
+        for (int e = t0; e < (sp - s) * sp; e += nt) {
           const int i = s + e % pr, j = e / pr;
           kkt[i + j * sp] = (i == j) ? -1.0 : 0.0;
         }
       }
-      if constexpr (h > 0) {         // [-Guhat ; 0],  Guhat = Gu + B^T Lth0                  (:264-272)
-        for (int e = tid; e < m * h; e += NT) { const int i = e / hh, j = e % hh; fth[(rK + i) * h + j] = -((LEG ? 0.0 : Gu[i + j * m]) + BtVth[i + j * m]); }
-        for (int e = tid; e < c * h; e += NT) fth[rZ * h + e] = 0.0;
+    };
+    auto kkt_rhs = [&](int t0, int nt) {     // [-rhat | . ; -d | -C], theta columns [-Guhat ; 0]     (:210-226, 264-272)
+      for (int i = t0; i < m; i += nt) ff[rK + i] = -(rv[i] + btvx[i]);          // -rhat
+      if constexpr (c > 0) {
+        constexpr int cc = c > 0 ? c : 1;
+        for (int i = t0; i < c; i += nt) ff[rZ + i] = -d[i];
+        for (int e = t0; e < c * n; e += nt) { const int i = e % cc, j = e / cc; fb[(rZ + i) * n + j] = -C[i + j * c]; }
+      }
+      if constexpr (h > 0) {
+        for (int e = t0; e < m * h; e += nt) { const int i = e / hh, j = e % hh; fth[(rK + i) * h + j] = -((LEG ? 0.0 : Gu[i + j * m]) + BtVth[i + j * m]); }
+        for (int e = t0; e < c * h; e += nt) fth[rZ * h + e] = 0.0;
       }
     };
-    auto build_rhs_K = [&]() {   // needs Shat complete
+    auto build_rhs_K = [&]() {   // needs Shat complete (fallback path only)
       for (int e = tid; e < m * n; e += NT) { const int i = e / n, j = e % n; fb[(rK + i) * n + j] = -S[j + i * n]; }
     };
-    build_kkt();
-    for (int i = tid; i < n; i += NT) qv[i] += atvx[i];                           // qhat
-    cta_sync<NT, GRP>();
-    build_rhs_K();
-    // (7) reduced KKT system [Rhat D^T; D -mueq I] [K kff; Z zff] = rhs                  (:202-228)
-    // The matrix is quasi-definite whenever Rhat > 0 (any convex stage): LDL^T in the natural
-    // order exists and its pivots are (+)^m (-)^c.  That inertia is verified pivot by pivot; a
-    // knot that fails the check is rebuilt and factorised with the reference's Bunch-Kaufman
-    // pivoting instead (bunchkaufman.hpp:20-167, 447-516).
+    if (NW == 1 || warp < NWG) {
+      mma_gemm<n, n + m, n, NWG>(warp, lane,
+          [&](int i, int k) { return X1[i + k * n]; },
+          [&](int k, int j) { return A[k + j * n]; },
+          [&](int i, int j) { return Q[i + j * n]; },           // [Q | S] contiguous as well
+          [&](int i, int j, double v) {
+            Q[i + j * n] = v;
+            if (j >= n) fb[(rK + (j - n)) * n + i] = -v;        // -Shat^T: right-hand side of K
+          });
+      kkt_rhs(tid, 32 * NWG);
+      for (int i = tid; i < n; i += 32 * NWG) qv[i] += atvx[i];                   // qhat
+    }
+    if (warp == FW) {
+      kkt_matrix(std::integral_constant<int, 1>{}, 0, lane, 32);
+      __syncwarp();
+      const bool okf = ldlt_factor_warp<sp, m>(lane, kkt, P, dinv);     // P[0, 4 sp): Vxx is consumed
+      if (lane == 0) *kkt_ok = okf ? 1 : 0;
+    }
     PH(7);
-    if constexpr (GRP > 1) __syncthreads();     // all groups enter the KKT chains together (see the kernel comment)
+    if constexpr (GRP > 1) __syncthreads();
     else cta_sync<NT, GRP>();
     PH(8);
+    // (7b) [K kff; Z zff] = KKT^{-1} rhs: one right-hand-side column per thread               (:210-228)
     {
-      // blocked LDL^T solve (backward stable; an explicit inverse of Rhat was measurably less
-      // accurate on the ill-conditioned knots of the reference distribution)
-      const bool okk = ldlt_solve_blocked<sp, na, NT, m, GRP>(tid, kkt, RhsGainsTh<n, h, s>{ff, fb, fth}, P, P + 4 * sp);
-      if (!okk) {                     // uniform: every thread computed the same pivots
-        build_kkt();
+      const bool okk = *kkt_ok != 0;
+      if (okk) {
+        ldlt_solve_cols<sp, na>(tid, kkt, dinv, RhsGainsTh<n, h, s>{ff, fb, fth});
+        cta_sync<NT, GRP>();
+      } else {                        // uniform: rebuild and factorise with the reference's Bunch-Kaufman pivoting
+        kkt_matrix(std::integral_constant<int, NW>{}, warp, tid, NT);
+        kkt_rhs(tid, NT);
         build_rhs_K();
         cta_sync<NT, GRP>();
         if (warp == 0) {
@@ -948,7 +966,9 @@ int launch_backward_fast(const DevParams &p, const int *h_nu_t, const int *h_nc_
   }
   if (p.nx == 12 && p.nu == 4 && p.nc == 0 && p.nth == 0) return launch_fast_t<12, 4, 0, 0, 1>(p, st);
   if (p.nx == 36 && p.nu == 12 && p.nc == 0 && p.nth == 0) {
-    return p.tune.group == 1 ? launch_fast_t<36, 12, 0, 0, 5>(p, st) : launch_fast_t<36, 12, 0, 0, 5, false, 3>(p, st);
+    // lockstep groups of 3 problems per CTA are opt-in: measured SLOWER than 3 independent CTAs per SM
+    // (c1b 28.4 vs 22.5 ms backward: the alignment barrier costs more than the chains gain)
+    return p.tune.group >= 2 ? launch_fast_t<36, 12, 0, 0, 5, false, 3>(p, st) : launch_fast_t<36, 12, 0, 0, 5>(p, st);
   }
   if (p.nx == 36 && p.nu == 12 && p.nc == 6 && p.nth == 4) {   // C3: E^{-1} from L2 -> 75 KB of shared memory, 3 CTAs per SM
     return p.tune.c3_eg ? launch_fast_t<36, 12, 6, 4, 5, true>(p, st) : launch_fast_t<36, 12, 6, 4, 5, false>(p, st);

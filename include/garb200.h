@@ -98,7 +98,7 @@ const char *garb200_version(void);
 
 /* Diagnostic tuning knobs, read by the kernel launchers of this solver only (no environment
  * variables anywhere in the library).  Names: "group" (problems per CTA of the nx = 36 sweep:
- * 0 default, 1 one CTA per problem), "einv_mode", "einv_minb", "fwd_stages", "condensed",
+ * 0/1 one CTA per problem (default), >= 2 three problems in lockstep), "einv_mode", "einv_minb", "fwd_stages", "condensed",
  * "c3_eg", "legs_generic", "explicit_dyn" (0: never take the E = -I path). */
 int garb200_set_tuning(garb200_solver *s, const char *name, int value);
 /* Run subsequent kernels/copies on this CUDA stream (a cudaStream_t, passed as void*). */

@@ -48,15 +48,15 @@ def _check(oracle, pp, mu, xs, us, vs, lb, theta=None, rtol=RTOL):
 
 @pytest.mark.parametrize("batch", [1, 2, 7], ids=lambda b: "B%d" % b)
 def test_c1_full_size_lockstep_groups(capi, oracle, batch):
-    """C1 / c1b: nx=36 nu=12 T=100, mu = 1e-11.  Batches that are not a multiple of the 3 problems a
-    CTA solves in lockstep (the padding groups re-solve the last problem), and the one-CTA-per-problem
-    launch of the same kernel must give the same bits."""
+    """C1 / c1b: nx=36 nu=12 T=100, mu = 1e-11, default launch (one CTA per problem) vs the oracle; the
+    opt-in lockstep launch (3 problems per CTA; batches that are not a multiple of 3 pad with a group that
+    re-solves the last problem) must give the same bits."""
     pp = generate_problems(batch, 100, 36, 12, seed=100 + batch)
     s, xs, us, vs, lb = _solve(capi, pp, 1e-11)
     assert s.used_fast_path()
     _check(oracle, pp, 1e-11, xs, us, vs, lb)
     g3 = s.download_gains()
-    s1, xs1, us1, vs1, lb1 = _solve(capi, pp, 1e-11, group=1)
+    s1, xs1, us1, vs1, lb1 = _solve(capi, pp, 1e-11, group=3)
     assert np.array_equal(xs, xs1) and np.array_equal(us, us1) and np.array_equal(lb, lb1)
     assert np.array_equal(g3, s1.download_gains())
     s.close(); s1.close()
@@ -185,4 +185,27 @@ def test_forward_is_const_repeated_theta(capi, oracle):
         theta = rng.standard_normal((B, nth)) * (rep + 1)
         xs, us, vs, lb = s.forward(theta)
         _check(oracle, pp, mu, xs, us, vs, lb, theta, rtol=1e-9)
+    s.close()
+
+
+def test_tiny_positive_pivot_falls_back_to_bunch_kaufman(capi, oracle):
+    """ADVICE r1 / VERDICT 2(e): a rank-deficient PSD Rhat whose control is determined only through
+    the constraint rows D.  R(0,0) = 1e-18 with S(:,0) = B(:,0) = 0 gives a tiny POSITIVE first
+    pivot: it passes the inertia check, and the unpivoted LDL^T would divide by rounding noise.  The
+    rank guard of ldlt_factor_warp must hand the knot to Bunch-Kaufman (which pivots with the D rows,
+    bunchkaufman.hpp:20-167) and the result must match the oracle."""
+    nx, nu, nc, nth, T, mu = 36, 12, 6, 4, 10, 1e-9
+    pp = generate_problems(3, T, nx, nu, nc, nth, seed=91, dist="explicit")
+    o = pp.layout.offsets
+    k = pp.knots[1, 4]
+    R = k[o["R"]: o["R"] + nu * nu].reshape(nu, nu, order="F")
+    R[0, :] = 0.0; R[:, 0] = 0.0; R[0, 0] = 1e-18
+    k[o["R"]: o["R"] + nu * nu] = R.reshape(-1, order="F")
+    k[o["S"]: o["S"] + nx] = 0.0                       # S(:, 0)
+    k[o["B"]: o["B"] + nx] = 0.0                       # B(:, 0)
+    k[o["Gu"]: o["Gu"] + nu * nth].reshape(nu, nth, order="F")[0, :] = 0.0
+    theta = np.random.default_rng(2).standard_normal((3, nth))
+    s, xs, us, vs, lb = _solve(capi, pp, mu, theta)
+    assert s.used_fast_path()
+    _check(oracle, pp, mu, xs, us, vs, lb, theta, rtol=1e-9)
     s.close()
