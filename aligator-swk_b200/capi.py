@@ -55,6 +55,7 @@ SYMBOLS = [
     "garb200_kkt_error", "garb200_upload_trajectory", "garb200_kernel_launches", "garb200_last_timings",
     "garb200_fp64_peak", "garb200_timing_log_start", "garb200_timing_log_read",
     "garb200_used_fast_path", "garb200_phase_cycles", "garb200_set_tuning",
+    "garb200_kkt_error_noalloc",
 ]
 
 
@@ -78,6 +79,7 @@ def lib():
             getattr(L, name).argtypes = [C.c_void_p] * 6 if name == "garb200_forward_device" else [C.c_void_p] * 6
         L.garb200_upload_packed.argtypes = [C.c_void_p] * 4
         L.garb200_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+        L.garb200_kkt_error_noalloc.argtypes = [C.c_void_p] * 9 + [C.c_double, C.c_double, C.c_void_p, C.c_void_p]
         L.garb200_set_tuning.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
         L.garb200_synchronize.argtypes = [C.c_void_p]
         L.garb200_destroy.argtypes = [C.c_void_p]
@@ -136,6 +138,29 @@ def fp64_peak(device=0, kind=0) -> float:
     out = C.c_double(0.0)
     check(lib().garb200_fp64_peak(device, kind, C.byref(out)))
     return out.value
+
+
+NOALLOC_SCRATCH_BYTES = 1 << 20
+
+
+def kkt_error_noalloc(nx, nu, nc, nth, horizon, nc0, batch, d_knots, d_G0, d_g0, d_xs, d_us, d_vs, d_lbdas,
+                      mudyn, mueq, d_theta=None, nu_t=None, nc_t=None, nu_term=0, nc_term=0, device=0,
+                      stream=None):
+    """garb200_kkt_error_noalloc: lqrComputeKktError on DEVICE pointers, no handle, no allocation
+    (static device scratch of NOALLOC_SCRATCH_BYTES).  -> host array [batch][3]."""
+    cfg = Config()
+    cfg.nx, cfg.nu, cfg.nc, cfg.nth = nx, nu, nc, nth
+    cfg.horizon, cfg.nc0, cfg.batch, cfg.device = horizon, nc0, batch, device
+    a = None if nu_t is None else np.ascontiguousarray(nu_t, dtype=np.int32)
+    b = None if nc_t is None else np.ascontiguousarray(nc_t, dtype=np.int32)
+    cfg.nu_t = None if a is None else a.ctypes.data_as(_ip)
+    cfg.nc_t = None if b is None else b.ctypes.data_as(_ip)
+    cfg.nu_term, cfg.nc_term = nu_term, nc_term
+    out = np.zeros((batch, 3))
+    check(lib().garb200_kkt_error_noalloc(C.byref(cfg), _ptr(d_knots), _ptr(d_G0), _ptr(d_g0), _ptr(d_xs),
+                                          _ptr(d_us), _ptr(d_vs), _ptr(d_lbdas), _ptr(d_theta),
+                                          float(mudyn), float(mueq), _ptr(stream), _ptr(out)))
+    return out
 
 
 class Solver:

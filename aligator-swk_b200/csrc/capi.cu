@@ -14,6 +14,7 @@ using namespace garb200;
 
 static thread_local std::string g_err;
 static int fail(int code, const std::string &msg) { g_err = msg; return code; }
+namespace garb200 { int set_error(int code, const std::string &msg) { return fail(code, msg); } }   // for noalloc.cu
 #define CK(call)                                                                              \
   do {                                                                                        \
     cudaError_t e_ = (call);                                                                  \

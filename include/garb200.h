@@ -182,6 +182,29 @@ int garb200_cycle_append(garb200_solver *s, const garb200_knot_view *knots, int 
 int garb200_kkt_error(garb200_solver *s, double mudyn, double mueq, const double *theta,
                       double *out);
 
+/* ---- allocation-free variant of the metric -------------------------------------------------
+ * This entry point has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same kernel and same numbers as garb200_kkt_error, but no
+ * solver handle and no allocation of any kind: the kernel's scratch (per-knot nu_t / nc_t arrays,
+ * [batch][3] result staging — cudaMalloc'd by garb200_create on the handle path) lives in ONE static
+ * __device__ array of GARB200_NOALLOC_SCRATCH_BYTES per GPU, held from library load until exit.
+ *   dims      nx, nu, nc, nth, horizon, nc0, batch, device, nu_t/nc_t (host, or NULL -> nu_term/
+ *             nc_term) are read; num_legs and flags are ignored
+ *   d_*       DEVICE pointers: packed knots [batch][T+1][stride] in logical time order
+ *             (garb200_layout.h), G0 [batch][nc0*nx], g0 [batch][nc0], trajectories laid out as at the
+ *             top of this file, theta [batch][nth] or NULL
+ *   out       HOST [batch][3] = {dyn, cstr, dual}; the call returns after the stream has drained
+ * Limit: 256-rounded 8 (T+1) bytes + 24 batch bytes <= GARB200_NOALLOC_SCRATCH_BYTES, otherwise
+ * GARB200_ERR_INVALID with the sizes in garb200_last_error() (e.g. T = 50: batch <= 43 667).
+ * The array is shared by every call on a device and keeps the last call's contents (each call
+ * rewrites what it reads and zeroes the result staging first): calls that OVERLAP on one GPU race. */
+#define GARB200_NOALLOC_SCRATCH_BYTES (1u << 20)
+int garb200_kkt_error_noalloc(const garb200_config *dims, const double *d_knots, const double *d_G0,
+                              const double *d_g0, const double *d_xs, const double *d_us,
+                              const double *d_vs, const double *d_lbdas, const double *d_theta,
+                              double mudyn, double mueq, void *cuda_stream, double *out);
+
 /* Host trajectory -> solver-owned device buffers (so garb200_kkt_error can score a solution
  * that was produced elsewhere, like the reference's free function does). */
 int garb200_upload_trajectory(garb200_solver *s, const double *xs, const double *us,
