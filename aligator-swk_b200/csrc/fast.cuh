@@ -13,6 +13,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <type_traits>
 #include "device_linalg.cuh"
 
 namespace garb200 {
@@ -578,6 +579,53 @@ __device__ __forceinline__ void ldlt_solve_cols(int tid, const double *S, const 
   }
 #pragma unroll
   for (int i = 0; i < N; i++) R.set(i, tid, x[i]);
+}
+
+// ldlt_solve_lanes: the same substitutions with every right-hand-side column spread over LPC
+// lanes of a warp (LPC = 4, 2 or 1: the largest with LPC * NR <= NT).  Lane q of a column's group
+// owns rows q, q + LPC, ...; at step k the owner broadcasts x_k with one shuffle and every lane
+// updates its own rows: still 2 N dependent steps, but each is one shuffle + ONE predicated FMA
+// deep instead of N - k FMAs, and LPC * NR threads (all warps of the CTA) work instead of NR.
+// All lanes of a participating warp execute the shuffles (lanes past the last column run a clamped
+// duplicate and store nothing).  No barrier inside.
+template <int N, int NR, int NT, class RH>
+__device__ __forceinline__ void ldlt_solve_lanes(int tid, const double *S, const double *dinv, RH R) {
+  constexpr int LPC = (4 * NR <= NT) ? 4 : (2 * NR <= NT) ? 2 : 1;
+  if constexpr (LPC == 1) { ldlt_solve_cols<N, NR>(tid, S, dinv, R); return; }
+  constexpr int RP = (N + LPC - 1) / LPC;          // rows per lane
+  if ((tid & ~31) >= LPC * NR) return;             // whole warps past the last column
+  const int lane = tid & 31, q = lane & (LPC - 1), gbase = lane & ~(LPC - 1);
+  const bool live = tid < LPC * NR;
+  const int col = live ? tid / LPC : NR - 1;
+  using LT = typename std::conditional<(N > 16), const volatile double, const double>::type;
+  LT *L = S;                                       // (large N: keep the loads in program order, see ldlt_solve_cols)
+  double x[RP];
+#pragma unroll
+  for (int r = 0; r < RP; r++) { const int i = r * LPC + q; x[r] = i < N ? R.get(i, col) : 0.0; }
+#pragma unroll
+  for (int k = 0; k < N - 1; k++) {
+    const double xk = __shfl_sync(0xffffffffu, x[k / LPC], gbase + (k % LPC));
+#pragma unroll
+    for (int r = k / LPC; r < RP; r++) {
+      const int i = r * LPC + q;
+      if (i > k && i < N) x[r] = fma(-L[i + k * N], xk, x[r]);
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < RP; r++) { const int i = r * LPC + q; if (i < N) x[r] *= dinv[i]; }
+#pragma unroll
+  for (int k = N - 1; k > 0; k--) {
+    const double xk = __shfl_sync(0xffffffffu, x[k / LPC], gbase + (k % LPC));
+#pragma unroll
+    for (int r = 0; r <= k / LPC; r++) {
+      const int i = r * LPC + q;
+      if (i < k) x[r] = fma(-L[k + i * N], xk, x[r]);
+    }
+  }
+  if (live) {
+#pragma unroll
+    for (int r = 0; r < RP; r++) { const int i = r * LPC + q; if (i < N) R.set(i, col, x[r]); }
+  }
 }
 
 // ------------------------------------------------------------------------------------------

@@ -503,7 +503,7 @@ sweep_kernel(const DevParams p) {
     {
       const bool okk = *kkt_ok != 0;
       if (okk) {
-        ldlt_solve_cols<sp, na>(tid, kkt, dinv, RhsGainsTh<n, h, s>{ff, fb, fth});
+        ldlt_solve_lanes<sp, na, NT>(tid, kkt, dinv, RhsGainsTh<n, h, s>{ff, fb, fth});
         cta_sync<NT, GRP>();
       } else {                        // uniform: rebuild and factorise with the reference's Bunch-Kaufman pivoting
         kkt_matrix(std::integral_constant<int, NW>{}, warp, tid, NT);

@@ -41,7 +41,7 @@ def _both(capi, pp, s, mu, theta=None):
     d_xs, d_us, d_vs, d_lb = s.device_trajectory()
     th_t = None
     if theta is not None:                  # the caller's own device buffer for theta (an INPUT)
-        th_t = torch.as_tensor(np.ascontiguousarray(np.broadcast_to(theta, (s.batch, s.nth))), device="cuda")
+        th_t = torch.as_tensor(np.array(np.broadcast_to(theta, (s.batch, s.nth))), device="cuda")
         torch.cuda.synchronize()
     ragged = not (np.all(pp.nu_t[:-1] == s.nu) and np.all(pp.nc_t[:-1] == s.nc))
     got = capi.kkt_error_noalloc(
