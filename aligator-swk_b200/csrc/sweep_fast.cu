@@ -396,8 +396,11 @@ sweep_kernel(const DevParams p) {
     cta_sync<NT, GRP>();
     PH(3);
     // (4) [Vxx | vx] = Lambda^{-1} [Ptilde | w]                                      (:185-190)
+    //     Neumann form: the product lands in the X1 block and STAYS there (no copy back): from here to
+    //     step (10) `VX` is the block holding [Vxx | vx | Lth0] (later [A_pre | tv | Yth_pre]) and `AT`
+    //     the other one, which receives AtV.  LDL^T form: solved in place in the P block.
     if (neumann) {
-      mma_gemm<n, na, n, NW>(warp, lane,
+      mma_gemm<n, na, n, NW>(warp, lane,      // (lower-triangle tiles only was measured slower: it loses the strip-mode fragment reuse)
           [&](int i, int k) { return -mudyn * P[i + k * n]; },
           [&](int k, int j) { return P[k + j * n]; },
           [&](int i, int j) { return P[i + j * n]; },
@@ -405,30 +408,28 @@ sweep_kernel(const DevParams p) {
             if (j >= n || i >= j) X1[i + j * n] = v;
             if (j < n && i > j) X1[j + i * n] = v;
           });
-      cta_sync<NT, GRP>();
       PH(4);
-      static_assert((n * na) % 2 == 0, "vector copy");
-      for (int e = tid; e < n * na / 2; e += NT)              // back into P
-        reinterpret_cast<double2 *>(P)[e] = reinterpret_cast<const double2 *>(X1)[e];
     } else {
       if (!ldlt_solve_blocked<n, na, NT, n, GRP>(tid, X1, RhsColMajor<n>{P}, Gs, dinv)) flags |= GARB200_FLAG_LLT_NOT_PD;
       PH(4);
       mirror_lower_ct<n, NT>(tid, P);
     }
+    double *const VX = neumann ? X1 : P, *const AT = neumann ? P : X1;
+    double *const vxv = VX + n * n, *const VXth = VX + n * (n + 1);
     cta_sync<NT, GRP>();
     PH(5);
     if (p.store_all_values) {
       double *v = p.values + ((size_t)b * p.nslots + (t + 1)) * p.VL.stride;
-      for (int e = tid; e < n * n; e += NT) v[p.VL.Vxx + e] = P[e];
-      for (int i = tid; i < n; i += NT) v[p.VL.vx + i] = pv[i];
+      for (int e = tid; e < n * n; e += NT) v[p.VL.Vxx + e] = VX[e];
+      for (int i = tid; i < n; i += NT) v[p.VL.vx + i] = vxv[i];
     }
-    // (5) [AtV ; BtV] = [A | B]^T [Vxx | vx]: rows < n -> X1 (+ A^T vx), rows >= n -> BtV (+ B^T vx)
+    // (5) [AtV ; BtV] = [A | B]^T [Vxx | vx]: rows < n -> AT (+ A^T vx), rows >= n -> BtV (+ B^T vx)
     mma_gemm<n + m, na, n, NW>(warp, lane,
         [&](int i, int k) { return A[k + i * n]; },           // [A | B] is one n x (n+m) col-major block
-        [&](int k, int j) { return P[k + j * n]; },
+        [&](int k, int j) { return VX[k + j * n]; },
         [](int, int) { return 0.0; },
         [&](int i, int j, double v) {
-          if (i < n) { if (j < n) X1[i + j * n] = v; else if (j == n) atvx[i] = v; }   // A^T Lth0 is not needed
+          if (i < n) { if (j < n) AT[i + j * n] = v; else if (j == n) atvx[i] = v; }   // A^T Lth0 is not needed
           else BtV[(i - n) + j * m] = v;                                             // B^T [Vxx | vx | Lth0]
         });
     cta_sync<NT, GRP>();
@@ -479,7 +480,7 @@ sweep_kernel(const DevParams p) {
     };
     if (NW == 1 || warp < NWG) {
       mma_gemm<n, n + m, n, NWG>(warp, lane,
-          [&](int i, int k) { return X1[i + k * n]; },
+          [&](int i, int k) { return AT[i + k * n]; },
           [&](int k, int j) { return A[k + j * n]; },
           [&](int i, int j) { return Q[i + j * n]; },           // [Q | S] contiguous as well
           [&](int i, int j, double v) {
@@ -492,7 +493,7 @@ sweep_kernel(const DevParams p) {
     if (warp == FW) {
       kkt_matrix(std::integral_constant<int, 1>{}, 0, lane, 32);
       __syncwarp();
-      const bool okf = ldlt_factor_warp<sp, m>(lane, kkt, P, dinv);     // P[0, 4 sp): Vxx is consumed
+      const bool okf = ldlt_factor_warp<sp, m>(lane, kkt, VX, dinv);    // VX[0, 4 sp): Vxx is consumed
       if (lane == 0) *kkt_ok = okf ? 1 : 0;
     }
     PH(7);
@@ -510,14 +511,16 @@ sweep_kernel(const DevParams p) {
         kkt_rhs(tid, NT);
         build_rhs_K();
         cta_sync<NT, GRP>();
+        double *const ksb = EG ? VX + 128 : ksub;                 // EG: scratch inside the dead Vxx block
+        int *const kpv = EG ? reinterpret_cast<int *>(VX + 128 + PL::KS) : kpiv;
         if (warp == 0) {
-          if (!bk_factor_warp(lane, s, kkt, sp, kpiv, ksub)) flags |= GARB200_FLAG_BK_SINGULAR;
+          if (!bk_factor_warp(lane, s, kkt, sp, kpv, ksb)) flags |= GARB200_FLAG_BK_SINGULAR;
         }
         cta_sync<NT, GRP>();
         for (int col = tid; col < na; col += NT) {
-          if (col == 0) bk_solve_column(s, kkt, sp, kpiv, ksub, ff, 1);
-          else if (col <= n) bk_solve_column(s, kkt, sp, kpiv, ksub, fb + (col - 1), n);
-          else bk_solve_column(s, kkt, sp, kpiv, ksub, fth + (col - n - 1), h);
+          if (col == 0) bk_solve_column(s, kkt, sp, kpv, ksb, ff, 1);
+          else if (col <= n) bk_solve_column(s, kkt, sp, kpv, ksb, fb + (col - 1), n);
+          else bk_solve_column(s, kkt, sp, kpv, ksb, fth + (col - n - 1), h);
         }
         cta_sync<NT, GRP>();
       }
@@ -525,16 +528,16 @@ sweep_kernel(const DevParams p) {
     PH(9);
     // (8) lff = vx + BtV^T kff ; tv = f + B kff - mudyn lff -> pv slot                  (:231-236)
     for (int i = tid; i < n; i += NT) {
-      double l = pv[i], tb = f[i];
+      double l = vxv[i], tb = f[i];
 #pragma unroll
       for (int k = 0; k < m; k++) { l = fma(BtV[k + i * m], ff[rK + k], l); tb = fma(B[i + k * n], ff[rK + k], tb); }
       ff[rL + i] = l;
-      pv[i] = tb - mudyn * l;
+      vxv[i] = tb - mudyn * l;
     }
     if constexpr (h > 0) {          // Lth = Lth0 + BtV^T Kth ; Yth_pre = B Kth - mudyn Lth        (:274-280)
       for (int e = tid; e < n * h; e += NT) {
         const int i = e % n, j = e / n;
-        double l = Pth[i + j * n], tb = 0.0;
+        double l = VXth[i + j * n], tb = 0.0;
 #pragma unroll
         for (int k = 0; k < m; k++) {
           const double kth = fth[(rK + k) * h + j];
@@ -542,7 +545,7 @@ sweep_kernel(const DevParams p) {
           tb = fma(B[i + k * n], kth, tb);
         }
         fth[(rL + i) * h + j] = l;
-        Pth[i + j * n] = tb - mudyn * l;
+        VXth[i + j * n] = tb - mudyn * l;
       }
     }
     // (9) L = AtV^T + BtV^T K  (Vxx A == AtV^T: Vxx is exactly symmetric) -> fb rows rL     (:238-239)
@@ -562,7 +565,7 @@ sweep_kernel(const DevParams p) {
           for (int u = 0; u < TN; u++) {
             jbk[u] = min(u * 8 + g, n - 1);
             const int jc = u * 8 + 2 * q, j0 = min(jc, n - 1), j1 = min(jc + 1, n - 1);
-            l0[u] = X1[j0 + ia * n]; l1[u] = X1[j1 + ia * n];
+            l0[u] = AT[j0 + ia * n]; l1[u] = AT[j1 + ia * n];
             a0[u] = A[ia + j0 * n];  a1[u] = A[ia + j1 * n];
           }
 #pragma unroll
@@ -582,8 +585,8 @@ sweep_kernel(const DevParams p) {
             const int jc = u * 8 + 2 * q;
             if (ic < n && jc < n) {
               *reinterpret_cast<double2 *>(gfbg + (rL + ic) * n + jc) = make_double2(l0[u], l1[u]);
-              P[ic + jc * n] = a0[u] - mudyn * l0[u];
-              P[ic + (jc + 1) * n] = a1[u] - mudyn * l1[u];
+              VX[ic + jc * n] = a0[u] - mudyn * l0[u];
+              VX[ic + (jc + 1) * n] = a1[u] - mudyn * l1[u];
             }
           }
         }
@@ -598,7 +601,7 @@ sweep_kernel(const DevParams p) {
         ia[u] = min(ti * 8 + g, n - 1);
         jbk[u] = min(tj * 8 + g, n - 1);
         const int jc = tj * 8 + 2 * q, j0 = min(jc, n - 1), j1 = min(jc + 1, n - 1);
-        l0[u] = X1[j0 + ia[u] * n]; l1[u] = X1[j1 + ia[u] * n];       // AtV^T
+        l0[u] = AT[j0 + ia[u] * n]; l1[u] = AT[j1 + ia[u] * n];       // AtV^T
         a0[u] = A[ia[u] + j0 * n];  a1[u] = A[ia[u] + j1 * n];
       }
 #pragma unroll
@@ -627,8 +630,8 @@ sweep_kernel(const DevParams p) {
           const int ic = ti * 8 + g, jc = tj * 8 + 2 * q;
           if (ic < n && jc < n) {
             *reinterpret_cast<double2 *>(gfbg + (rL + ic) * n + jc) = make_double2(l0[u], l1[u]);
-            P[ic + jc * n] = a0[u] - mudyn * l0[u];
-            P[ic + (jc + 1) * n] = a1[u] - mudyn * l1[u];
+            VX[ic + jc * n] = a0[u] - mudyn * l0[u];
+            VX[ic + (jc + 1) * n] = a1[u] - mudyn * l1[u];
           }
         }
       }
@@ -642,7 +645,7 @@ sweep_kernel(const DevParams p) {
     if constexpr (EG)
       strip_gemm<n + h, na, n, NW, true, false>(warp, lane,
         [&](int i, int k) { return i < n ? -__ldg(gE + i + k * n) : Pxt[k + (i - n) * n]; },
-        [&](int k, int j) { return P[k + j * n]; },
+        [&](int k, int j) { return VX[k + j * n]; },
         [](int, int) { return 0.0; },
         [&](int i, int j, double v) {
           if (i < n) {
@@ -659,7 +662,7 @@ sweep_kernel(const DevParams p) {
     else
     mma_gemm<n + h, na, n, NW>(warp, lane,
         [&](int i, int k) { return i < n ? -Einv[i + k * n] : Pxt[k + (i - n) * n]; },
-        [&](int k, int j) { return P[k + j * n]; },
+        [&](int k, int j) { return VX[k + j * n]; },
         [](int, int) { return 0.0; },
         [&](int i, int j, double v) {
           if (i < n) {
