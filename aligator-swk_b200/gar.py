@@ -127,6 +127,71 @@ def lqrInitializeSolution(problem: LqrProblem):
     return xs, us, vs, lbdas
 
 
+def lqrNumRows(problem: LqrProblem) -> int:
+    """utils.hpp (lqrNumRows): nc0 + sum_t (nx + nu + nc) + sum_{t<N} nx2."""
+    st = problem.stages
+    return problem.nc0 + sum(k.nx + k.nu + k.nc for k in st) + sum(k.nx2 for k in st[:-1])
+
+
+def lqrDenseMatrix(problem: LqrProblem, mudyn: float, mueq: float):
+    """utils.hxx:194-267 / expose-utils.cpp:33-53: the dense KKT system ``mat z = -rhs`` of the whole problem,
+    unknowns ordered [lbd0 | x0 u0 v0 lbd1 | x1 u1 v1 lbd2 | ...].  Pure assembly of the caller's matrices
+    (host utility, no arithmetic beyond copies): what ``examples/gar-elqr.py`` feeds a dense LDLT."""
+    st, N = problem.stages, problem.horizon
+    n = lqrNumRows(problem)
+    mat, rhs = np.zeros((n, n)), np.zeros(n)
+    nc0, nx0 = problem.nc0, st[0].nx
+    G0 = np.asarray(problem.G0, dtype=np.float64).reshape(nc0, nx0)
+    mat[nc0:nc0 + nx0, :nc0] = G0.T
+    mat[:nc0, nc0:nc0 + nx0] = G0
+    mat[np.arange(nc0), np.arange(nc0)] = -mudyn
+    rhs[:nc0] = problem.g0
+    idx = nc0
+    for t, k in enumerate(st):
+        nx, nu, nc = k.nx, k.nu, k.nc
+        nb = nx + nu + nc
+        blk = mat[idx:idx + nb, idx:idx + nb]
+        blk[:nx, :nx] = k.Q
+        blk[nx:nx + nu, :nx] = np.asarray(k.S).T
+        blk[nx:nx + nu, nx:nx + nu] = k.R
+        blk[nx + nu:, :nx] = k.C
+        blk[nx + nu:, nx:nx + nu] = k.D
+        blk[nx + nu + np.arange(nc), nx + nu + np.arange(nc)] = -mueq
+        low = np.tril(blk)                                # selfadjointView<Lower>
+        blk[:] = low + np.tril(blk, -1).T
+        rhs[idx:idx + nx] = k.q
+        rhs[idx + nx:idx + nx + nu] = k.r
+        rhs[idx + nx + nu:idx + nb] = k.d
+        if t != N:
+            r0 = idx + nb
+            row = np.zeros((nx, nb + 2 * nx))             # [A B 0 -mu I E]
+            row[:, :nx] = k.A
+            row[:, nx:nx + nu] = k.B
+            row[np.arange(nx), nb + np.arange(nx)] = -mudyn
+            row[:, nb + nx:] = k.E
+            mat[r0:r0 + nx, idx:idx + nb + 2 * nx] = row
+            mat[idx:idx + nb + 2 * nx, r0:r0 + nx] = row.T
+            rhs[r0:r0 + k.nx2] = k.f
+            idx += nb + k.nx2
+    return mat, rhs
+
+
+def lqrDenseSolutionToTraj(problem: LqrProblem, solution):
+    """utils.hpp:106-137."""
+    st, N = problem.stages, problem.horizon
+    nc0 = problem.nc0
+    z = np.asarray(solution, dtype=np.float64)
+    xs, us, vs, lbdas = [], [], [], [z[:nc0].copy()]
+    idx = nc0
+    for t, k in enumerate(st):
+        xs.append(z[idx:idx + k.nx].copy()); idx += k.nx
+        us.append(z[idx:idx + k.nu].copy()); idx += k.nu
+        vs.append(z[idx:idx + k.nc].copy()); idx += k.nc
+        if t < N:
+            lbdas.append(z[idx:idx + k.nx2].copy()); idx += k.nx2
+    return xs, us, vs, lbdas
+
+
 class RiccatiSolverBase:
     """riccati-base.hpp:12-34 — the drop-in boundary."""
 
@@ -150,12 +215,15 @@ class RiccatiSolverBase:
 
 
 class _GpuSolver(RiccatiSolverBase):
-    def __init__(self, problem: LqrProblem, num_legs=0, device=0):
+    def __init__(self, problem: LqrProblem, num_legs=0, device=0, store_all_values=True):
         self.problem_ = problem
         pp = problem.pack()
         self._pp = pp
+        # datas[t].vm of every knot is part of the serial solver's public state (proximal-riccati.hpp:18);
+        # the parallel-in-time solver only needs the leg heads, and keeping every value function would
+        # take it off the specialised leg sweep
         self._solver = capi.Solver.for_problems(pp, num_legs=num_legs, device=device,
-                                                flags=capi.STORE_ALL_VALUES)
+                                                flags=capi.STORE_ALL_VALUES if store_all_values else 0)
 
     def _upload(self):
         # the reference re-reads problem_->stages on every backward() (proximal-riccati.hxx:37)
@@ -262,7 +330,7 @@ class ParallelRiccatiSolver(_GpuSolver):
             raise RuntimeError(f"(ParallelRiccatiSolver) num_threads (={num_threads}) should be "
                                "greater than or equal to 2.")
         self.numThreads = num_threads
-        super().__init__(problem, num_threads, device)
+        super().__init__(problem, num_threads, device, store_all_values=False)
 
     def forward(self, xs, us, vs, lbdas, theta=None):   # theta ignored (parallel-solver.hxx:184)
         X, U, V, Lb = self._solver.forward(None)

@@ -182,6 +182,55 @@ def workload_config(name, w, world):
             "parallelism": f"batch-sharded x{world}"}
 
 
+def parity_sample(s, w, theta_np, kkt, k=8):
+    """Measured parity at bench scale: the k problems of THIS rank's timed batch with
+    the worst KKT residual are downloaded and re-solved by the CPU oracle on the very same bytes.
+    -> dict(max_rel_err over (xs, us, vs, lbdas), kkt of the GPU and of the oracle on those problems)."""
+    from aligator_swk_b200.synth import PackedProblems
+    from aligator_swk_b200.layout import KnotLayout
+    import pyoracle as po
+    po.build()
+    nx, nu, nc, nth, T, legs = w["nx"], w["nu"], w["nc"], w["nth"], w["T"], w["legs"]
+    xs, us, vs, lb = s.forward(theta_np)
+    worst = np.argsort(-np.nan_to_num(kkt.max(axis=1), nan=np.inf))[:k]
+    L = KnotLayout(nx, nu, nc, nth)
+    err, kg, ko = 0.0, 0.0, 0.0
+    for b in worst:
+        b = int(b)
+        knots, G0, g0 = s.download_packed(b, 1)
+        pp = PackedProblems(L, T, s.nc0, s.nu_t, s.nc_t, knots, G0, g0)
+        th = None if theta_np is None else theta_np[b]
+        # the oracle's SERIAL solver is the yardstick also for the parallel-in-time workload (tests/gar/parallel.cpp:243-260)
+        ref = po.prox_solve(pp, MU, MU, theta=th)
+        for got, key in ((xs[b], "xs"), (us[b], "us"), (vs[b], "vs"), (lb[b], "lbdas")):
+            if got.size:
+                err = max(err, float(np.abs(got - ref[key]).max() / max(np.abs(ref[key]).max(), 1e-300)))
+        kg = max(kg, float(kkt[b].max())); ko = max(ko, float(ref["kkt"].max()))
+    out = {"problems": int(len(worst)), "selection": "worst KKT residual of this rank's timed batch",
+           "max_rel_err": err, "kkt_gpu": kg, "kkt_oracle": ko, "tolerance": 1e-10}
+    # Which one moved?  For the single worst problem: GPU and oracle against the dense KKT system of the
+    # same bytes solved with extended-precision iterative refinement (oracle/extended_precision.py).
+    rows = s.nc0 + (T + 1) * nx + T * (nu + nc) + T * nx
+    if nth == 0 and rows <= 12000 and len(worst):
+        try:
+            from extended_precision import refined_solve
+            b = int(worst[0])
+            knots, G0, g0 = s.download_packed(b, 1)
+            pp = PackedProblems(L, T, s.nc0, s.nu_t, s.nc_t, knots, G0, g0)
+            mat, rhs = po.dense_kkt(pp, MU, MU)
+            z, hist = refined_solve(mat, rhs)
+            rx, ru, rv, rl = po.dense_solution_to_traj(pp, z)
+            ref = po.prox_solve(pp, MU, MU)
+            rel = lambda a, r_: float(np.abs(a - r_).max() / max(np.abs(r_).max(), 1e-300)) if a.size else 0.0
+            out["worst_problem_vs_extended_precision"] = {
+                "gpu": max(rel(xs[b], rx), rel(us[b], ru), rel(vs[b], rv), rel(lb[b], rl)),
+                "oracle": max(rel(ref["xs"], rx), rel(ref["us"], ru), rel(ref["vs"], rv), rel(ref["lbdas"], rl)),
+                "refinement_backward_error": float(min(hist)), "kkt_rows": int(rows)}
+        except Exception as e:   # evidence row only
+            out["worst_problem_vs_extended_precision"] = {"error": str(e)[:200]}
+    return out
+
+
 def gpu_arm(args, w, rank, world, local_rank):
     import torch
     import garb200_pkg
@@ -278,18 +327,28 @@ def gpu_arm(args, w, rank, world, local_rank):
     bwd_ms, fwd_ms = s.timing_log_read()
     s.forward_device(d_theta=theta_d)    # into the solver-owned trajectory (scored below)
     s.synchronize()                      # raises if any problem flagged a numerical failure
-    kkt = s.kkt_error(MU, MU, theta=None if not nth else theta_t.cpu().numpy())
-    t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
+    theta_np = None if not nth else theta_t.cpu().numpy()
+    kkt = s.kkt_error(MU, MU, theta=theta_np)
+    par = parity_sample(s, w, theta_np, kkt, k=args.parity_k) if args.parity_k > 0 else None
+    # every rank scores ITS slice: maxima over all ranks (round 1 reported rank 0's only)
+    red = torch.tensor([ms_total, float(np.nanmax(kkt[:, 0])), float(np.nanmax(kkt[:, 1])), float(np.nanmax(kkt[:, 2]))]
+                       + ([par["max_rel_err"], par["kkt_gpu"], par["kkt_oracle"]] if par else [0.0, 0.0, 0.0]),
+                       dtype=torch.float64, device="cuda")
     if dist is not None:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total = float(t.item())
+        dist.all_reduce(red, op=dist.ReduceOp.MAX)
+    red = red.cpu().numpy()
+    ms_total = float(red[0])
+    kkt_max = {"dyn": float(red[1]), "cstr": float(red[2]), "dual": float(red[3]), "over": f"all {world} rank(s)"}
+    if par:
+        par.update(max_rel_err=float(red[4]), kkt_gpu=float(red[5]), kkt_oracle=float(red[6]), ranks=world,
+                   problems=par["problems"] * world)
     ms_step = ms_total / K
     value = B * world / (ms_step * 1e-3)
 
     # ---- e2e: host buffers through the C ABI, H2D + D2H inside the timed region ----------
     e2e = None
     if not args.no_e2e:
-        e2e = e2e_run(torch, capi, s, w, K, W, dist, world, theta_t.cpu().numpy() if nth else None)
+        e2e = e2e_run(torch, capi, s, w, max(3, min(K, 10)), W, dist, world, theta_np)
 
     if rank != 0:
         if dist is not None:
@@ -344,15 +403,59 @@ def gpu_arm(args, w, rank, world, local_rank):
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": workload_config(args.workload, w, world),
         "knots_per_s": value * (T + 1),
-        "kkt_max": {"dyn": float(kkt[:, 0].max()), "cstr": float(kkt[:, 1].max()), "dual": float(kkt[:, 2].max())},
+        "kkt_max": kkt_max, "parity_sample": par,
         "roofline": roof,
         "cpu_baseline": {"value": cpu_v, "unit": "solves/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
         "collective": None if world == 1 else "one NCCL gather of (xs,us,vs,lbdas) to rank 0 per step, on a side stream (overlaps the next backward sweep)",
     }
+    if world == 1 and args.others:
+        s.close()
+        line["other_configs"] = {}
+        for name in args.others.split(","):
+            if name and name != args.workload and name in WORKLOADS:
+                line["other_configs"][name] = short_run(torch, capi, name, local_rank, hbm_peak, fp64_peak)
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
+
+
+def short_run(torch, capi, name, dev, hbm_peak, fp64_peak, K=5, W=3):
+    """One-line summary of another BASELINE config in the same driver run (device-resident, CUDA events)."""
+    w = WORKLOADS[name]
+    nx, nu, nc, nth, T, B, legs = w["nx"], w["nu"], w["nc"], w["nth"], w["T"], w["batch"], w["legs"]
+    try:
+        s = capi.Solver(nx, nu, nc, nth, horizon=T, batch=B, num_legs=legs, device=dev)
+        s.generate(seed=42, dist=0)
+        th = None
+        if nth:
+            th_t = torch.randn(B, nth, dtype=torch.float64, device="cuda", generator=torch.Generator("cuda").manual_seed(1))
+            th = th_t.data_ptr()
+        for _ in range(W):
+            s.backward(MU, MU); s.forward_device(d_theta=th)
+        torch.cuda.synchronize()
+        s.timing_log_start(K)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(K):
+            s.backward(MU, MU); s.forward_device(d_theta=th)
+        e1.record(); torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / K
+        bwd_ms, _ = s.timing_log_read()
+        s.synchronize()
+        kkt = s.kkt_error(MU, MU, theta=None if not nth else th_t.cpu().numpy())
+        _, f_bwd, _ = flops_model(nx, nu, nc, nx if legs >= 2 else nth, T, nx)
+        b_in, b_gain, _ = bytes_model(nx, nu, nc, nx if legs >= 2 else nth, T)
+        bwd = float(np.mean(bwd_ms)) * 1e-3
+        hf, ff = B * (b_in + b_gain) / bwd / 1e9 / hbm_peak, B * f_bwd / bwd / 1e12 / fp64_peak
+        out = {"workload": f"{name}: {w['desc']}", "value": B / (ms * 1e-3), "unit": "solves/s", "ms_per_step": ms,
+               "backward_ms": bwd * 1e3, "bound": "hbm" if hf >= ff else "tensor", "roofline_frac": max(hf, ff),
+               "hbm_frac": hf, "fp64_frac": ff, "steps": K, "warmup": W,
+               "kkt_max": {"dyn": float(np.nanmax(kkt[:, 0])), "cstr": float(np.nanmax(kkt[:, 1])), "dual": float(np.nanmax(kkt[:, 2]))}}
+        s.close()
+        return out
+    except Exception as e:   # a summary row must never take the headline down
+        return {"workload": name, "error": str(e)[:200]}
 
 
 def e2e_run(torch, capi, s_dev, w, K, W, dist, world, theta):
@@ -499,13 +602,15 @@ def horizon_sweep(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=40)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="c1b", choices=sorted(WORKLOADS))
     ap.add_argument("--batch", type=int, default=0, help="override the per-GPU batch")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU-port timing")
+    ap.add_argument("--parity-k", type=int, default=8, help="problems per rank re-solved by the CPU oracle after the timed region (0: off)")
+    ap.add_argument("--others", default="c2,c3,c5", help="other BASELINE configs summarised in other_configs at N = 1 ('' = none)")
     ap.add_argument("--tune", action="append", default=[], help="diagnostic launcher knob key=value (garb200_set_tuning)")
     ap.add_argument("--horizons", action="store_true", help="the reference's own latency sweep over horizons (one GPU)")
     args = ap.parse_args()

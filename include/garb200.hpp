@@ -137,7 +137,10 @@ public:
     }
     nu_ = cfg.nu; nc_ = cfg.nc; nth_ = cfg.nth; legs_ = num_legs;
     cfg.horizon = T; cfg.nc0 = problem.nc0(); cfg.batch = 1; cfg.num_legs = num_legs;
-    cfg.device = device; cfg.flags = GARB200_STORE_ALL_VALUES;
+    cfg.device = device;
+    // datas[t].vm of every knot belongs to the serial solver's public state; the parallel-in-time solver
+    // keeps the leg heads only (storing all of them would take it off the specialised leg sweep)
+    cfg.flags = num_legs >= 2 ? 0 : GARB200_STORE_ALL_VALUES;
     cfg.nu_t = nu_t_.data(); cfg.nc_t = nc_t_.data();
     check(garb200_create(&cfg, &h_), "garb200_create");
     if (!h_) throw std::runtime_error(std::string("garb200_create: ") + garb200_last_error());

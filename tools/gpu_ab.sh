@@ -9,7 +9,7 @@ fi
 i=0
 for spec in "$@"; do
   i=$((i+1))
-  timeout 300 python bench.py --workload $spec --steps 5 --warmup 3 --no-e2e --cpu-budget 1 > gpurun_out/ab_$i.json 2> gpurun_out/ab_$i.err; echo "[$i] $spec rc=$?"; tail -2 gpurun_out/ab_$i.err
+  timeout 300 python bench.py --workload $spec --steps 5 --warmup 3 --no-e2e --cpu-budget 1 --parity-k 0 --others '' > gpurun_out/ab_$i.json 2> gpurun_out/ab_$i.err; echo "[$i] $spec rc=$?"; tail -2 gpurun_out/ab_$i.err
   python - <<PY
 import json
 try:

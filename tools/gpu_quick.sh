@@ -3,7 +3,7 @@
 mkdir -p gpurun_out
 timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -5 gpurun_out/pytest_gpu.log
 for wl in "${@:-c2 c1b}"; do for w in $wl; do
-  timeout 200 python bench.py --workload $w --steps 5 --warmup 3 --no-e2e --cpu-budget 1 > gpurun_out/q_$w.json 2> gpurun_out/q_$w.err; echo "$w rc=$?"; tail -3 gpurun_out/q_$w.err
+  timeout 200 python bench.py --workload $w --steps 5 --warmup 3 --no-e2e --cpu-budget 1 --parity-k 0 --others '' > gpurun_out/q_$w.json 2> gpurun_out/q_$w.err; echo "$w rc=$?"; tail -3 gpurun_out/q_$w.err
   python - <<PY
 import json
 try:
