@@ -18,6 +18,7 @@ OK, ERR_INVALID, ERR_CUDA, ERR_NUMERIC, ERR_STATE = 0, 1, 2, 3, 4
 STORE_ALL_VALUES = 1
 FORCE_GENERIC = 2
 PHASE_TIMERS = 4
+EXPLICIT_DYNAMICS = 8
 
 _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int)
@@ -55,7 +56,7 @@ SYMBOLS = [
     "garb200_kkt_error", "garb200_upload_trajectory", "garb200_kernel_launches", "garb200_last_timings",
     "garb200_fp64_peak", "garb200_timing_log_start", "garb200_timing_log_read",
     "garb200_used_fast_path", "garb200_phase_cycles", "garb200_set_tuning",
-    "garb200_kkt_error_noalloc",
+    "garb200_kkt_error_noalloc", "garb200_used_explicit_path",
 ]
 
 
@@ -102,6 +103,7 @@ def lib():
         L.garb200_last_timings.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.garb200_fp64_peak.argtypes = [C.c_int, C.c_int, C.c_void_p]
         L.garb200_used_fast_path.argtypes = [C.c_void_p]
+        L.garb200_used_explicit_path.argtypes = [C.c_void_p]
         L.garb200_phase_cycles.argtypes = [C.c_void_p, C.c_void_p]
         L.garb200_timing_log_start.argtypes = [C.c_void_p, C.c_int]
         L.garb200_timing_log_read.argtypes = [C.c_void_p] * 4
@@ -345,6 +347,9 @@ class Solver:
 
     def used_fast_path(self) -> bool:
         return bool(lib().garb200_used_fast_path(self._h))
+
+    def used_explicit_path(self) -> bool:
+        return bool(lib().garb200_used_explicit_path(self._h))
 
     def phase_cycles(self):
         out = np.zeros(16, np.int64)

@@ -49,6 +49,8 @@ struct garb200_solver {
   bool h2d_pending = false;
   double *h_gains = nullptr;     // pinned mirror of the gains records (getFeedback/getFeedforward cache)
   bool gains_fresh = false;
+  bool problem_dirty = true;     // the resident problem changed since E == -I was last checked
+  int *d_expl = nullptr;         // device flag written by detect_explicit_kernel
   cudaStream_t side = nullptr;   // leg mode: the last leg runs beside the coupled legs
   cudaEvent_t side_e0 = nullptr, side_e1 = nullptr;
   int nblk = 0;                  // blocks of the condensed system (2 * legs)
@@ -152,6 +154,7 @@ int garb200_create(const garb200_config *cfg, garb200_solver **out) {
   p.T = T; p.nc0 = c.nc0; p.batch = c.batch; p.num_legs = legs ? c.num_legs : 0;
   p.shift = 0;
   p.store_all_values = (c.flags & GARB200_STORE_ALL_VALUES) ? 1 : 0;
+  p.explicit_dyn = 0;
   p.uniform_knots = (s->nu_t[T] == 0 && s->nc_t[T] == 0) ? 1 : 0;
   for (int t = 0; t < T; t++)
     if (s->nu_t[t] != c.nu || s->nc_t[t] != c.nc) p.uniform_knots = 0;
@@ -202,6 +205,7 @@ int garb200_create(const garb200_config *cfg, garb200_solver **out) {
   TRYB(dmalloc(s, &p.flags, B));
   TRYB(dmalloc(s, &p.refine_steps, B));
   TRYB(dmalloc(s, &s->d_kkt_out, B * 3));
+  TRYB(dmalloc(s, &s->d_expl, 1));
   p.phase_cycles = nullptr;
   if (c.flags & GARB200_PHASE_TIMERS) { TRYB(dmalloc(s, &p.phase_cycles, 16)); cudaMemset(p.phase_cycles, 0, 16 * sizeof(long long)); }
   cudaMemset(p.flags, 0, B * sizeof(int32_t));
@@ -270,7 +274,7 @@ int garb200_set_tuning(garb200_solver *s, const char *name, int value) {
   else if (k == "condensed") t.condensed = value;
   else if (k == "c3_eg") t.c3_eg = value;
   else if (k == "legs_generic") t.legs_generic = value;
-  else if (k == "explicit_dyn") t.explicit_dyn = value;
+  else if (k == "explicit_dyn") { t.explicit_dyn = value; s->problem_dirty = true; }
   else return fail(GARB200_ERR_INVALID, "unknown tuning knob: " + k);
   return GARB200_OK;
 }
@@ -345,6 +349,7 @@ int garb200_upload_packed(garb200_solver *s, const double *knots, const double *
   if (G0) CK(cudaMemcpyAsync(p.G0, G0, B * p.nc0 * n * sizeof(double), cudaMemcpyHostToDevice, s->stream));
   if (g0) CK(cudaMemcpyAsync(p.g0, g0, B * p.nc0 * sizeof(double), cudaMemcpyHostToDevice, s->stream));
   s->has_problem = true;
+  s->problem_dirty = true;
   return GARB200_OK;
 }
 
@@ -418,6 +423,7 @@ int garb200_commit(garb200_solver *s) {
     CK(cudaEventRecord(s->ev_h2d, s->stream));
     s->h2d_pending = true;
     s->any_dirty = false;
+    s->problem_dirty = true;
   }
   s->has_problem = true;
   return GARB200_OK;
@@ -429,6 +435,7 @@ int garb200_device_problem(garb200_solver *s, double **d_knots, double **d_G0, d
   if (d_G0) *d_G0 = s->p.G0;
   if (d_g0) *d_g0 = s->p.g0;
   s->has_problem = true;  // the caller fills it on device
+  s->problem_dirty = true;
   return GARB200_OK;
 }
 
@@ -439,6 +446,7 @@ int garb200_generate(garb200_solver *s, uint64_t seed, int dist) {
   if (rc < 0) return fail(rc == -1 ? GARB200_ERR_INVALID : GARB200_ERR_CUDA, "generate kernel launch failed");
   s->launches += rc;
   s->has_problem = true;
+  s->problem_dirty = true;
   return GARB200_OK;
 }
 
@@ -464,6 +472,25 @@ int garb200_backward(garb200_solver *s, double mudyn, double mueq) {
   DevParams &p = s->p;
   p.mudyn = mudyn; p.mueq = mueq;
   CK(cudaMemsetAsync(p.flags, 0, (size_t)p.batch * sizeof(int32_t), s->stream));
+  // Explicit dynamics (E_t == -I for every knot, explicit-dynamics.hxx:32): checked on the device whenever
+  // the resident problem changed (one pass over the E blocks + a 4-byte read back), or promised by the
+  // caller with GARB200_EXPLICIT_DYNAMICS.  Only the specialised sweeps have such a path.
+  if (s->problem_dirty) {
+    p.explicit_dyn = 0;
+    if (p.einv != nullptr && p.tune.explicit_dyn && p.T >= 1) {
+      if (s->cfg.flags & GARB200_EXPLICIT_DYNAMICS) p.explicit_dyn = 1;
+      else {
+        const int rcd = launch_detect_explicit(p, s->d_expl, s->stream);
+        if (rcd < 0) return fail(GARB200_ERR_CUDA, "explicit-dynamics detection launch failed");
+        s->launches += rcd;
+        int *hflag = reinterpret_cast<int *>(s->h_scratch);
+        CK(cudaMemcpyAsync(hflag, s->d_expl, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaStreamSynchronize(s->stream));
+        p.explicit_dyn = *hflag != 0;
+      }
+    }
+    s->problem_dirty = false;
+  }
   CK(cudaEventRecord(s->ev[0], s->stream));
   const bool logb = s->tlog_bwd < s->tlog_cap;
   if (logb) CK(cudaEventRecord(s->tlog[4 * s->tlog_bwd + 0], s->stream));
@@ -691,6 +718,7 @@ int garb200_cycle_append(garb200_solver *s, const garb200_knot_view *knots, int 
   CK(cudaMemsetAsync(p.thHess, 0, std::max<size_t>(B * p.nth * p.nth, 1) * sizeof(double), s->stream));
   s->did_forward = false;
   s->gains_fresh = false;
+  s->problem_dirty = true;
   return GARB200_OK;
 }
 
@@ -740,6 +768,7 @@ int garb200_last_timings(garb200_solver *s, float *backward_ms, float *forward_m
 }
 
 int garb200_used_fast_path(const garb200_solver *s) { return s && s->used_fast ? 1 : 0; }
+int garb200_used_explicit_path(const garb200_solver *s) { return s && s->used_fast && s->p.explicit_dyn ? 1 : 0; }
 
 int garb200_phase_cycles(garb200_solver *s, long long *out16) {
   if (!s || !out16) return fail(GARB200_ERR_INVALID, "null argument");

@@ -133,6 +133,49 @@ __device__ __forceinline__ void mma_gemm(int warp, int lane, FA a, FB b, FC cin,
 }
 
 // ------------------------------------------------------------------------------------------
+// Column-strip GEMM that may run IN PLACE on its b operand:  C(:, J) <- cin(:, J) + a b(:, J).
+// A warp owns whole 8-column strips of C (strip J -> warp J % NW), computes all row tiles of a strip
+// before storing any of it, and is the only warp that reads those columns of b — so `store` may
+// overwrite b.  a and cin must not alias the output.  One b fragment feeds TM DMMAs.
+// ------------------------------------------------------------------------------------------
+template <int M, int N, int K, int NW, class FA, class FB, class FC, class FS>
+__device__ __forceinline__ void mma_gemm_colstrips(int warp, int lane, FA a, FB b, FC cin, FS store) {
+  constexpr int TM = (M + 7) / 8, TN = (N + 7) / 8, KS = (K + 3) / 4;
+  const int g = lane >> 2, q = lane & 3;
+  int ia[TM];
+#pragma unroll
+  for (int r = 0; r < TM; r++) ia[r] = min(r * 8 + g, M - 1);
+#pragma unroll 1
+  for (int tj = warp; tj < TN; tj += NW) {
+    const int jb = min(tj * 8 + g, N - 1), jc = tj * 8 + 2 * q;
+    double acc[TM][2];
+#pragma unroll
+    for (int r = 0; r < TM; r++) {
+      acc[r][0] = cin(ia[r], min(jc, N - 1));
+      acc[r][1] = cin(ia[r], min(jc + 1, N - 1));
+    }
+#pragma unroll
+    for (int ks = 0; ks < KS; ks++) {
+      const int k = ks * 4 + q;
+      const bool kv = (K % 4 == 0) || (k < K);
+      const int kc = min(k, K - 1);
+      const double bv = kv ? b(kc, jb) : 0.0;
+#pragma unroll
+      for (int r = 0; r < TM; r++) dmma_884(acc[r][0], acc[r][1], kv ? a(ia[r], kc) : 0.0, bv);
+    }
+    __syncwarp();                                  // every lane has read its b fragments of this strip
+#pragma unroll
+    for (int r = 0; r < TM; r++) {
+      const int ic = r * 8 + g;
+      if (ic < M) {
+        if (jc < N) store(ic, jc, acc[r][0]);
+        if (jc + 1 < N) store(ic, jc + 1, acc[r][1]);
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // Row-strip GEMM for operands that do not all fit in shared memory (nx = 76): a warp owns whole
 // 8-row strips of C (strip s -> warp s % NW, or the mirrored assignment with REV so that two
 // back-to-back uneven GEMMs load the warps evenly).  The strip-side operand a(i, k) may live in

@@ -27,7 +27,7 @@ __global__ void __launch_bounds__(128) generate_kernel(const DevParams p, unsign
   for (int e = tid; e < d * dof; e += NT) W[e] = nrm();
   for (int e = tid; e < KL.stride; e += NT) rec[e] = 0.0;
   __syncthreads();
-  const bool singular = t < T;
+  const bool singular = t < T && dist != 2;    // dist 2 ("explicit_psd"): convex stage costs, the value function stays PSD
   for (int e = tid; e < d * d; e += NT) {
     const int i = e % d, j = e / d;
     double acc = 0.0;
@@ -41,7 +41,7 @@ __global__ void __launch_bounds__(128) generate_kernel(const DevParams p, unsign
   const double ascale = 0.1 / sqrt((double)n);
   for (int e = tid; e < n * n; e += NT) {
     const double a = nrm(), ee = nrm();
-    if (dist == 1) {
+    if (dist == 1 || dist == 2) {
       rec[KL.A + e] = ((e % n) == (e / n) ? 0.9 : 0.0) + ascale * a;
       rec[KL.E + e] = ((e % n) == (e / n)) ? -1.0 : 0.0;
     } else {
@@ -73,6 +73,28 @@ __global__ void __launch_bounds__(128) generate_kernel(const DevParams p, unsign
     for (int e = tid; e < p.nc0 * n; e += NT) G0[e] = ((e % p.nc0) == (e / p.nc0)) ? 1.0 : 0.0;
     for (int i = tid; i < p.nc0; i += NT) g0[i] = -nrm();
   }
+}
+
+// E_t == -I exactly?  One warp per (problem, knot t < T); the first mismatch clears the flag.
+__global__ void detect_explicit_kernel(const DevParams p, int *flag) {
+  const int n = p.nx, lane = threadIdx.x & 31;
+  const long long total = (long long)p.batch * p.T;
+  const long long w = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (w >= total) return;
+  const int b = (int)(w / p.T), t = (int)(w % p.T);
+  const double *E = p.knots + ((size_t)b * (p.T + 1) + t) * p.KL.stride + p.KL.E;   // every knot: physical order is fine
+  bool ok = true;
+  for (int e = lane; e < n * n; e += 32) ok = ok && (__ldg(E + e) == ((e % n) == (e / n) ? -1.0 : 0.0));
+  if (!__all_sync(0xffffffffu, ok) && lane == 0) *flag = 0;
+}
+
+int launch_detect_explicit(const DevParams &p, int *d_flag, cudaStream_t st) {
+  const long long total = (long long)p.batch * p.T;
+  if (cudaMemsetAsync(d_flag, 1, sizeof(int), st) != cudaSuccess) return -2;     // 0x01010101: "true"
+  if (total == 0) return 0;
+  constexpr int WPB = 8;
+  detect_explicit_kernel<<<(unsigned)((total + WPB - 1) / WPB), 32 * WPB, 0, st>>>(p, d_flag);
+  return cudaGetLastError() == cudaSuccess ? 1 : -2;
 }
 
 int launch_generate(const DevParams &p, uint64_t seed, int dist, cudaStream_t st) {

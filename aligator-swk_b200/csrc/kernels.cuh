@@ -31,6 +31,7 @@ struct DevParams {
   int T, nc0, batch, num_legs;
   int shift;            // ring offset of the time axis (cycleAppend)
   int store_all_values;
+  int explicit_dyn;     // 1: every E_t == -I exactly (E and E^{-1} are never read by the specialised sweeps)
   int uniform_knots;    // 1: every knot t < T has (nu, nc), the terminal knot has nu = nc = 0
   int nslots;           // value slots per problem (T+1 when storing all, else #legs or 1)
   const int *nu_t, *nc_t;         // [T+1] logical-time dims
@@ -87,6 +88,8 @@ int launch_collapse(const DevParams &p, cudaStream_t st);
 int launch_kkt_error(const DevParams &p, const double *d_theta, double mudyn, double mueq,
                      double *d_out, cudaStream_t st);
 int launch_generate(const DevParams &p, uint64_t seed, int dist, cudaStream_t st);
+// *d_flag = 1 iff E_t == -I exactly for every problem and knot t < T (one pass over the E blocks)
+int launch_detect_explicit(const DevParams &p, int *d_flag, cudaStream_t st);
 int fp64_peak(int kind, double *tflops);
 
 } // namespace garb200

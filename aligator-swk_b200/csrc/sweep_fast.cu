@@ -115,7 +115,10 @@ template <int NX, int NU, int NC, int NTH = 0, int HREC = NTH, bool EG = false> 
 // factorizations run while NO group feeds the tensor pipe (a dependent DFMA queued behind the other
 // CTAs' DMMAs waits ~100 cycles; alone it takes ~10), and the GEMM phases of all groups saturate the pipe
 // together.  Independent CTAs (GRP = 1, 3 per SM) drift apart and pay that queueing in every chain.
-template <int NX, int NU, int NC, int NTH, int NW, bool PROF, bool LEG = false, bool EG = false, int GRP = 1>
+// EX: explicit dynamics, E_t = -I at every knot (explicit-dynamics.hxx:32, solver-proxddp.hxx:826 — what
+// ProxDDP feeds).  Then E^{-1} = -I exactly: no pre-pass, the E block is never read, product (1) is a sign
+// flip, (2) the lower-symmetrisation of Pmat, (10) a copy — the same numbers as the general path, bit for bit.
+template <int NX, int NU, int NC, int NTH, int NW, bool PROF, bool LEG = false, bool EG = false, int GRP = 1, bool EX = false>
 __global__ void __launch_bounds__(32 * NW * GRP, GRP > 1 ? 1 : (NW >= 8 ? 2 : (NW == 5 && NTH <= 4) ? 3 : NW == 1 ? 24 : 1))
 sweep_kernel(const DevParams p) {
   extern __shared__ __align__(16) double sm_cta[];
@@ -190,6 +193,12 @@ sweep_kernel(const DevParams p) {
     const int pt = phys_t(p, t);
     const double *src = p.knots + (pbase + pt) * PL::kstride;
     fence_proxy_async();
+    if constexpr (EX) {                 // [Q..B] and [f..]: E = -I is never read
+      mbar_expect_tx(bar, (uint32_t)(PL::kstride - n * n) * 8u);
+      tma_load_1d(rec, src, (uint32_t)PL::oE * 8u, bar);
+      tma_load_1d(rec + (EG ? PL::oE : PL::of), src + PL::of, (uint32_t)(PL::kstride - PL::of) * 8u, bar);
+      return;
+    }
     if constexpr (EG) {                 // [Q..B] and [f..], the E block is never staged
       mbar_expect_tx(bar, (uint32_t)(PL::kstride - PL::esh) * 8u);
       tma_load_1d(rec, src, (uint32_t)PL::oE * 8u, bar);
@@ -327,48 +336,64 @@ sweep_kernel(const DevParams p) {
       if (t > beg) {          // next knot's record and E^{-1} towards L2 while this one is solved
         const int pn = phys_t(p, t - 1);
         l2_prefetch(p.knots + (pbase + pn) * PL::kstride, (uint32_t)PL::kstride * 8u);
-        l2_prefetch(p.einv + ((size_t)b * T + pn) * (size_t)(n * n), (uint32_t)(n * n) * 8u);
+        if constexpr (!EX) l2_prefetch(p.einv + ((size_t)b * T + pn) * (size_t)(n * n), (uint32_t)(n * n) * 8u);
       }
       tma_store_wait_read();
     }
-    if constexpr (EG) gE = p.einv + ((size_t)b * T + phys_t(p, t)) * (size_t)(n * n);
+    if constexpr (EG && !EX) gE = p.einv + ((size_t)b * T + phys_t(p, t)) * (size_t)(n * n);
     mbar_wait(bar, phase); phase ^= 1;
     cta_sync<NT, GRP>();
     PH(0);
-    // (1) [X1 | x1v] = Einv^T [P | pvec]          EinvP, -ptilde      (:175-178)
-    //     theta columns: Pxttilde = -Einv^T Vxt -> Pxt                                   (:261-262)
-    if constexpr (EG)
-      strip_gemm<n, na, n, NW, true, false>(warp, lane,
-          [&](int i, int k) { return __ldg(gE + k + i * n); },
+    double fro = 0.0;
+    if constexpr (EX) {
+      // E^{-1} = -I: EinvP = -Pmat and -ptilde = -pvec are never formed; Ptilde = (Pmat) lower-symmetrised
+      // (:179-180, exact), Pxttilde = -Einv^T Vxt = Vxt                                      (:261-262)
+      for (int e = tid; e < n * n; e += NT) {
+        const int i = e % n, j = e / n;
+        if (i >= j) {
+          const double v = P[e];
+          if (i > j) P[j + i * n] = v;
+          fro = fma(i == j ? v : 2.0 * v, v, fro);
+        }
+      }
+      if constexpr (h > 0)
+        for (int e = tid; e < n * h; e += NT) Pxt[e] = Pth[e];
+      PH(1);
+    } else {
+      // (1) [X1 | x1v] = Einv^T [P | pvec]          EinvP, -ptilde      (:175-178)
+      //     theta columns: Pxttilde = -Einv^T Vxt -> Pxt                                   (:261-262)
+      if constexpr (EG)
+        strip_gemm<n, na, n, NW, true, false>(warp, lane,
+            [&](int i, int k) { return __ldg(gE + k + i * n); },
+            [&](int k, int j) { return P[k + j * n]; },
+            [](int, int) { return 0.0; },
+            [&](int i, int j, double v) { if (j <= n) X1[i + j * n] = v; else Pxt[i + (j - n - 1) * n] = -v; });
+      else
+      mma_gemm<n, na, n, NW>(warp, lane,
+          [&](int i, int k) { return Einv[k + i * n]; },
           [&](int k, int j) { return P[k + j * n]; },
           [](int, int) { return 0.0; },
           [&](int i, int j, double v) { if (j <= n) X1[i + j * n] = v; else Pxt[i + (j - n - 1) * n] = -v; });
-    else
-    mma_gemm<n, na, n, NW>(warp, lane,
-        [&](int i, int k) { return Einv[k + i * n]; },
-        [&](int k, int j) { return P[k + j * n]; },
-        [](int, int) { return 0.0; },
-        [&](int i, int j, double v) { if (j <= n) X1[i + j * n] = v; else Pxt[i + (j - n - 1) * n] = -v; });
-    cta_sync<NT, GRP>();
-    PH(1);
-    // (2) Ptilde = X1 * Einv (lower triangle kept, mirrored); ||Ptilde||_F^2 on the fly  (:179-180)
-    double fro = 0.0;
-    if constexpr (EG)      // transposed: Ptilde^T = Einv^T X1^T, whose upper triangle is the reference's lower one
-      strip_gemm<n, n, n, NW, true, false>(warp, lane,
-          [&](int i, int k) { return __ldg(gE + k + i * n); },
-          [&](int k, int j) { return X1[j + k * n]; },
+      cta_sync<NT, GRP>();
+      PH(1);
+      // (2) Ptilde = X1 * Einv (lower triangle kept, mirrored); ||Ptilde||_F^2 on the fly  (:179-180)
+      if constexpr (EG)      // transposed: Ptilde^T = Einv^T X1^T, whose upper triangle is the reference's lower one
+        strip_gemm<n, n, n, NW, true, false>(warp, lane,
+            [&](int i, int k) { return __ldg(gE + k + i * n); },
+            [&](int k, int j) { return X1[j + k * n]; },
+            [](int, int) { return 0.0; },
+            [&](int i, int j, double v) {
+              if (i <= j) { P[j + i * n] = v; P[i + j * n] = v; fro = fma(i == j ? v : 2.0 * v, v, fro); }
+            });
+      else
+      mma_gemm_lower<n, n, NW>(warp, lane,
+          [&](int i, int k) { return X1[i + k * n]; },
+          [&](int k, int j) { return Einv[k + j * n]; },
           [](int, int) { return 0.0; },
           [&](int i, int j, double v) {
-            if (i <= j) { P[j + i * n] = v; P[i + j * n] = v; fro = fma(i == j ? v : 2.0 * v, v, fro); }
+            if (i >= j) { P[i + j * n] = v; P[j + i * n] = v; fro = fma(i == j ? v : 2.0 * v, v, fro); }
           });
-    else
-    mma_gemm_lower<n, n, NW>(warp, lane,
-        [&](int i, int k) { return X1[i + k * n]; },
-        [&](int k, int j) { return Einv[k + j * n]; },
-        [](int, int) { return 0.0; },
-        [&](int i, int j, double v) {
-          if (i >= j) { P[i + j * n] = v; P[j + i * n] = v; fro = fma(i == j ? v : 2.0 * v, v, fro); }
-        });
+    }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) fro += __shfl_xor_sync(0xffffffffu, fro, o);
     if (lane == 0) red[warp] = fro;
@@ -377,15 +402,21 @@ sweep_kernel(const DevParams p) {
     fro = 0.0;
 #pragma unroll
     for (int w = 0; w < NW; w++) fro += red[w];
-    // Lambda = I + mudyn Ptilde.  When mudyn ||Ptilde||_F <= 1e-9 the first-order Neumann form
-    //   Lambda^{-1} X = X - mudyn Ptilde X        (truncation <= (mudyn ||Ptilde||)^2 <= 1e-18 relative,
-    // below the rounding error of the LLT solve it replaces) is ONE product on the tensor pipe;
-    // otherwise the blocked LDL^T solve runs.  Uniform over the CTA (same `fro` in every thread).
-    const bool neumann = mudyn * sqrt(fro) <= 1e-9;
+    // Lambda = I + mudyn Ptilde.  When mudyn ||Ptilde||_F is small the Neumann series
+    //   Lambda^{-1} X = X - mudyn Ptilde X + (mudyn Ptilde)^2 X - ...     evaluated as  Y <- X - mudyn Ptilde Y
+    // is one to three products on the tensor pipe; otherwise the blocked LDL^T solve runs.  Uniform over
+    // the CTA (same `fro` in every thread).
+    // Order of the series: x = mudyn ||Ptilde||_F bounds the spectral radius of mudyn Ptilde, the order-k
+    // partial sum has relative truncation error <= x^(k+1) <= 1e-18 (below the rounding of the LLT solve it
+    // replaces): k = 1 for x <= 1e-9 (implicit dynamics with |E| >> 1), k = 2 for x <= 1e-6, k = 3 for
+    // x <= 3e-5 (explicit dynamics, E = -I: Ptilde = Pmat); beyond that the LDL^T solve runs.
+    const double xnorm = mudyn * sqrt(fro);
+    const int order = xnorm <= 1e-9 ? 1 : xnorm <= 1e-6 ? 2 : xnorm <= 3e-5 ? 3 : 0;
+    const bool neumann = order > 0;
     // (3) w = ptilde + Ptilde f -> pv                                                   (:182-187)
     gemv4<n, n, NT>(tid, [&](int i, int j) { return P[i + j * n]; }, [&](int j) { return f[j]; },
-                    [&](int i) { return -x1v[i]; }, [&](int i, double v) { pv[i] = v; });
-    if constexpr (h > 0)
+                    [&](int i) { return EX ? pv[i] : -x1v[i]; }, [&](int i, double v) { pv[i] = v; });   // ptilde = -x1v (EX: = pvec)
+    if constexpr (h > 0 && !EX)
       for (int e = tid; e < n * h; e += NT) Pth[e] = Pxt[e];     // right-hand sides of Lth0 = Lambda^{-1} Pxttilde
     if (!neumann) {
       for (int e = tid; e < n * n; e += NT) {
@@ -404,10 +435,23 @@ sweep_kernel(const DevParams p) {
           [&](int i, int k) { return -mudyn * P[i + k * n]; },
           [&](int k, int j) { return P[k + j * n]; },
           [&](int i, int j) { return P[i + j * n]; },
-          [&](int i, int j, double v) {                       // lower triangle kept and mirrored in the epilogue
-            if (j >= n || i >= j) X1[i + j * n] = v;
-            if (j < n && i > j) X1[j + i * n] = v;
+          [&](int i, int j, double v) {                       // last product: lower triangle kept and mirrored in the epilogue
+            if (order > 1 || j >= n || i >= j) X1[i + j * n] = v;
+            if (order == 1 && j < n && i > j) X1[j + i * n] = v;
           });
+#pragma unroll 1
+      for (int it = 1; it < order; it++) {                    // Y <- [Ptilde | w] - mudyn Ptilde Y, in place (column strips)
+        cta_sync<NT, GRP>();
+        mma_gemm_colstrips<n, na, n, NW>(warp, lane,
+            [&](int i, int k) { return -mudyn * P[i + k * n]; },
+            [&](int k, int j) { return X1[k + j * n]; },
+            [&](int i, int j) { return P[i + j * n]; },
+            [&](int i, int j, double v) { X1[i + j * n] = v; });
+      }
+      if (order > 1) {                                        // selfadjointView<Lower> of the result (:190)
+        cta_sync<NT, GRP>();
+        mirror_lower_ct<n, NT>(tid, X1);
+      }
       PH(4);
     } else {
       if (!ldlt_solve_blocked<n, na, NT, n, GRP>(tid, X1, RhsColMajor<n>{P}, Gs, dinv)) flags |= GARB200_FLAG_LLT_NOT_PD;
@@ -642,6 +686,23 @@ sweep_kernel(const DevParams p) {
     // (10) [Afb | yff] = -Einv [A_pre | tv]                                              (:243-245)
     //      rows n..n+h-1 of the same product: Pxttilde^T [A_pre | tv | Yth_pre] = Vxt^T [Afb | yff | Yth]
     //      (Vxt^T Einv^{-1}... = Pxttilde^T exactly), the three Vxt-contractions of :286-298
+    if constexpr (EX) {
+      // -E^{-1} = I: [Afb | yff | Yth] = [A_pre | tv | Yth_pre], a (transposing) copy into the gains record
+      for (int e = tid; e < n * n; e += NT) { const int i = e / n, j = e % n; gfbg[(rA + i) * n + j] = VX[i + j * n]; }
+      for (int i = tid; i < n; i += NT) ff[rA + i] = vxv[i];
+      if constexpr (h > 0) {
+        for (int e = tid; e < n * h; e += NT) { const int i = e / hh, j = e % hh; fth[(rA + i) * h + j] = VXth[i + j * n]; }
+        mma_gemm<h, na, n, NW>(warp, lane,                  // the Vxt contractions: Pxttilde^T [A_pre | tv | Yth_pre]
+            [&](int i, int k) { return Pxt[k + i * n]; },
+            [&](int k, int j) { return VX[k + j * n]; },
+            [](int, int) { return 0.0; },
+            [&](int a, int j, double v) {
+              if (j < n) Vxn[j + a * n] = v;
+              else if (j == n) vtp[a] = v;
+              else Vttp[a + (j - n - 1) * h] = v;
+            });
+      }
+    } else
     if constexpr (EG)
       strip_gemm<n + h, na, n, NW, true, false>(warp, lane,
         [&](int i, int k) { return i < n ? -__ldg(gE + i + k * n) : Pxt[k + (i - n) * n]; },
@@ -871,7 +932,7 @@ sweep_kernel(const DevParams p) {
 }
 
 // ---- host side -----------------------------------------------------------------------------
-template <int NX, int NU, int NC, int NTH, int NW, bool EG = false, int GRP = 1>
+template <int NX, int NU, int NC, int NTH, int NW, bool EG = false, int GRP = 1, bool EX = false>
 static int launch_fast_t(const DevParams &p, cudaStream_t st) {
   using PL = FastPlan<NX, NU, NC, NTH, NTH, EG>;
   static_assert(!EG || PL::BtV + PL::KS + (PL::KS + 1) / 2 + 2 <= PL::kkt, "EG: BK scratch of the initial stage must fit in BtV");
@@ -885,7 +946,7 @@ static int launch_fast_t(const DevParams &p, cudaStream_t st) {
   constexpr int MPB = WPB * GjShape<NX>::MPW;
   const long long total = (long long)p.batch * p.T;
   int launched = 0;
-  if (total > 0) {
+  if (total > 0 && !EX) {
     const bool force_regs = p.tune.einv_mode == 1;
     if constexpr (NX % 4 == 0 && NX > 16) {
       if (!force_regs) {
@@ -907,7 +968,7 @@ static int launch_fast_t(const DevParams &p, cudaStream_t st) {
   }
   const size_t smem = (size_t)GRP * PL::total * sizeof(double);
   static_assert((size_t)GRP * PL::total * sizeof(double) <= 227u * 1024u, "lockstep groups exceed the shared memory of one SM");
-  auto ks = p.phase_cycles ? sweep_kernel<NX, NU, NC, NTH, NW, true, false, EG, GRP> : sweep_kernel<NX, NU, NC, NTH, NW, false, false, EG, GRP>;
+  auto ks = p.phase_cycles ? sweep_kernel<NX, NU, NC, NTH, NW, true, false, EG, GRP, EX> : sweep_kernel<NX, NU, NC, NTH, NW, false, false, EG, GRP, EX>;
   if (cudaFuncSetAttribute(ks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -2;
   ks<<<(p.batch + GRP - 1) / GRP, 32 * NW * GRP, smem, st>>>(p);
   if (cudaGetLastError() != cudaSuccess) return -2;
@@ -966,6 +1027,11 @@ int launch_backward_fast(const DevParams &p, const int *h_nu_t, const int *h_nc_
     if (p.tune.legs_generic || p.store_all_values) return -3;
     if (p.nx == 36 && p.nu == 12 && p.nc == 0 && p.nth == 0) return launch_fast_legs<36, 12, 5>(p, st);
     return -3;
+  }
+  if (p.explicit_dyn) {       // every E_t == -I (verified on the device by detect_explicit_kernel, or promised by the caller)
+    if (p.nx == 12 && p.nu == 4 && p.nc == 0 && p.nth == 0) return launch_fast_t<12, 4, 0, 0, 1, false, 1, true>(p, st);
+    if (p.nx == 36 && p.nu == 12 && p.nc == 0 && p.nth == 0) return launch_fast_t<36, 12, 0, 0, 5, false, 1, true>(p, st);
+    if (p.nx == 36 && p.nu == 12 && p.nc == 6 && p.nth == 4) return launch_fast_t<36, 12, 6, 4, 5, true, 1, true>(p, st);
   }
   if (p.nx == 12 && p.nu == 4 && p.nc == 0 && p.nth == 0) return launch_fast_t<12, 4, 0, 0, 1>(p, st);
   if (p.nx == 36 && p.nu == 12 && p.nc == 0 && p.nth == 0) {

@@ -110,7 +110,7 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(reasons), "samples": len(self.rows)}
 
 
-def cpu_port_throughput(w, budget_s=12.0):
+def cpu_port_throughput(w, budget_s=12.0, dist="ref"):
     """Time the CPU oracle port (OpenMP over independent problems, all host cores) on a bounded
     sample of the workload. -> (solves/s, cores, sample description)."""
     import garb200_pkg
@@ -127,7 +127,7 @@ def cpu_port_throughput(w, budget_s=12.0):
     rng = np.random.default_rng(3)
 
     def run(nprob, reps):
-        pp = generate_problems(nprob, T, nx, nu, nc, nth, seed=42)
+        pp = generate_problems(nprob, T, nx, nu, nc, nth, seed=42, dist=dist)
         theta = rng.standard_normal(nth) if nth else None
         secs, used = po.bench(pp, MU, MU, theta=theta, num_legs=legs, reps=reps, nthreads=cores)
         return secs, used
@@ -156,7 +156,7 @@ def reference_arm(args, w, rank, world):
     cores = 1
     budget = max(3.0, min(15.0, 60.0 / max(1, args.steps + args.warmup)))
     for i in range(args.warmup + args.steps):
-        v, cores, sample = cpu_port_throughput(w, budget_s=budget)
+        v, cores, sample = cpu_port_throughput(w, budget_s=budget, dist=args.dist)
         if i >= args.warmup:
             per_step.append(v)
     v = float(np.mean(per_step))
@@ -165,7 +165,7 @@ def reference_arm(args, w, rank, world):
         "impl": "reference", "metric": "batched LQ solves/sec (bwd+fwd)", "value": v, "unit": "solves/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic", "config": workload_config(args.workload, w, world),
+        "data": "synthetic", "config": workload_config(args.workload, w, world, args.dist),
         "knots_per_s": v * (w["T"] + 1),
         "cpu_baseline": {"value": v, "unit": "solves/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -174,10 +174,16 @@ def reference_arm(args, w, rank, world):
     print(json.dumps(line), flush=True)
 
 
-def workload_config(name, w, world):
-    return {"workload": f"{name}: {w['desc']}", "nx": w["nx"], "nu": w["nu"], "nc": w["nc"], "nth": w["nth"],
+DIST_DESC = {"ref": "ref (tests/gar/test_util.cpp distributions, distinct knots)",
+             "explicit": "explicit-dyn (E = -I, A = 0.9 I + 0.1/sqrt(n) N(0,1), rest as ref; SURVEY 8(d) secondary row). NOTE: the ref generator's zeroed Q block makes the stage costs nonconvex; with E = -I that propagates into Rhat, so every knot takes the Bunch-Kaufman fallback",
+             "explicit_psd": "explicit-dyn with convex stage costs (E = -I, A = 0.9 I + 0.1/sqrt(n) N(0,1), [Q S; S^T R] = W W^T without the zeroed block): the shape of what ProxDDP feeds (explicit-dynamics.hxx:32, PSD Gauss-Newton Hessians)"}
+DIST_ID = {"ref": 0, "explicit": 1, "explicit_psd": 2}
+
+
+def workload_config(name, w, world, dist="ref"):
+    return {"workload": f"{name}: {w['desc']}" + (f" [{dist}: E = -I]" if dist != "ref" else ""), "nx": w["nx"], "nu": w["nu"], "nc": w["nc"], "nth": w["nth"],
             "horizon": w["T"], "batch_per_gpu": w["batch"], "global_batch": w["batch"] * world,
-            "num_legs": w["legs"], "mu": MU, "dist": "ref (tests/gar/test_util.cpp distributions, distinct knots)",
+            "num_legs": w["legs"], "mu": MU, "dist": DIST_DESC[dist],
             "l2_policy": "inputs larger than L2 (126 MB) for the batched workloads; none needed for latency rows",
             "parallelism": f"batch-sharded x{world}"}
 
@@ -249,7 +255,7 @@ def gpu_arm(args, w, rank, world, local_rank):
     K, W = args.steps, args.warmup
     s = capi.Solver(nx, nu, nc, nth, horizon=T, batch=B, num_legs=legs, device=local_rank)
     s.set_tuning(**args.tune_knobs)
-    s.generate(seed=42 + rank, dist=0)
+    s.generate(seed=42 + rank, dist=DIST_ID[args.dist])
     s.synchronize_stream_only()
     theta_d = None
     if nth:
@@ -396,12 +402,13 @@ def gpu_arm(args, w, rank, world, local_rank):
             roof["traffic_source"] = os.path.basename(digests[-1]) + ": dram__bytes_read.sum + dram__bytes_write.sum of " + " + ".join(sorted(parts))
     except Exception:
         pass
-    cpu_v, cores, sample = cpu_port_throughput(w, budget_s=args.cpu_budget)
+    cpu_v, cores, sample = cpu_port_throughput(w, budget_s=args.cpu_budget, dist=args.dist)
     line = {
         "metric": "batched LQ solves/sec (bwd+fwd)", "value": value, "unit": "solves/s", "n_gpus": world,
         "steps": K, "warmup": W, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(args.workload, w, world),
+        "config": workload_config(args.workload, w, world, args.dist),
+        "explicit_path": bool(s.used_explicit_path()),
         "knots_per_s": value * (T + 1),
         "kkt_max": kkt_max, "parity_sample": par,
         "roofline": roof,
@@ -412,21 +419,23 @@ def gpu_arm(args, w, rank, world, local_rank):
     if world == 1 and args.others:
         s.close()
         line["other_configs"] = {}
-        for name in args.others.split(","):
-            if name and name != args.workload and name in WORKLOADS:
-                line["other_configs"][name] = short_run(torch, capi, name, local_rank, hbm_peak, fp64_peak)
+        for spec in args.others.split(","):
+            name, _, dname = spec.partition("+")
+            dname = dname or "ref"
+            if name in WORKLOADS and dname in DIST_DESC and (name, dname) != (args.workload, args.dist):
+                line["other_configs"][spec] = short_run(torch, capi, name, local_rank, hbm_peak, fp64_peak, dist=dname)
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
 
 
-def short_run(torch, capi, name, dev, hbm_peak, fp64_peak, K=5, W=3):
+def short_run(torch, capi, name, dev, hbm_peak, fp64_peak, K=5, W=3, dist="ref"):
     """One-line summary of another BASELINE config in the same driver run (device-resident, CUDA events)."""
     w = WORKLOADS[name]
     nx, nu, nc, nth, T, B, legs = w["nx"], w["nu"], w["nc"], w["nth"], w["T"], w["batch"], w["legs"]
     try:
         s = capi.Solver(nx, nu, nc, nth, horizon=T, batch=B, num_legs=legs, device=dev)
-        s.generate(seed=42, dist=0)
+        s.generate(seed=42, dist=DIST_ID[dist])
         th = None
         if nth:
             th_t = torch.randn(B, nth, dtype=torch.float64, device="cuda", generator=torch.Generator("cuda").manual_seed(1))
@@ -448,7 +457,9 @@ def short_run(torch, capi, name, dev, hbm_peak, fp64_peak, K=5, W=3):
         b_in, b_gain, _ = bytes_model(nx, nu, nc, nx if legs >= 2 else nth, T)
         bwd = float(np.mean(bwd_ms)) * 1e-3
         hf, ff = B * (b_in + b_gain) / bwd / 1e9 / hbm_peak, B * f_bwd / bwd / 1e12 / fp64_peak
-        out = {"workload": f"{name}: {w['desc']}", "value": B / (ms * 1e-3), "unit": "solves/s", "ms_per_step": ms,
+        out = {"workload": f"{name}: {w['desc']}", "dist": dist, "explicit_path": bool(s.used_explicit_path()),
+               "note": None if dist == "ref" else "fractions use the REFERENCE algorithm's operation count (17 n^3 incl. LU(E), E^-1 products) and record bytes incl. E; the E = -I path executes fewer of both",
+               "value": B / (ms * 1e-3), "unit": "solves/s", "ms_per_step": ms,
                "backward_ms": bwd * 1e3, "bound": "hbm" if hf >= ff else "tensor", "roofline_frac": max(hf, ff),
                "hbm_frac": hf, "fp64_frac": ff, "steps": K, "warmup": W,
                "kkt_max": {"dyn": float(np.nanmax(kkt[:, 0])), "cstr": float(np.nanmax(kkt[:, 1])), "dual": float(np.nanmax(kkt[:, 2]))}}
@@ -610,7 +621,8 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU-port timing")
     ap.add_argument("--parity-k", type=int, default=8, help="problems per rank re-solved by the CPU oracle after the timed region (0: off)")
-    ap.add_argument("--others", default="c2,c3,c5", help="other BASELINE configs summarised in other_configs at N = 1 ('' = none)")
+    ap.add_argument("--dist", default="ref", choices=["ref", "explicit", "explicit_psd"], help="synthetic distribution (SURVEY 8d)")
+    ap.add_argument("--others", default="c2,c3,c5,c1b+explicit_psd,c2+explicit_psd,c1b+explicit", help="other BASELINE configs summarised in other_configs at N = 1 ('' = none)")
     ap.add_argument("--tune", action="append", default=[], help="diagnostic launcher knob key=value (garb200_set_tuning)")
     ap.add_argument("--horizons", action="store_true", help="the reference's own latency sweep over horizons (one GPU)")
     args = ap.parse_args()

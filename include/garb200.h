@@ -53,6 +53,10 @@ extern "C" {
                                         leg heads only — what the algorithm itself consumes)  */
 
 #define GARB200_FORCE_GENERIC 2      /* never use the dimension-specialised kernels (testing)  */
+#define GARB200_EXPLICIT_DYNAMICS 8  /* the caller PROMISES E_t == -I at every knot (explicit dynamics,
+                                        explicit-dynamics.hxx:32): E is never read and the device-side
+                                        check that garb200_backward otherwise runs after every change
+                                        of the problem is skipped                                  */
 #define GARB200_PHASE_TIMERS 4       /* diagnostic: per-phase clock64 timers in the specialised
                                         sweep (garb200_phase_cycles); slower instrumented kernel */
 
@@ -126,7 +130,9 @@ int garb200_commit(garb200_solver *s);
 /* raw device pointers of the resident problem (for upstream device producers) */
 int garb200_device_problem(garb200_solver *s, double **d_knots, double **d_G0, double **d_g0);
 /* fill the resident problem with synthetic random data ON DEVICE (bench data source;
- * distributions of tests/gar/test_util.cpp:13-66; dist 0 = "ref", 1 = "explicit" E=-I) */
+ * distributions of tests/gar/test_util.cpp:13-66; dist 0 = "ref", 1 = "explicit" E = -I with the
+ * generator's zeroed Q block (nonconvex stages: Bunch-Kaufman at every knot), 2 = "explicit_psd" E = -I
+ * with convex stage costs) */
 int garb200_generate(garb200_solver *s, uint64_t seed, int dist);
 /* D2H of the packed problem of `count` problems starting at `first` */
 int garb200_download_packed(garb200_solver *s, int first, int count, double *knots, double *G0,
@@ -217,6 +223,8 @@ int64_t garb200_kernel_launches(const garb200_solver *s);
 int garb200_last_timings(garb200_solver *s, float *backward_ms, float *forward_ms);
 /* 1 if the last backward ran the dimension-specialised (DMMA) sweep, 0 for the generic kernel */
 int garb200_used_fast_path(const garb200_solver *s);
+/* 1 if it ran with the explicit-dynamics path (every E_t == -I: no E^-1 pre-pass, E never read) */
+int garb200_used_explicit_path(const garb200_solver *s);
 /* Diagnostic: accumulated clock64() cycles of thread 0 of every CTA per phase of the specialised
  * sweep since the last call (solver created with GARB200_PHASE_TIMERS in config.flags). */
 int garb200_phase_cycles(garb200_solver *s, long long *out16);

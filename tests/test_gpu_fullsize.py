@@ -209,3 +209,41 @@ def test_tiny_positive_pivot_falls_back_to_bunch_kaufman(capi, oracle):
     assert s.used_fast_path()
     _check(oracle, pp, mu, xs, us, vs, lb, theta, rtol=1e-9)
     s.close()
+
+
+@pytest.mark.parametrize("shape", [(12, 4, 0, 0, 50, 2), (36, 12, 0, 0, 100, 2), (36, 12, 6, 4, 30, 2)],
+                         ids=lambda c: "nx%d_nu%d_nc%d_nth%d_T%d_B%d" % c)
+def test_explicit_dynamics_path_is_exact(capi, oracle, shape):
+    """E_t == -I at every knot (explicit-dynamics.hxx:32, solver-proxddp.hxx:826 — what ProxDDP feeds): detected
+    on the device, the sweep then skips the E^-1 pre-pass and never reads E.  Same bits as the general path
+    on the same input, and parity with the oracle (batch 2 of this seed is well conditioned: on the long
+    explicit-dynamics horizons some problems put the oracle itself 1e-9 from the extended-precision
+    solution, see tests/test_reference_fixtures.py); one knot with E != -I switches it off again; the
+    GARB200_EXPLICIT_DYNAMICS promise flag takes the same path without the check."""
+    nx, nu, nc, nth, T, B = shape
+    mu = 1e-9
+    pp = generate_problems(B, T, nx, nu, nc, nth, seed=61, dist="explicit_psd")
+    theta = np.random.default_rng(6).standard_normal((B, nth)) if nth else None
+    s, xs, us, vs, lb = _solve(capi, pp, mu, theta)
+    assert s.used_fast_path() and s.used_explicit_path()
+    _check(oracle, pp, mu, xs, us, vs, lb, theta)
+    g = s.download_gains()
+    # general path on the same bytes: identical bits
+    s0, xs0, us0, vs0, lb0 = _solve(capi, pp, mu, theta, explicit_dyn=0)
+    assert s0.used_fast_path() and not s0.used_explicit_path()
+    assert np.array_equal(xs, xs0) and np.array_equal(us, us0) and np.array_equal(vs, vs0) and np.array_equal(lb, lb0)
+    assert np.array_equal(g, s0.download_gains())
+    # the promise flag
+    s1 = capi.Solver.for_problems(pp, flags=capi.EXPLICIT_DYNAMICS)
+    s1.upload(pp); s1.backward(mu, mu)
+    xs1, us1, vs1, lb1 = s1.forward(theta)
+    assert s1.used_explicit_path() and np.array_equal(xs1, xs) and np.array_equal(lb1, lb)
+    # one knot with E != -I: the check must switch the path off after the re-upload
+    o = pp.layout.offsets
+    pp.knots[B - 1, T // 2, o["E"] + 1] = 1e-3
+    s.upload(pp); s.backward(mu, mu)
+    xs2, us2, vs2, lb2 = s.forward(theta)
+    assert s.used_fast_path() and not s.used_explicit_path()
+    _check(oracle, pp, mu, xs2, us2, vs2, lb2, theta)
+    for x in (s, s0, s1):
+        x.close()

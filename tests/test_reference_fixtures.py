@@ -148,7 +148,8 @@ def _problem_from_packed(gar, pp, b=0):
         m, c = int(pp.nu_t[t]), int(pp.nc_t[t])
         k = gar.LqrKnot(L.nx, m, c, nth=L.nth)
         for name, a in L.unpack(pp.knots[b, t], m, c).items():
-            getattr(k, name)[...] = a
+            dst = getattr(k, name)
+            dst[...] = np.asarray(a).reshape(dst.shape)
         knots.append(k)
     prob = gar.LqrProblem(knots, pp.nc0)
     prob.G0[:] = pp.G0[b].reshape(pp.nc0, L.nx, order="F")

@@ -7,8 +7,10 @@ garb200_pkg.load()
 from aligator_swk_b200 import capi
 w = dict(bench.WORKLOADS[sys.argv[1]]); B = int(sys.argv[2]) if len(sys.argv) > 2 else w["batch"]
 s = capi.Solver(w["nx"], w["nu"], w["nc"], w["nth"], horizon=w["T"], batch=B, flags=capi.PHASE_TIMERS)
-s.set_tuning(**{kv.split("=")[0]: int(kv.split("=")[1]) for kv in sys.argv[3:]})
-s.generate(42, 0)
+kv = {a.split("=")[0]: int(a.split("=")[1]) for a in sys.argv[3:]}
+dist = kv.pop("dist", 0)
+s.set_tuning(**kv)
+s.generate(42, dist)
 for _ in range(2):
     s.backward(bench.MU, bench.MU)
 s.synchronize_stream_only(); s.phase_cycles()
