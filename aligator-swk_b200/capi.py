@@ -37,6 +37,15 @@ class Config(C.Structure):
                 ("nu_t", _ip), ("nc_t", _ip), ("nu_term", C.c_int), ("nc_term", C.c_int)]
 
 
+class DeviceField(C.Structure):
+    _fields_ = [("ptr", C.c_void_p), ("stride_b", C.c_longlong), ("stride_t", C.c_longlong), ("ld", C.c_int)]
+
+
+class DeviceProblemView(C.Structure):
+    _fields_ = [(n, DeviceField) for n in ("Q", "S", "R", "q", "r", "A", "B", "E", "f", "C", "D", "d",
+                                           "Gth", "Gx", "Gu", "gamma", "G0", "g0")]
+
+
 class KnotView(C.Structure):
     _fields_ = [("nu", C.c_int), ("nc", C.c_int)] + [
         (n, _dp) for n in ("Q", "S", "R", "q", "r", "A", "B", "E", "f", "C", "D", "d",
@@ -57,6 +66,7 @@ SYMBOLS = [
     "garb200_fp64_peak", "garb200_timing_log_start", "garb200_timing_log_read",
     "garb200_used_fast_path", "garb200_phase_cycles", "garb200_set_tuning",
     "garb200_kkt_error_noalloc", "garb200_used_explicit_path",
+    "garb200_pack_from_device", "garb200_linear_step", "garb200_rollout_device",
 ]
 
 
@@ -81,6 +91,9 @@ def lib():
         L.garb200_upload_packed.argtypes = [C.c_void_p] * 4
         L.garb200_set_stream.argtypes = [C.c_void_p, C.c_void_p]
         L.garb200_kkt_error_noalloc.argtypes = [C.c_void_p] * 9 + [C.c_double, C.c_double, C.c_void_p, C.c_void_p]
+        L.garb200_pack_from_device.argtypes = [C.c_void_p, C.c_void_p, C.c_double]
+        L.garb200_linear_step.argtypes = [C.c_void_p, C.c_double] + [C.c_void_p] * 8
+        L.garb200_rollout_device.argtypes = [C.c_void_p, C.c_double] + [C.c_void_p] * 4
         L.garb200_set_tuning.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
         L.garb200_synchronize.argtypes = [C.c_void_p]
         L.garb200_destroy.argtypes = [C.c_void_p]
@@ -250,6 +263,17 @@ class Solver:
         a, b, c = C.c_void_p(), C.c_void_p(), C.c_void_p()
         check(lib().garb200_device_problem(self._h, C.byref(a), C.byref(b), C.byref(c)))
         return a.value, b.value, c.value
+
+    def pack_from_device(self, view: DeviceProblemView, preg=0.0):
+        """device-resident producer (updateLQSubproblem, solver-proxddp.hxx:802-873)"""
+        check(lib().garb200_pack_from_device(self._h, C.byref(view), float(preg)))
+
+    def linear_step(self, alpha, cur, trial):
+        """trial = cur + alpha * (solver-owned direction); cur / trial: 4-tuples of device pointers"""
+        check(lib().garb200_linear_step(self._h, float(alpha), *[_ptr(a) for a in cur], *[_ptr(a) for a in trial]))
+
+    def rollout_device(self, alpha, d_dxs, d_dus, d_dvs, d_dlbdas):
+        check(lib().garb200_rollout_device(self._h, float(alpha), _ptr(d_dxs), _ptr(d_dus), _ptr(d_dvs), _ptr(d_dlbdas)))
 
     def stage_knot(self, problem, t, view: KnotView):
         check(lib().garb200_stage_knot(self._h, problem, t, C.byref(view)))

@@ -439,6 +439,44 @@ int garb200_device_problem(garb200_solver *s, double **d_knots, double **d_G0, d
   return GARB200_OK;
 }
 
+int garb200_pack_from_device(garb200_solver *s, const garb200_device_problem_view *v, double preg) {
+  if (!s || !v) return fail(GARB200_ERR_INVALID, "null argument");
+  CK(cudaSetDevice(s->cfg.device));
+  const int rc = launch_pack_from_device(s->p, *v, preg, s->stream);
+  if (rc < 0) return fail(GARB200_ERR_CUDA, "pack_from_device launch failed");
+  s->launches += rc;
+  s->has_problem = true;
+  s->problem_dirty = true;
+  return GARB200_OK;
+}
+
+int garb200_linear_step(garb200_solver *s, double alpha, const double *d_xs, const double *d_us,
+                        const double *d_vs, const double *d_lbdas, double *d_trial_xs, double *d_trial_us,
+                        double *d_trial_vs, double *d_trial_lbdas) {
+  if (!s) return fail(GARB200_ERR_INVALID, "null solver");
+  if (!s->did_forward) return fail(GARB200_ERR_STATE, "linear_step needs a forward() into the solver-owned trajectory");
+  CK(cudaSetDevice(s->cfg.device));
+  const double *cur[4] = {d_xs, d_us, d_vs, d_lbdas};
+  double *out[4] = {d_trial_xs, d_trial_us, d_trial_vs, d_trial_lbdas};
+  const int rc = launch_linear_step(s->p, alpha, cur, out, s->stream);
+  if (rc < 0) return fail(GARB200_ERR_CUDA, "linear_step launch failed");
+  s->launches += rc;
+  return GARB200_OK;
+}
+
+int garb200_rollout_device(garb200_solver *s, double alpha, const double *d_dxs, double *d_dus, double *d_dvs,
+                           double *d_dlbdas) {
+  if (!s || !d_dxs || !d_dlbdas) return fail(GARB200_ERR_INVALID, "null argument");
+  if ((s->p.nu > 0 && !d_dus) || (s->p.nc > 0 && !d_dvs)) return fail(GARB200_ERR_INVALID, "null output for a non-empty block");
+  if (!s->did_backward) return fail(GARB200_ERR_STATE, "no factorization yet");
+  if (s->p.num_legs >= 2) return fail(GARB200_ERR_STATE, "the nonlinear rollout is not supported with the parallel-in-time solver (solver-proxddp.hxx:170-173)");
+  CK(cudaSetDevice(s->cfg.device));
+  const int rc = launch_rollout(s->p, alpha, d_dxs, d_dus, d_dvs, d_dlbdas, s->stream);
+  if (rc < 0) return fail(rc == -1 ? GARB200_ERR_INVALID : GARB200_ERR_CUDA, "rollout launch failed");
+  s->launches += rc;
+  return GARB200_OK;
+}
+
 int garb200_generate(garb200_solver *s, uint64_t seed, int dist) {
   if (!s) return fail(GARB200_ERR_INVALID, "null solver");
   CK(cudaSetDevice(s->cfg.device));

@@ -91,5 +91,9 @@ int launch_generate(const DevParams &p, uint64_t seed, int dist, cudaStream_t st
 // *d_flag = 1 iff E_t == -I exactly for every problem and knot t < T (one pass over the E blocks)
 int launch_detect_explicit(const DevParams &p, int *d_flag, cudaStream_t st);
 int fp64_peak(int kind, double *tflops);
+// consumer.cu: device-side producer / consumers around the solve
+int launch_pack_from_device(const DevParams &p, const garb200_device_problem_view &v, double preg, cudaStream_t st);
+int launch_linear_step(const DevParams &p, double alpha, const double *const cur[4], double *const out[4], cudaStream_t st);
+int launch_rollout(const DevParams &p, double alpha, const double *dxs, double *dus, double *dvs, double *dlams, cudaStream_t st);
 
 } // namespace garb200

@@ -416,6 +416,9 @@ def gpu_arm(args, w, rank, world, local_rank):
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
         "collective": None if world == 1 else "one NCCL gather of (xs,us,vs,lbdas) to rank 0 per step, on a side stream (overlaps the next backward sweep)",
     }
+    if world == 1 and not args.no_e2e:
+        line["consumers"] = consumer_bandwidth(torch, s, w, hbm_peak)
+        line["e2e_dropin"] = dropin_latency()
     if world == 1 and args.others:
         s.close()
         line["other_configs"] = {}
@@ -427,6 +430,55 @@ def gpu_arm(args, w, rank, world, local_rank):
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
+
+
+def dropin_latency():
+    """c1 (1 x nx=36 nu=12 T=100) end to end through the ADAPTER's call sequence (garb200_stage_knot x (T+1),
+    commit, backward, forward, updateGains read-back), timed by tools/dropin_bench (built by build())."""
+    exe = os.path.join(ROOT, "tools", "dropin_bench")
+    if not os.path.exists(exe):
+        return {"error": "tools/dropin_bench not built (run __graft_entry__.build())"}
+    try:
+        out = subprocess.run([exe, "36", "12", "100", "50"], capture_output=True, text=True, timeout=120)
+        return json.loads(out.stdout.strip().splitlines()[-1])
+    except Exception as e:
+        return {"error": str(e)[:200]}
+
+
+def consumer_bandwidth(torch, s, w, hbm_peak, K=5):
+    """The device-side steps around the solve on the bench batch: HBM-bound kernels,
+    algorithmic bytes / CUDA-event time."""
+    nx, nu, nc, T, B, legs = w["nx"], w["nu"], w["nc"], w["T"], w["batch"], w["legs"]
+    if legs >= 2:
+        return None
+    try:
+        n_x, n_u, n_v, n_l = B * (T + 1) * nx, B * (T + 1) * nu, B * (T + 1) * nc, B * (nx + T * nx)
+        mk = lambda n: torch.zeros(max(n, 1), dtype=torch.float64, device="cuda")
+        cur = [mk(n) for n in (n_x, n_u, n_v, n_l)]
+        out = [mk(n) for n in (n_x, n_u, n_v, n_l)]
+        ptr = lambda ts, ns: [t.data_ptr() if n else None for t, n in zip(ts, ns)]
+        ns = (n_x, n_u, n_v, n_l)
+        res = {}
+        def timed(fn):
+            fn(); torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(K):
+                fn()
+            e1.record(); torch.cuda.synchronize()
+            return e0.elapsed_time(e1) / K * 1e-3
+        t = timed(lambda: s.linear_step(0.5, ptr(cur, ns), ptr(out, ns)))
+        by = 3 * 8 * sum(ns)
+        res["linear_step"] = {"ms": t * 1e3, "gbs": by / t / 1e9, "hbm_frac": by / t / 1e9 / hbm_peak}
+        t = timed(lambda: s.rollout_device(0.5, cur[0].data_ptr(), out[1].data_ptr() if nu else None,
+                                           out[2].data_ptr() if nc else None, out[3].data_ptr()))
+        rows = nu + nc + nx
+        by = 8 * B * (T + 1) * (rows * (nx + 1) + nx + rows)
+        res["rollout_device"] = {"ms": t * 1e3, "gbs": by / t / 1e9, "hbm_frac": by / t / 1e9 / hbm_peak,
+                                 "bytes_model": "ff + K/Z/L rows of fb read, dxs read, dus/dvs/dlams written"}
+        return res
+    except Exception as e:
+        return {"error": str(e)[:200]}
 
 
 def short_run(torch, capi, name, dev, hbm_peak, fp64_peak, K=5, W=3, dist="ref"):

@@ -129,6 +129,25 @@ int garb200_stage_initial(garb200_solver *s, int problem, const double *G0, cons
 int garb200_commit(garb200_solver *s);
 /* raw device pointers of the resident problem (for upstream device producers) */
 int garb200_device_problem(garb200_solver *s, double **d_knots, double **d_G0, double **d_g0);
+/* ---- device-resident producer ------------------------------------------------
+ * SolverProxDDPTpl::updateLQSubproblem          solvers/proxddp/solver-proxddp.hxx:802-873
+ * A batched caller keeps its derivatives on the device; this packs them into the resident problem with
+ * one kernel (no host staging, no H2D): knot.A = Jx, knot.B = Ju, knot.E = Jy, knot.f = Lds[t+1],
+ * knot.Q = Lxx (+ preg on the diagonal), knot.S = Lxu, knot.R = Luu (+ preg), q, r, C, D, d (:824-850),
+ * G0 = init Jx, g0 = Lds[0] (:867-868).  Element (i, j) of knot t of problem b of a field F is read at
+ * F.ptr[b * stride_b + t * stride_t + i + j * ld] (column-major blocks, any strides); F.ptr == NULL means
+ * zeros — except E, where NULL means EXPLICIT dynamics, E = -I (explicit-dynamics.hxx:32).  Blocks of a
+ * knot are read with that knot's own (nu_t, nc_t). */
+typedef struct garb200_device_field {
+  const double *ptr;
+  long long stride_b, stride_t;
+  int ld;
+} garb200_device_field;
+typedef struct garb200_device_problem_view {
+  garb200_device_field Q, S, R, q, r, A, B, E, f, C, D, d, Gth, Gx, Gu, gamma, G0, g0;
+} garb200_device_problem_view;
+int garb200_pack_from_device(garb200_solver *s, const garb200_device_problem_view *v, double preg);
+
 /* fill the resident problem with synthetic random data ON DEVICE (bench data source;
  * distributions of tests/gar/test_util.cpp:13-66; dist 0 = "ref", 1 = "explicit" E = -I with the
  * generator's zeroed Q block (nonconvex stages: Bunch-Kaufman at every knot), 2 = "explicit_psd" E = -I
@@ -155,6 +174,20 @@ int garb200_forward_device(garb200_solver *s, const double *d_theta, double *d_x
 /* solver-owned device trajectory buffers (valid after forward*) */
 int garb200_device_trajectory(garb200_solver *s, double **d_xs, double **d_us, double **d_vs,
                               double **d_lbdas);
+
+/* ---- device-resident consumers -----------------------------------------------
+ * SolverProxDDPTpl::tryLinearStep (vector spaces)    solver-proxddp.hxx:104-148
+ *   trial_* = cur_* + alpha * (direction of the last forward*, solver-owned) for xs, us, vs, lbdas in one
+ *   pass; DEVICE pointers in the trajectory layouts at the top of this file; a NULL cur/trial pair is skipped. */
+int garb200_linear_step(garb200_solver *s, double alpha, const double *d_xs, const double *d_us,
+                        const double *d_vs, const double *d_lbdas, double *d_trial_xs,
+                        double *d_trial_us, double *d_trial_vs, double *d_trial_lbdas);
+/* the linear part of SolverProxDDPTpl::tryNonlinearRollout   solver-proxddp.hxx:372-391, 431-446
+ *   dus[t] = alpha kff_t + K_t dxs[t], dvs[t] = alpha zff_t + Z_t dxs[t], dlbdas[t+1] = alpha lff_t + L_t dxs[t]
+ * for every knot from the gains records in place (getFeedforward / getFeedback never leave the device);
+ * d_dxs [batch][T+1][nx] is the caller's state deviation; dlbdas[0] (nc0 entries) is not written. */
+int garb200_rollout_device(garb200_solver *s, double alpha, const double *d_dxs, double *d_dus,
+                           double *d_dvs, double *d_dlbdas);
 
 /* ---- solver state readers ------------------------------------------------------------
  * getFeedforward(i) / getFeedback(i)                      riccati-base.hpp:30-31

@@ -1,0 +1,158 @@
+"""The steps immediately before and after the solve, on the device:
+garb200_pack_from_device  (updateLQSubproblem, solver-proxddp.hxx:802-873)
+garb200_linear_step       (tryLinearStep, :104-148)
+garb200_rollout_device    (linear part of tryNonlinearRollout, :372-391, 431-446)
+each against a numpy restatement / the host-staged path on the same data."""
+import numpy as np
+import pytest
+
+from aligator_swk_b200.layout import GainLayout
+from aligator_swk_b200.synth import generate_problems
+from conftest import relerr
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def capi():
+    from aligator_swk_b200 import capi as c
+    c.lib()
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return c
+
+
+def _producer_arrays(torch, pp, pad=0, skip=()):
+    """The packed problem re-laid out as a PRODUCER would hold it: one device array per field, shape
+    [B][T+1][cols][rows + pad] (column-major blocks with leading dimension rows + pad), knots with a smaller
+    own nu/nc use the top-left corner.  -> (DeviceProblemView, keep-alive list)"""
+    from aligator_swk_b200 import capi
+    L = pp.layout
+    B, T = pp.batch, pp.horizon
+    view, keep = capi.DeviceProblemView(), []
+    shapes = L.shapes()
+    for name in ("Q", "S", "R", "q", "r", "A", "B", "E", "f", "C", "D", "d", "Gth", "Gx", "Gu", "gamma"):
+        rows, cols = shapes[name]
+        if name in skip or rows * cols == 0:
+            continue
+        host = np.full((B, T + 1, cols, rows + pad), np.nan)
+        for b in range(B):
+            for t in range(T + 1):
+                m, c = int(pp.nu_t[t]), int(pp.nc_t[t])
+                blk = L.unpack(pp.knots[b, t], m, c)[name]
+                host[b, t, :blk.shape[1], :blk.shape[0]] = blk.T
+        dev = torch.as_tensor(host, device="cuda")
+        keep.append(dev)
+        f = getattr(view, name)
+        f.ptr, f.stride_b, f.stride_t, f.ld = dev.data_ptr(), (T + 1) * cols * (rows + pad), cols * (rows + pad), rows + pad
+    nx, c0 = L.nx, pp.nc0
+    G0 = torch.as_tensor(np.ascontiguousarray(pp.G0.reshape(B, nx, c0)), device="cuda")     # col-major c0 x nx
+    g0 = torch.as_tensor(np.ascontiguousarray(pp.g0), device="cuda")
+    keep += [G0, g0]
+    view.G0.ptr, view.G0.stride_b, view.G0.stride_t, view.G0.ld = G0.data_ptr(), nx * c0, 0, c0
+    view.g0.ptr, view.g0.stride_b, view.g0.stride_t, view.g0.ld = g0.data_ptr(), c0, 0, c0
+    torch.cuda.synchronize()
+    return view, keep
+
+
+@pytest.mark.parametrize("dims", [(12, 4, 0, 0, 9, 3, 0), (36, 12, 6, 4, 7, 2, 3), (7, 3, 2, 1, 5, 2, 1)],
+                         ids=lambda d: "nx%d_nu%d_nc%d_nth%d_T%d_B%d_pad%d" % d)
+def test_pack_from_device_equals_host_staging(capi, oracle, dims):
+    import torch
+    nx, nu, nc, nth, T, B, pad = dims
+    mu = 1e-9
+    pp = generate_problems(B, T, nx, nu, nc, nth, seed=17)
+    view, keep = _producer_arrays(torch, pp, pad)
+    s = capi.Solver.for_problems(pp)
+    s.pack_from_device(view, 0.0)
+    k, G0, g0 = s.download_packed(0, B)
+    assert np.array_equal(k, pp.knots) and np.array_equal(G0, pp.G0) and np.array_equal(g0, pp.g0)
+    theta = np.random.default_rng(0).standard_normal((B, nth)) if nth else None
+    s.backward(mu, mu)
+    xs, us, vs, lb = s.forward(theta)
+    for b in range(B):
+        ref = oracle.prox_solve(pp, mu, mu, theta=None if theta is None else theta[b], b=b)
+        assert relerr(xs[b], ref["xs"]) < 1e-10 and relerr(lb[b], ref["lbdas"]) < 1e-10
+    # preg on the diagonals of Q and R (solver-proxddp.hxx:835-836)
+    s.pack_from_device(view, 0.25)
+    k2, _, _ = s.download_packed(0, B)
+    o, L = pp.layout.offsets, pp.layout
+    exp = pp.knots.copy()
+    for t in range(T + 1):
+        m = int(pp.nu_t[t])
+        exp[:, t, o["Q"]: o["Q"] + nx * nx: nx + 1] += 0.25
+        if m:
+            exp[:, t, o["R"]: o["R"] + m * m: m + 1] += 0.25
+    assert np.array_equal(k2, exp)
+    s.close()
+
+
+def test_pack_from_device_without_Jy_is_explicit_dynamics(capi, oracle):
+    """No E array: explicit dynamics, E = -I (explicit-dynamics.hxx:32) -> the explicit path, same answer as
+    the host-staged problem with E = -I."""
+    import torch
+    nx, nu, T, B, mu = 36, 12, 10, 2, 1e-9
+    pp = generate_problems(B, T, nx, nu, seed=5, dist="explicit_psd")
+    view, keep = _producer_arrays(torch, pp, 0, skip=("E",))
+    s = capi.Solver.for_problems(pp)
+    s.pack_from_device(view, 0.0)
+    k, _, _ = s.download_packed(0, B)
+    assert np.array_equal(k, pp.knots)
+    s.backward(mu, mu)
+    assert s.used_explicit_path()
+    xs, us, vs, lb = s.forward()
+    for b in range(B):
+        ref = oracle.prox_solve(pp, mu, mu, b=b)
+        assert relerr(xs[b], ref["xs"]) < 1e-10 and relerr(us[b], ref["us"]) < 1e-10
+    s.close()
+
+
+@pytest.mark.parametrize("dims", [(12, 4, 0, 20, 5), (36, 12, 6, 9, 3), (5, 2, 1, 4, 2)],
+                         ids=lambda d: "nx%d_nu%d_nc%d_T%d_B%d" % d)
+def test_linear_step_and_rollout_device(capi, dims):
+    import torch
+    nx, nu, nc, T, B = dims
+    mu, alpha = 1e-9, 0.37
+    pp = generate_problems(B, T, nx, nu, nc, seed=23)
+    s = capi.Solver.for_problems(pp)
+    s.upload(pp); s.backward(mu, mu)
+    dxs_h, dus_h, dvs_h, dlb_h = s.forward()           # the direction (dxs, dus, dvs, dlams) of the LQ solve
+    rng = np.random.default_rng(1)
+    cur = [rng.standard_normal(a.shape) for a in (dxs_h, dus_h, dvs_h, dlb_h)]
+    cur_d = [torch.as_tensor(a, device="cuda") for a in cur]
+    out_d = [torch.full_like(a, float("nan")) for a in cur_d]
+    torch.cuda.synchronize()
+    s.linear_step(alpha, [a.data_ptr() if a.numel() else None for a in cur_d],
+                  [a.data_ptr() if a.numel() else None for a in out_d])
+    s.synchronize()
+    for c, d, o in zip(cur, (dxs_h, dus_h, dvs_h, dlb_h), out_d):
+        if c.size:
+            assert (np.abs(o.cpu().numpy() - (c + alpha * d)) <= 4e-16 * (np.abs(c) + np.abs(alpha * d))).all()
+
+    # rollout step: dus = alpha kff + K dxs, dvs = alpha zff + Z dxs, dlams[t+1] = alpha lff + L dxs   (:380-391)
+    G = GainLayout(nx, nu, nc, 0)
+    gains = s.download_gains()
+    dxs = rng.standard_normal((B, T + 1, nx))
+    dxs_d = torch.as_tensor(dxs, device="cuda")
+    du_d = torch.full((B, T + 1, max(nu, 1)), float("nan"), dtype=torch.float64, device="cuda")[:, :, :nu].contiguous()
+    dv_d = torch.full((B, T + 1, max(nc, 1)), float("nan"), dtype=torch.float64, device="cuda")[:, :, :nc].contiguous()
+    dl_d = torch.full((B, nx + T * nx), float("nan"), dtype=torch.float64, device="cuda")
+    torch.cuda.synchronize()
+    s.rollout_device(alpha, dxs_d.data_ptr(), du_d.data_ptr() if nu else None, dv_d.data_ptr() if nc else None, dl_d.data_ptr())
+    s.synchronize()
+    du, dv, dl = du_d.cpu().numpy(), dv_d.cpu().numpy(), dl_d.cpu().numpy()
+    for b in range(B):
+        for t in range(T + 1):
+            m, c = int(pp.nu_t[t]), int(pp.nc_t[t])
+            ff, fb, _ = G.unpack(gains[b, t], m, c)
+            x = dxs[b, t]
+            scale = max(np.abs(fb).max() * np.abs(x).max() * nx, 1e-300) if fb.size else 1.0
+            if m:
+                assert np.abs(du[b, t, :m] - (alpha * ff[:m] + fb[:m] @ x)).max() <= 1e-13 * scale
+            if c:
+                assert np.abs(dv[b, t, :c] - (alpha * ff[m:m + c] + fb[m:m + c] @ x)).max() <= 1e-13 * scale
+            if t < T:
+                ref = alpha * ff[m + c:m + c + nx] + fb[m + c:m + c + nx] @ x
+                assert np.abs(dl[b, nx + t * nx: nx + (t + 1) * nx] - ref).max() <= 1e-13 * scale
+    assert np.isnan(dl[:, :nx]).all()        # dlams[0] is not written
+    s.close()
