@@ -2,6 +2,7 @@
 // No CPU fallback lives here: every compute entry point launches sm_100a kernels or
 // fails with GARB200_ERR_CUDA.
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>   // header-only NVTX v3: ranges show up in nsys / ncu, cost nothing without a tool attached
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
@@ -11,6 +12,12 @@
 
 namespace garb200 { size_t backward_smem_bytes(const DevParams &p); }
 using namespace garb200;
+
+// NVTX ranges around the phases of a solve (the reference's Tracy zones: riccati-kernel.hxx:67,93,156,170,257,308)
+struct NvtxRange {
+  explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
 
 static thread_local std::string g_err;
 static int fail(int code, const std::string &msg) { g_err = msg; return code; }
@@ -341,6 +348,7 @@ static int copy_knots_rotated(garb200_solver *s, double *dev, double *host, int 
 }
 int garb200_upload_packed(garb200_solver *s, const double *knots, const double *G0,
                           const double *g0) {
+  NvtxRange nvtx_("garb200::upload_packed (H2D)");
   if (!s || !knots) return fail(GARB200_ERR_INVALID, "null argument");
   CK(cudaSetDevice(s->cfg.device));
   const DevParams &p = s->p;
@@ -371,6 +379,7 @@ static void pack_knot(const garb200_knot_layout &L, const garb200_knot_view &k, 
 }
 
 int garb200_stage_knot(garb200_solver *s, int problem, int t, const garb200_knot_view *k) {
+  NvtxRange nvtx_("garb200::stage_knot (host pack)");
   if (!s || !k) return fail(GARB200_ERR_INVALID, "null argument");
   const DevParams &p = s->p;
   if (!s->h_stage) return fail(GARB200_ERR_STATE, "batch too large for pinned staging: use garb200_upload_packed");
@@ -396,6 +405,7 @@ int garb200_stage_initial(garb200_solver *s, int problem, const double *G0, cons
 }
 
 int garb200_commit(garb200_solver *s) {
+  NvtxRange nvtx_("garb200::commit (H2D of staged knots)");
   if (!s) return fail(GARB200_ERR_INVALID, "null solver");
   if (!s->h_stage) return fail(GARB200_ERR_STATE, "batch too large for pinned staging");
   CK(cudaSetDevice(s->cfg.device));
@@ -440,6 +450,7 @@ int garb200_device_problem(garb200_solver *s, double **d_knots, double **d_G0, d
 }
 
 int garb200_pack_from_device(garb200_solver *s, const garb200_device_problem_view *v, double preg) {
+  NvtxRange nvtx_("garb200::pack_from_device");
   if (!s || !v) return fail(GARB200_ERR_INVALID, "null argument");
   CK(cudaSetDevice(s->cfg.device));
   const int rc = launch_pack_from_device(s->p, *v, preg, s->stream);
@@ -504,6 +515,7 @@ int garb200_download_packed(garb200_solver *s, int first, int count, double *kno
 
 // ---- the hot path ----------------------------------------------------------------------
 int garb200_backward(garb200_solver *s, double mudyn, double mueq) {
+  NvtxRange nvtx_("garb200::backward (E^-1 pre-pass + sweep [+ condensed])");
   if (!s) return fail(GARB200_ERR_INVALID, "null solver");
   if (!s->has_problem) return fail(GARB200_ERR_STATE, "no problem uploaded");
   CK(cudaSetDevice(s->cfg.device));
@@ -553,6 +565,7 @@ int garb200_backward(garb200_solver *s, double mudyn, double mueq) {
 
 int garb200_forward_device(garb200_solver *s, const double *d_theta, double *d_xs, double *d_us,
                            double *d_vs, double *d_lbdas) {
+  NvtxRange nvtx_("garb200::forward (rollout kernel)");
   if (!s) return fail(GARB200_ERR_INVALID, "null solver");
   if (!s->did_backward) return fail(GARB200_ERR_STATE, "forward before backward");
   CK(cudaSetDevice(s->cfg.device));
@@ -573,6 +586,7 @@ int garb200_forward_device(garb200_solver *s, const double *d_theta, double *d_x
 
 int garb200_forward(garb200_solver *s, const double *theta, double *xs, double *us, double *vs,
                     double *lbdas) {
+  NvtxRange nvtx_("garb200::forward + D2H");
   if (!s) return fail(GARB200_ERR_INVALID, "null solver");
   if (!s->did_backward) return fail(GARB200_ERR_STATE, "forward before backward");
   CK(cudaSetDevice(s->cfg.device));
@@ -637,6 +651,7 @@ int garb200_get_gains(garb200_solver *s, int problem, int t, double *ff, double 
 }
 
 int garb200_download_gains(garb200_solver *s, int first, int count, double *gains) {
+  NvtxRange nvtx_("garb200::download_gains (D2H)");
   if (!s || !gains) return fail(GARB200_ERR_INVALID, "null argument");
   const DevParams &p = s->p;
   if (!s->did_backward) return fail(GARB200_ERR_STATE, "no factorization yet");
@@ -762,6 +777,7 @@ int garb200_cycle_append(garb200_solver *s, const garb200_knot_view *knots, int 
 
 // ---- metric -------------------------------------------------------------------------------
 int garb200_kkt_error(garb200_solver *s, double mudyn, double mueq, const double *theta, double *out) {
+  NvtxRange nvtx_("garb200::kkt_error");
   if (!s || !out) return fail(GARB200_ERR_INVALID, "null argument");
   if (!s->did_forward) return fail(GARB200_ERR_STATE, "kkt_error needs a forward() into the solver-owned trajectory");
   CK(cudaSetDevice(s->cfg.device));
