@@ -167,7 +167,8 @@ def reference_arm(args, w, rank, world):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic", "config": workload_config(args.workload, w, world, args.dist),
         "knots_per_s": v * (w["T"] + 1),
-        "cpu_baseline": {"value": v, "unit": "solves/s", "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": v, "unit": "solves/s", "cores": cores, "kind": "port", "sample": sample,
+                         "gflops_per_core": v * flops_model(w["nx"], w["nu"], w["nc"], w["nx"] if w["legs"] >= 2 else w["nth"], w["T"], w["nx"])[0] / max(cores, 1) / 1e9},
         "e2e": {"value": v, "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -412,7 +413,9 @@ def gpu_arm(args, w, rank, world, local_rank):
         "knots_per_s": value * (T + 1),
         "kkt_max": kkt_max, "parity_sample": par,
         "roofline": roof,
-        "cpu_baseline": {"value": cpu_v, "unit": "solves/s", "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": cpu_v, "unit": "solves/s", "cores": cores, "kind": "port", "sample": sample,
+                         "gflops_per_core": cpu_v * f_all / max(cores, 1) / 1e9,
+                         "note": "Eigen-free port of the reference algorithm (oracle/): malloc-free stage solve, register-blocked GEMM, 4-RHS blocked triangular solves; the reference itself needs Eigen 3.4 (not installable here)"},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
         "collective": None if world == 1 else "one NCCL gather of (xs,us,vs,lbdas) to rank 0 per step, on a side stream (overlaps the next backward sweep)",
     }

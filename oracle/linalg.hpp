@@ -46,60 +46,87 @@ struct Mat {
 // GEMM family.  C (m x n) = beta*C + alpha * op(A) * op(B); column-major.
 // Loop orders are chosen so the innermost loop is unit-stride (auto-vectorised).
 // ---------------------------------------------------------------------------------
+// Register-blocked micro-kernel: an MR x NR tile of C stays in registers across the whole k loop
+// (the textbook axpy form re-loaded and re-stored a column of C for every multiply-add and ran at
+// ~6 GFLOP/s per core; Eigen's kernels, which the reference uses, are register blocked as well).
+// A: m x k column-major (lda), Bt(l, j) = element (l, j) of op(B) read through (ldb_l, ldb_j) strides.
+template <int MR, int NR>
+static inline void gemm_tile(int kk, double alpha, const double *A, int lda, const double *B, long sl, long sj,
+                             double beta, double *C, int ldc, int mr, int nr) {
+  double acc[NR][MR];
+  for (int j = 0; j < NR; j++)
+    for (int i = 0; i < MR; i++) acc[j][i] = 0.0;
+  if (mr == MR && nr == NR) {
+    for (int l = 0; l < kk; l++) {
+      const double *al = A + (size_t)l * lda;
+      for (int j = 0; j < NR; j++) {
+        const double b = B[l * sl + j * sj];
+#pragma omp simd
+        for (int i = 0; i < MR; i++) acc[j][i] += al[i] * b;
+      }
+    }
+  } else {
+    for (int l = 0; l < kk; l++) {
+      const double *al = A + (size_t)l * lda;
+      for (int j = 0; j < nr; j++) {
+        const double b = B[l * sl + j * sj];
+        for (int i = 0; i < mr; i++) acc[j][i] += al[i] * b;
+      }
+    }
+  }
+  for (int j = 0; j < nr; j++) {
+    double *cj = C + (size_t)j * ldc;
+    if (beta == 0.0) for (int i = 0; i < mr; i++) cj[i] = alpha * acc[j][i];
+    else for (int i = 0; i < mr; i++) cj[i] = beta * cj[i] + alpha * acc[j][i];
+  }
+}
+// C (m x n) = beta C + alpha A (m x k, column-major) * op(B), op(B)(l, j) = B[l * sl + j * sj]
+static inline void gemm_core(int m, int n, int kk, double alpha, const double *A, int lda, const double *B, long sl,
+                             long sj, double beta, double *C, int ldc) {
+  constexpr int MR = 16, NR = 4;
+  for (int j0 = 0; j0 < n; j0 += NR)
+    for (int i0 = 0; i0 < m; i0 += MR)
+      gemm_tile<MR, NR>(kk, alpha, A + i0, lda, B + j0 * sj, sl, sj, beta, C + i0 + (size_t)j0 * ldc, ldc,
+                        m - i0 < MR ? m - i0 : MR, n - j0 < NR ? n - j0 : NR);
+}
+// scratch for the transposed-A forms (no allocation after the first call on a thread)
+static inline double *tls_scratch(size_t n) {
+  static thread_local std::vector<double> buf;
+  if (buf.size() < n) buf.resize(n);
+  return buf.data();
+}
 inline void gemm_nn(double alpha, const Mat &A, const Mat &B, double beta, Mat &C) {
   const int m = A.r, k = A.c, n = B.c;
   assert(B.r == k && C.r == m && C.c == n);
-  for (int j = 0; j < n; j++) {
-    double *cj = C.col(j);
-    if (beta == 0.0) std::fill(cj, cj + m, 0.0);
-    else if (beta != 1.0) for (int i = 0; i < m; i++) cj[i] *= beta;
-    for (int l = 0; l < k; l++) {
-      const double b = alpha * B(l, j);
-      const double *al = A.col(l);
-      for (int i = 0; i < m; i++) cj[i] += al[i] * b;
-    }
-  }
+  if (m == 0 || n == 0) return;
+  gemm_core(m, n, k, alpha, A.a.data(), m, B.a.data(), 1, k, beta, C.a.data(), m);
 }
 /// C = beta*C + alpha * A^T * B
 inline void gemm_tn(double alpha, const Mat &A, const Mat &B, double beta, Mat &C) {
   const int m = A.c, k = A.r, n = B.c;
   assert(B.r == k && C.r == m && C.c == n);
-  for (int j = 0; j < n; j++) {
-    const double *bj = B.col(j);
-    for (int i = 0; i < m; i++) {
-      const double *ai = A.col(i);
-      double s = 0.0;
-      for (int l = 0; l < k; l++) s += ai[l] * bj[l];
-      C(i, j) = (beta == 0.0 ? 0.0 : beta * C(i, j)) + alpha * s;
-    }
-  }
+  if (m == 0 || n == 0) return;
+  double *At = tls_scratch((size_t)m * k);                 // A^T, column-major m x k
+  for (int i = 0; i < m; i++)
+    for (int l = 0; l < k; l++) At[i + (size_t)l * m] = A.a[l + (size_t)i * k];
+  gemm_core(m, n, k, alpha, At, m, B.a.data(), 1, k, beta, C.a.data(), m);
 }
 /// C = beta*C + alpha * A * B^T
 inline void gemm_nt(double alpha, const Mat &A, const Mat &B, double beta, Mat &C) {
   const int m = A.r, k = A.c, n = B.r;
   assert(B.c == k && C.r == m && C.c == n);
-  for (int j = 0; j < n; j++) {
-    double *cj = C.col(j);
-    if (beta == 0.0) std::fill(cj, cj + m, 0.0);
-    else if (beta != 1.0) for (int i = 0; i < m; i++) cj[i] *= beta;
-    for (int l = 0; l < k; l++) {
-      const double b = alpha * B(j, l);
-      const double *al = A.col(l);
-      for (int i = 0; i < m; i++) cj[i] += al[i] * b;
-    }
-  }
+  if (m == 0 || n == 0) return;
+  gemm_core(m, n, k, alpha, A.a.data(), m, B.a.data(), n, 1, beta, C.a.data(), m);
 }
 /// C = beta*C + alpha * A^T * B^T
 inline void gemm_tt(double alpha, const Mat &A, const Mat &B, double beta, Mat &C) {
   const int m = A.c, k = A.r, n = B.r;
   assert(B.c == k && C.r == m && C.c == n);
-  for (int j = 0; j < n; j++)
-    for (int i = 0; i < m; i++) {
-      const double *ai = A.col(i);
-      double s = 0.0;
-      for (int l = 0; l < k; l++) s += ai[l] * B(j, l);
-      C(i, j) = (beta == 0.0 ? 0.0 : beta * C(i, j)) + alpha * s;
-    }
+  if (m == 0 || n == 0) return;
+  double *At = tls_scratch((size_t)m * k);
+  for (int i = 0; i < m; i++)
+    for (int l = 0; l < k; l++) At[i + (size_t)l * m] = A.a[l + (size_t)i * k];
+  gemm_core(m, n, k, alpha, At, m, B.a.data(), n, 1, beta, C.a.data(), m);
 }
 
 inline Mat transpose(const Mat &A) {
@@ -166,7 +193,27 @@ struct PartialPivLU {
     for (int k = 0; k < n; k++)
       if (piv[k] != k)
         for (int j = 0; j < X.c; j++) std::swap(X(k, j), X(piv[k], j));
-    for (int j = 0; j < X.c; j++) {
+    // four right-hand sides per pass: every column of L / U is loaded once for four columns of X (the
+    // per-column operation order is unchanged, so are the bits)
+    const int nc4 = X.c & ~3;
+    for (int j = 0; j < nc4; j += 4) {
+      double *x0 = X.col(j), *x1 = X.col(j + 1), *x2 = X.col(j + 2), *x3 = X.col(j + 3);
+      for (int k = 0; k < n; k++) {           // unit-lower forward substitution
+        const double a0 = x0[k], a1 = x1[k], a2 = x2[k], a3 = x3[k];
+        const double *lk = lu.col(k);
+#pragma omp simd
+        for (int i = k + 1; i < n; i++) { const double l = lk[i]; x0[i] -= l * a0; x1[i] -= l * a1; x2[i] -= l * a2; x3[i] -= l * a3; }
+      }
+      for (int k = n - 1; k >= 0; k--) {      // upper back substitution
+        const double dk = lu(k, k);
+        x0[k] /= dk; x1[k] /= dk; x2[k] /= dk; x3[k] /= dk;
+        const double a0 = x0[k], a1 = x1[k], a2 = x2[k], a3 = x3[k];
+        const double *uk = lu.col(k);
+#pragma omp simd
+        for (int i = 0; i < k; i++) { const double u = uk[i]; x0[i] -= u * a0; x1[i] -= u * a1; x2[i] -= u * a2; x3[i] -= u * a3; }
+      }
+    }
+    for (int j = nc4; j < X.c; j++) {
       double *x = X.col(j);
       for (int k = 0; k < n; k++) {           // unit-lower forward substitution
         const double xk = x[k];
@@ -209,7 +256,27 @@ struct LLT {
   /// X <- A^{-1} X
   void solveInPlace(Mat &X) const {
     const int n = l.r;
-    for (int j = 0; j < X.c; j++) {
+    // four right-hand sides per pass (same per-column operation order as the one-column loop below)
+    const int nc4 = X.c & ~3;
+    for (int j = 0; j < nc4; j += 4) {
+      double *x0 = X.col(j), *x1 = X.col(j + 1), *x2 = X.col(j + 2), *x3 = X.col(j + 3);
+      for (int k = 0; k < n; k++) {
+        const double dk = l(k, k);
+        x0[k] /= dk; x1[k] /= dk; x2[k] /= dk; x3[k] /= dk;
+        const double a0 = x0[k], a1 = x1[k], a2 = x2[k], a3 = x3[k];
+        const double *lk = l.col(k);
+#pragma omp simd
+        for (int i = k + 1; i < n; i++) { const double v = lk[i]; x0[i] -= v * a0; x1[i] -= v * a1; x2[i] -= v * a2; x3[i] -= v * a3; }
+      }
+      for (int k = n - 1; k >= 0; k--) {
+        double s0 = x0[k], s1 = x1[k], s2 = x2[k], s3 = x3[k];
+        const double *lk = l.col(k);
+        for (int i = k + 1; i < n; i++) { const double v = lk[i]; s0 -= v * x0[i]; s1 -= v * x1[i]; s2 -= v * x2[i]; s3 -= v * x3[i]; }
+        const double dk = l(k, k);
+        x0[k] = s0 / dk; x1[k] = s1 / dk; x2[k] = s2 / dk; x3[k] = s3 / dk;
+      }
+    }
+    for (int j = nc4; j < X.c; j++) {
       double *x = X.col(j);
       for (int k = 0; k < n; k++) {
         x[k] /= l(k, k);

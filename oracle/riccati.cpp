@@ -114,20 +114,22 @@ void terminalSolve(const Knot &model, double mueq, StageFactor &d) {
 
 // riccati-kernel.hxx:167-300
 void stageKernelSolve(const Knot &model, StageFactor &d, Value &vn, double mudyn, double mueq) {
+  // workspaces are thread-local and reused: nothing is allocated per knot after the first one
+  // (ALIGATOR_NOMALLOC_SCOPED, proximal-riccati.hxx:35)
   const int nx = model.nx, nu = model.nu, nc = model.nc, nth = model.nth;
   // step 1: E^{-1} by partial-pivot LU applied to the identity         (:172-174)
   d.Efact.compute(model.E);
   d.Einv.resize(nx, nx);
   for (int i = 0; i < nx; i++) d.Einv(i, i) = 1.0;
   d.Efact.solveInPlace(d.Einv);
-  Mat ptilde(nx);                                                      // (:175-177)
+  static thread_local Mat ptilde; ptilde.resize(nx);                                                      // (:175-177)
   gemm_tn(-1.0, d.Einv, vn.pvec, 0.0, ptilde);
-  Mat EinvP(nx, nx);                                                   // (:178-180)
+  static thread_local Mat EinvP; EinvP.resize(nx, nx);                                                   // (:178-180)
   gemm_tn(1.0, d.Einv, vn.Pmat, 0.0, EinvP);
   gemm_nn(1.0, EinvP, d.Einv, 0.0, d.Ptilde);
   symmetrize_from_lower(d.Ptilde);
 
-  Mat schur(nx, nx);                                                   // (:182-185)
+  static thread_local Mat schur; schur.resize(nx, nx);                                                   // (:182-185)
   for (int j = 0; j < nx; j++)
     for (int i = 0; i < nx; i++) schur(i, j) = (i == j ? 1.0 : 0.0) + mudyn * d.Ptilde(i, j);
   d.schurChol.compute(schur);
@@ -147,10 +149,10 @@ void stageKernelSolve(const Knot &model, StageFactor &d, Value &vn, double mudyn
   d.rhat = model.r;  gemm_tn(1.0, model.B, vn.vx, 1.0, d.rhat);
 
   // reduced KKT [Rhat D^T; D -mueq I], lower triangle -> BK                (:202-208)
-  Mat kkt = assemble_reduced_kkt(d.Rhat, model.D, mueq);
+  static thread_local Mat kkt; kkt = assemble_reduced_kkt(d.Rhat, model.D, mueq);
   d.kktChol.compute(kkt);
 
-  Mat rhs(nu + nc, 1 + nx);                                            // (:216-228)
+  static thread_local Mat rhs; rhs.resize(nu + nc, 1 + nx);                                            // (:216-228)
   for (int i = 0; i < nu; i++) rhs(i, 0) = -d.rhat[i];
   for (int i = 0; i < nc; i++) rhs(nu + i, 0) = -model.d[i];
   for (int j = 0; j < nx; j++) {
@@ -158,7 +160,8 @@ void stageKernelSolve(const Knot &model, StageFactor &d, Value &vn, double mudyn
     for (int i = 0; i < nc; i++) rhs(nu + i, 1 + j) = -model.C(i, j);
   }
   d.kktChol.solveInPlace(rhs);
-  Mat kff(nu), zff(nc), K(nu, nx), Z(nc, nx);
+  static thread_local Mat kff, zff, K, Z;
+  kff.resize(nu); zff.resize(nc); K.resize(nu, nx); Z.resize(nc, nx);
   for (int i = 0; i < nu; i++) kff[i] = rhs(i, 0);
   for (int i = 0; i < nc; i++) zff[i] = rhs(nu + i, 0);
   for (int j = 0; j < nx; j++) {
@@ -167,21 +170,21 @@ void stageKernelSolve(const Knot &model, StageFactor &d, Value &vn, double mudyn
   }
 
   // closed-loop dynamics                                               (:231-245)
-  Mat lff = vn.vx;
+  static thread_local Mat lff; lff = vn.vx;
   gemm_tn(1.0, d.BtV, kff, 1.0, lff);
-  Mat yff_pre = model.f;
+  static thread_local Mat yff_pre; yff_pre = model.f;
   gemm_nn(1.0, model.B, kff, 1.0, yff_pre);
   axpy(-mudyn, lff, yff_pre);
-  Mat yff(nx);
+  static thread_local Mat yff; yff.resize(nx);
   gemm_nn(-1.0, d.Einv, yff_pre, 0.0, yff);
 
-  Mat L(nx, nx);
+  static thread_local Mat L; L.resize(nx, nx);
   gemm_nn(1.0, vn.Vxx, model.A, 0.0, L);
   gemm_tn(1.0, d.BtV, K, 1.0, L);
-  Mat A_pre = model.A;
+  static thread_local Mat A_pre; A_pre = model.A;
   gemm_nn(1.0, model.B, K, 1.0, A_pre);
   axpy(-mudyn, L, A_pre);
-  Mat Afb(nx, nx);
+  static thread_local Mat Afb; Afb.resize(nx, nx);
   gemm_nn(-1.0, d.Einv, A_pre, 0.0, Afb);
 
   Value &vc = d.vm;                                                    // (:247-250)
@@ -192,20 +195,21 @@ void stageKernelSolve(const Knot &model, StageFactor &d, Value &vn, double mudyn
   gemm_nn(1.0, d.Shat, kff, 1.0, vc.pvec);
   gemm_tn(1.0, model.C, zff, 1.0, vc.pvec);
 
-  Mat Kth(nu, nth), Zth(nc, nth), Lth(nx, nth), Yth(nx, nth);
+  static thread_local Mat Kth, Zth, Lth, Yth;
+  Kth.resize(nu, nth); Zth.resize(nc, nth); Lth.resize(nx, nth); Yth.resize(nx, nth);
   if (nth > 0) {                                                       // (:256-299)
     gemm_tn(-1.0, d.Einv, vn.Vxt, 0.0, Lth);      // Pxttilde = -E^{-T} Vxt
     d.schurChol.solveInPlace(Lth);                // Lambda^{-1} Pxttilde
     d.Guhat = model.Gu;
     gemm_tn(1.0, model.B, Lth, 1.0, d.Guhat);
-    Mat rth(nu + nc, nth);
+    static thread_local Mat rth; rth.resize(nu + nc, nth);
     for (int j = 0; j < nth; j++)
       for (int i = 0; i < nu; i++) rth(i, j) = -d.Guhat(i, j);   // Zth rhs = 0 (:272)
     d.kktChol.solveInPlace(rth);
     Kth = get_rows(rth, 0, nu);
     Zth = get_rows(rth, nu, nc);
     gemm_tn(1.0, d.BtV, Kth, 1.0, Lth);
-    Mat Yth_pre(nx, nth);
+    static thread_local Mat Yth_pre; Yth_pre.resize(nx, nth);
     gemm_nn(1.0, model.B, Kth, 0.0, Yth_pre);
     axpy(-mudyn, Lth, Yth_pre);
     gemm_nn(-1.0, d.Einv, Yth_pre, 0.0, Yth);
