@@ -19,6 +19,7 @@ STORE_ALL_VALUES = 1
 FORCE_GENERIC = 2
 PHASE_TIMERS = 4
 EXPLICIT_DYNAMICS = 8
+DENSE_KERNEL = 16
 
 _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int)
@@ -66,7 +67,11 @@ SYMBOLS = [
     "garb200_fp64_peak", "garb200_timing_log_start", "garb200_timing_log_read",
     "garb200_used_fast_path", "garb200_phase_cycles", "garb200_set_tuning",
     "garb200_kkt_error_noalloc", "garb200_used_explicit_path",
-    "garb200_pack_from_device", "garb200_linear_step", "garb200_rollout_device",
+    "garb200_pack_from_device", "garb200_linear_step", "garb200_rollout_device", "garb200_device_theta",
+    "garb200_upload_gv",
+    "garb200_multi_create", "garb200_multi_destroy", "garb200_multi_num_shards", "garb200_multi_shard",
+    "garb200_multi_upload_packed", "garb200_multi_generate", "garb200_multi_backward", "garb200_multi_forward",
+    "garb200_multi_synchronize", "garb200_multi_kkt_error",
 ]
 
 
@@ -94,6 +99,19 @@ def lib():
         L.garb200_pack_from_device.argtypes = [C.c_void_p, C.c_void_p, C.c_double]
         L.garb200_linear_step.argtypes = [C.c_void_p, C.c_double] + [C.c_void_p] * 8
         L.garb200_rollout_device.argtypes = [C.c_void_p, C.c_double] + [C.c_void_p] * 4
+        L.garb200_device_theta.argtypes = [C.c_void_p, C.c_void_p]
+        L.garb200_upload_gv.argtypes = [C.c_void_p, C.c_void_p]
+        L.garb200_multi_create.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.garb200_multi_destroy.argtypes = [C.c_void_p]
+        L.garb200_multi_destroy.restype = None
+        L.garb200_multi_num_shards.argtypes = [C.c_void_p]
+        L.garb200_multi_shard.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 4
+        L.garb200_multi_upload_packed.argtypes = [C.c_void_p] * 4
+        L.garb200_multi_generate.argtypes = [C.c_void_p, C.c_uint64, C.c_int]
+        L.garb200_multi_backward.argtypes = [C.c_void_p, C.c_double, C.c_double]
+        L.garb200_multi_forward.argtypes = [C.c_void_p, C.c_void_p, C.c_int] + [C.c_void_p] * 4
+        L.garb200_multi_synchronize.argtypes = [C.c_void_p]
+        L.garb200_multi_kkt_error.argtypes = [C.c_void_p, C.c_double, C.c_double, C.c_void_p, C.c_void_p]
         L.garb200_set_tuning.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
         L.garb200_synchronize.argtypes = [C.c_void_p]
         L.garb200_destroy.argtypes = [C.c_void_p]
@@ -251,6 +269,11 @@ class Solver:
     def generate(self, seed=42, dist=0):
         check(lib().garb200_generate(self._h, C.c_uint64(seed), int(dist)))
 
+    def upload_gv(self, gv):
+        """Gv for the dense solver: [batch][T+1][nth][nc] (column-major nc x nth blocks) or None"""
+        g = None if gv is None else np.ascontiguousarray(gv, dtype=np.float64)
+        check(lib().garb200_upload_gv(self._h, _ptr(g)))
+
     def download_packed(self, first, count):
         from .layout import KnotLayout
         L = KnotLayout(self.nx, self.nu, self.nc, self.nth)
@@ -395,3 +418,72 @@ class Solver:
         a, b = C.c_float(0), C.c_float(0)
         check(lib().garb200_last_timings(self._h, C.byref(a), C.byref(b)))
         return a.value, b.value
+
+
+class MultiSolver:
+    """garb200_multi_*: one logical batched solver over several GPUs of one box (contiguous batch shards,
+    no communication inside the solve, gather by device->host or peer copies)."""
+
+    def __init__(self, nx, nu, nc=0, nth=0, horizon=1, nc0=None, batch=1, devices=(0,), flags=0, nu_term=0, nc_term=0):
+        self._h = None
+        cfg = Config()
+        cfg.nx, cfg.nu, cfg.nc, cfg.nth = nx, nu, nc, nth
+        cfg.horizon, cfg.nc0, cfg.batch, cfg.flags = horizon, (nx if nc0 is None else nc0), batch, flags
+        cfg.nu_term, cfg.nc_term = nu_term, nc_term
+        dev = np.ascontiguousarray(devices, dtype=np.int32)
+        h = C.c_void_p()
+        check(lib().garb200_multi_create(C.byref(cfg), dev.ctypes.data_as(_ip), len(dev), C.byref(h)))
+        self._h = h
+        self.nx, self.nu, self.nc, self.nth, self.horizon, self.nc0, self.batch = nx, nu, nc, nth, horizon, cfg.nc0, batch
+
+    def close(self):
+        if self._h is not None:
+            lib().garb200_multi_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def shards(self):
+        out = []
+        for i in range(lib().garb200_multi_num_shards(self._h)):
+            s, d, f, c = C.c_void_p(), C.c_int(), C.c_int(), C.c_int()
+            check(lib().garb200_multi_shard(self._h, i, C.byref(s), C.byref(d), C.byref(f), C.byref(c)))
+            out.append((d.value, f.value, c.value))
+        return out
+
+    def upload(self, pp):
+        self._keep = (np.ascontiguousarray(pp.knots), np.ascontiguousarray(pp.G0), np.ascontiguousarray(pp.g0))
+        check(lib().garb200_multi_upload_packed(self._h, *[_ptr(a) for a in self._keep]))
+
+    def generate(self, seed=42, dist=0):
+        check(lib().garb200_multi_generate(self._h, C.c_uint64(seed), int(dist)))
+
+    def backward(self, mudyn, mueq):
+        check(lib().garb200_multi_backward(self._h, float(mudyn), float(mueq)))
+
+    def forward(self, theta=None):
+        B, T = self.batch, self.horizon
+        xs, us = np.zeros((B, T + 1, self.nx)), np.zeros((B, T + 1, self.nu))
+        vs, lb = np.zeros((B, T + 1, self.nc)), np.zeros((B, self.nc0 + T * self.nx))
+        th = None if theta is None else np.ascontiguousarray(np.broadcast_to(np.asarray(theta, dtype=np.float64), (B, self.nth)))
+        check(lib().garb200_multi_forward(self._h, _ptr(th), -1, _ptr(xs), _ptr(us), _ptr(vs), _ptr(lb)))
+        self.synchronize()
+        return xs, us, vs, lb
+
+    def forward_to_device(self, root_device, d_xs, d_us, d_vs, d_lbdas, theta=None):
+        th = None if theta is None else np.ascontiguousarray(np.broadcast_to(np.asarray(theta, dtype=np.float64), (self.batch, self.nth)))
+        self._th_keep = th
+        check(lib().garb200_multi_forward(self._h, _ptr(th), int(root_device), _ptr(d_xs), _ptr(d_us), _ptr(d_vs), _ptr(d_lbdas)))
+
+    def synchronize(self):
+        check(lib().garb200_multi_synchronize(self._h))
+
+    def kkt_error(self, mudyn, mueq, theta=None):
+        out = np.zeros((self.batch, 3))
+        th = None if theta is None else np.ascontiguousarray(np.broadcast_to(np.asarray(theta, dtype=np.float64), (self.batch, self.nth)))
+        check(lib().garb200_multi_kkt_error(self._h, float(mudyn), float(mueq), _ptr(th), _ptr(out)))
+        return out

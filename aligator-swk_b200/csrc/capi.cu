@@ -171,10 +171,19 @@ int garb200_create(const garb200_config *cfg, garb200_solver **out) {
   p.GL = garb200_make_gain_layout(c.nx, c.nu, c.nc, nth_eff);
   p.VL = garb200_make_value_layout(c.nx, nth_eff);
   p.mudyn = p.mueq = 0.0;
-  const bool want_fast = !(c.flags & GARB200_FORCE_GENERIC) && fast_path_available(c.nx, c.nu, c.nc, c.nth, c.num_legs);
+  p.dense = (c.flags & GARB200_DENSE_KERNEL) ? 1 : 0;
+  p.gv = nullptr;
+  if (p.dense && legs) { delete s; return fail(GARB200_ERR_INVALID, "GARB200_DENSE_KERNEL: the dense solver has no parallel-in-time mode"); }
+  if (p.dense && dense_smem_bytes(p) > 227u * 1024u) {
+    char buf[256];
+    snprintf(buf, sizeof buf, "GARB200_DENSE_KERNEL: the (nu + nc + 2 nx)^2 stage KKT matrix needs %zu bytes of shared memory (> 227 KB)", dense_smem_bytes(p));
+    delete s;
+    return fail(GARB200_ERR_INVALID, buf);
+  }
+  const bool want_fast = !p.dense && !(c.flags & GARB200_FORCE_GENERIC) && fast_path_available(c.nx, c.nu, c.nc, c.nth, c.num_legs);
   // (a shape with a specialised sweep may exceed the generic kernel's shared-memory plan: it then has
   //  no generic fallback and ragged knots are refused at backward())
-  if (!want_fast && backward_smem_bytes(p) > 227u * 1024u) {
+  if (!want_fast && !p.dense && backward_smem_bytes(p) > 227u * 1024u) {
     char buf[256];
     snprintf(buf, sizeof buf, "dimensions need %zu bytes of shared memory per CTA (> 227 KB): "
              "nx=%d nu=%d nc=%d nth=%d not supported by this kernel generation",
@@ -209,6 +218,10 @@ int garb200_create(const garb200_config *cfg, garb200_solver **out) {
   TRYB(dmalloc(s, &p.vs, B * (T + 1) * c.nc));
   TRYB(dmalloc(s, &p.lbdas, B * (c.nc0 + (size_t)T * n)));
   TRYB(dmalloc(s, &p.theta, B * c.nth));
+  if (p.dense && c.nc * c.nth > 0) {
+    TRYB(dmalloc(s, &p.gv, B * (T + 1) * c.nc * c.nth));
+    cudaMemset(p.gv, 0, B * (T + 1) * c.nc * c.nth * sizeof(double));
+  }
   TRYB(dmalloc(s, &p.flags, B));
   TRYB(dmalloc(s, &p.refine_steps, B));
   TRYB(dmalloc(s, &s->d_kkt_out, B * 3));
@@ -439,6 +452,19 @@ int garb200_commit(garb200_solver *s) {
   return GARB200_OK;
 }
 
+int garb200_upload_gv(garb200_solver *s, const double *gv) {
+  if (!s) return fail(GARB200_ERR_INVALID, "null solver");
+  const DevParams &p = s->p;
+  if (!p.dense) return fail(GARB200_ERR_STATE, "Gv is only read by the dense solver: create with GARB200_DENSE_KERNEL");
+  const size_t len = (size_t)p.batch * (p.T + 1) * p.nc * p.nth;
+  if (len == 0) return GARB200_OK;
+  CK(cudaSetDevice(s->cfg.device));
+  if (gv) CK(cudaMemcpyAsync(p.gv, gv, len * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+  else CK(cudaMemsetAsync(p.gv, 0, len * sizeof(double), s->stream));
+  CK(cudaStreamSynchronize(s->stream));     // gv may be pageable caller memory
+  return GARB200_OK;
+}
+
 int garb200_device_problem(garb200_solver *s, double **d_knots, double **d_G0, double **d_g0) {
   if (!s) return fail(GARB200_ERR_INVALID, "null solver");
   if (d_knots) *d_knots = s->p.knots;
@@ -544,8 +570,9 @@ int garb200_backward(garb200_solver *s, double mudyn, double mueq) {
   CK(cudaEventRecord(s->ev[0], s->stream));
   const bool logb = s->tlog_bwd < s->tlog_cap;
   if (logb) CK(cudaEventRecord(s->tlog[4 * s->tlog_bwd + 0], s->stream));
-  int rc = (p.einv != nullptr) ? launch_backward_fast(p, s->nu_t.data(), s->nc_t.data(), s->stream) : -3;
-  s->used_fast = (rc >= 0);
+  int rc = p.dense ? launch_backward_dense(p, s->stream)
+                   : (p.einv != nullptr) ? launch_backward_fast(p, s->nu_t.data(), s->nc_t.data(), s->stream) : -3;
+  s->used_fast = (rc >= 0) && !p.dense;
   if (rc == -3) rc = launch_backward(p, s->stream);
   if (rc < 0) return fail(rc == -1 ? GARB200_ERR_INVALID : GARB200_ERR_CUDA,
                           std::string("backward launch failed: ") + cudaGetErrorString(cudaGetLastError()));
@@ -604,6 +631,12 @@ int garb200_forward(garb200_solver *s, const double *theta, double *xs, double *
   if (lbdas) CK(cudaMemcpyAsync(lbdas, p.lbdas, B * (p.nc0 + T * n) * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
   CK(cudaStreamSynchronize(s->stream));
   return check_flags(s);
+}
+
+int garb200_device_theta(garb200_solver *s, double **d_theta) {
+  if (!s || !d_theta) return fail(GARB200_ERR_INVALID, "null argument");
+  *d_theta = s->p.theta;
+  return GARB200_OK;
 }
 
 int garb200_device_trajectory(garb200_solver *s, double **d_xs, double **d_us, double **d_vs,

@@ -43,6 +43,8 @@ struct DevParams {
   double *kkt0_ff, *kkt0_fth, *thGrad, *thHess;  // per problem
   double *xs, *us, *vs, *lbdas;   // solver-owned trajectories
   double *theta;                  // [batch][nth] device copy (forward)
+  double *gv;                     // dense solver only: Gv [batch][T+1][nc*nth] (col-major nc x nth, logical time order) or nullptr
+  int dense;                      // 1: RiccatiSolverDense (dense.cu) instead of the proximal sweep
   // condensed system of the parallel-in-time solver (leg mode), per problem:
   // (blocks themselves are read in place from value / knot records; only factors are stored)
   double *cdiagF, *csubF, *crhs, *csol, *cerr, *csubd;
@@ -91,6 +93,9 @@ int launch_generate(const DevParams &p, uint64_t seed, int dist, cudaStream_t st
 // *d_flag = 1 iff E_t == -I exactly for every problem and knot t < T (one pass over the E blocks)
 int launch_detect_explicit(const DevParams &p, int *d_flag, cudaStream_t st);
 int fp64_peak(int kind, double *tflops);
+// dense.cu: RiccatiSolverDense (one BK of the (nu + nc + 2 nx)^2 stage KKT matrix per knot)
+int launch_backward_dense(const DevParams &p, cudaStream_t st);
+size_t dense_smem_bytes(const DevParams &p);
 // consumer.cu: device-side producer / consumers around the solve
 int launch_pack_from_device(const DevParams &p, const garb200_device_problem_view &v, double preg, cudaStream_t st);
 int launch_linear_step(const DevParams &p, double alpha, const double *const cur[4], double *const out[4], cudaStream_t st);

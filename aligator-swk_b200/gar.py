@@ -215,7 +215,7 @@ class RiccatiSolverBase:
 
 
 class _GpuSolver(RiccatiSolverBase):
-    def __init__(self, problem: LqrProblem, num_legs=0, device=0, store_all_values=True):
+    def __init__(self, problem: LqrProblem, num_legs=0, device=0, store_all_values=True, extra_flags=0):
         self.problem_ = problem
         pp = problem.pack()
         self._pp = pp
@@ -223,7 +223,7 @@ class _GpuSolver(RiccatiSolverBase):
         # the parallel-in-time solver only needs the leg heads, and keeping every value function would
         # take it off the specialised leg sweep
         self._solver = capi.Solver.for_problems(pp, num_legs=num_legs, device=device,
-                                                flags=capi.STORE_ALL_VALUES if store_all_values else 0)
+                                                flags=(capi.STORE_ALL_VALUES if store_all_values else 0) | extra_flags)
 
     def _upload(self):
         # the reference re-reads problem_->stages on every backward() (proximal-riccati.hxx:37)
@@ -307,19 +307,23 @@ class ProximalRiccatiSolver(_GpuSolver):
 
 
 class RiccatiSolverDense(ProximalRiccatiSolver):
-    """dense-riccati.hpp:28-58 — same constructor and virtuals.  The reference's dense solver factors
-    the (nu + nc + 2 nx)^2 stage KKT matrix per knot (dense-kernel.hpp:56-212) and returns the solution
-    the proximal sweep returns; on the GPU both names run the same sweep.  One documented difference:
-    only the reference's DENSE kernel reads Gv (dense-kernel.hpp:76,134; the proximal kernel zeroes
-    that right-hand side, riccati-kernel.hxx:128,272), so a problem with a non-zero Gv is refused here
-    instead of being solved with the proximal semantics."""
+    """dense-riccati.hpp:28-58, GPU-backed (csrc/dense.cu): one Bunch-Kaufman factorization of the
+    (nu + nc + 2 nx)^2 stage KKT matrix per knot (dense-kernel.hpp:56-212) instead of the proximal sweep.
+    Same constructor, virtuals and gains layout; unlike the proximal kernel it reads Gv
+    (dense-kernel.hpp:76,134 vs riccati-kernel.hxx:128,272)."""
 
     def __init__(self, problem: LqrProblem, device=0):
-        for t, k in enumerate(problem.stages):
-            if np.any(np.asarray(k.Gv) != 0.0):
-                raise ValueError(f"RiccatiSolverDense (GPU): knot {t} has a non-zero Gv, which the proximal "
-                                 "sweep does not read (riccati-kernel.hxx:128,272)")
-        super().__init__(problem, device)
+        _GpuSolver.__init__(self, problem, 0, device, store_all_values=True, extra_flags=capi.DENSE_KERNEL)
+
+    def _upload(self):
+        super()._upload()
+        st = self.problem_.stages
+        nc, nth = max(k.nc for k in st), st[0].nth
+        if nc * nth:
+            gv = np.zeros((1, len(st), nth, nc))
+            for t, k in enumerate(st):
+                gv[0, t, :, :k.nc] = np.asarray(k.Gv, dtype=np.float64).reshape(k.nc, nth).T
+            self._solver.upload_gv(gv)
 
 
 class ParallelRiccatiSolver(_GpuSolver):

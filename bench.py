@@ -253,6 +253,10 @@ def gpu_arm(args, w, rank, world, local_rank):
         dist = dist_mod
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     nx, nu, nc, nth, T, B, legs = w["nx"], w["nu"], w["nc"], w["nth"], w["T"], w["batch"], w["legs"]
+    if args.scaling == "strong":          # the config's batch is the GLOBAL batch: contiguous slices
+        lo, hi = sharding.shard_bounds(B, rank, world)
+        B = hi - lo
+        w = dict(w, batch=B)
     K, W = args.steps, args.warmup
     s = capi.Solver(nx, nu, nc, nth, horizon=T, batch=B, num_legs=legs, device=local_rank)
     s.set_tuning(**args.tune_knobs)
@@ -274,11 +278,49 @@ def gpu_arm(args, w, rank, world, local_rank):
     # sweep): the forward kernel writes straight into the send buffer.
     send = recv = None
     out_ptrs = [{}, {}]
+    p2p_dst = None
+    gather_kind = None
     if dist is not None:
         sizes = sharding.trajectory_sizes(B, T, nx, nu, nc)
         # two send buffers: the forward rollout of step i+1 writes the other one while step i's is in flight
-        send = [torch.empty(sum(sizes), dtype=torch.float64, device="cuda") for _ in range(2)]
-        recv = [torch.empty_like(send[0]) for _ in range(world)] if rank == 0 else None
+        nmax = torch.tensor([sum(sizes)], dtype=torch.int64, device="cuda")
+        dist.all_reduce(nmax, op=dist.ReduceOp.MAX)
+        slot = int(nmax.item())            # strong scaling: slices differ by at most one problem
+        send = [torch.zeros(slot, dtype=torch.float64, device="cuda") for _ in range(2)]
+        recv_flat = torch.empty(world * slot, dtype=torch.float64, device="cuda") if rank == 0 else None
+        recv = [recv_flat[r * slot: r * slot + slot] for r in range(world)] if rank == 0 else None
+        gather_kind = "nccl"
+        if args.gather in ("auto", "p2p"):
+            # SM-free gather: rank 0 exports its receive buffer (CUDA IPC), every rank maps it and copies its
+            # slice there with a plain device-to-device copy (copy engines over NVLink) on a side stream
+            ok, handle = 1, [None]
+            try:
+                if rank == 0:
+                    handle = [recv_flat.untyped_storage()._share_cuda_()]
+            except Exception:
+                ok = 0
+            dist.broadcast_object_list(handle, src=0)
+            try:
+                if rank != 0 and handle[0] is not None:
+                    st = torch.UntypedStorage._new_shared_cuda(*handle[0])
+                    full = torch.empty(0, dtype=torch.float64, device=st.device).set_(st)
+                    p2p_dst = full[rank * slot: rank * slot + slot]
+                    p2p_dst.copy_(send[0])          # exercises the peer mapping once
+                    torch.cuda.synchronize()
+                elif rank == 0:
+                    p2p_dst = recv_flat[:slot]
+                else:
+                    ok = 0
+            except Exception:
+                ok = 0
+            flag = torch.tensor([ok], dtype=torch.int32, device="cuda")
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            if int(flag.item()) == 1:
+                gather_kind = "p2p"
+            else:
+                p2p_dst = None
+                if args.gather == "p2p":
+                    raise SystemExit("bench.py: --gather p2p requested but the CUDA IPC mapping failed on some rank")
         for k in range(2):
             for name, view in zip(("d_xs", "d_us", "d_vs", "d_lbdas"), sharding.carve(send[k], sizes)):
                 out_ptrs[k][name] = view.data_ptr()
@@ -302,7 +344,10 @@ def gpu_arm(args, w, rank, world, local_rank):
         if dist is not None:
             side.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(side):
-                sharding.gather_to_root(dist, send[k], rank, world, recv)
+                if p2p_dst is not None:
+                    p2p_dst.copy_(send[k], non_blocking=True)
+                else:
+                    sharding.gather_to_root(dist, send[k], rank, world, recv)
                 ev = torch.cuda.Event()
                 ev.record(side)
                 gathered[k] = ev
@@ -350,7 +395,10 @@ def gpu_arm(args, w, rank, world, local_rank):
         par.update(max_rel_err=float(red[4]), kkt_gpu=float(red[5]), kkt_oracle=float(red[6]), ranks=world,
                    problems=par["problems"] * world)
     ms_step = ms_total / K
-    value = B * world / (ms_step * 1e-3)
+    btot = torch.tensor([B], dtype=torch.int64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(btot)
+    value = int(btot.item()) / (ms_step * 1e-3)
 
     # ---- e2e: host buffers through the C ABI, H2D + D2H inside the timed region ----------
     e2e = None
@@ -406,7 +454,7 @@ def gpu_arm(args, w, rank, world, local_rank):
     cpu_v, cores, sample = cpu_port_throughput(w, budget_s=args.cpu_budget, dist=args.dist)
     line = {
         "metric": "batched LQ solves/sec (bwd+fwd)", "value": value, "unit": "solves/s", "n_gpus": world,
-        "steps": K, "warmup": W, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+        "steps": K, "warmup": W, "ms_per_step": ms_step, "higher_is_better": True, "scaling": args.scaling,
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": workload_config(args.workload, w, world, args.dist),
         "explicit_path": bool(s.used_explicit_path()),
@@ -417,7 +465,11 @@ def gpu_arm(args, w, rank, world, local_rank):
                          "gflops_per_core": cpu_v * f_all / max(cores, 1) / 1e9,
                          "note": "Eigen-free port of the reference algorithm (oracle/): malloc-free stage solve, register-blocked GEMM, 4-RHS blocked triangular solves; the reference itself needs Eigen 3.4 (not installable here)"},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
-        "collective": None if world == 1 else "one NCCL gather of (xs,us,vs,lbdas) to rank 0 per step, on a side stream (overlaps the next backward sweep)",
+        "collective": None if world == 1 else (
+            "one gather of (xs,us,vs,lbdas) to rank 0 per step on a side stream (overlaps the next backward sweep): "
+            + ("device-to-device copies into rank 0's buffer through a CUDA IPC mapping — copy engines over NVLink, no kernel on any SM"
+               if gather_kind == "p2p" else "NCCL gather")),
+        "gather": gather_kind,
     }
     if world == 1 and not args.no_e2e:
         line["consumers"] = consumer_bandwidth(torch, s, w, hbm_peak)
@@ -430,6 +482,7 @@ def gpu_arm(args, w, rank, world, local_rank):
             dname = dname or "ref"
             if name in WORKLOADS and dname in DIST_DESC and (name, dname) != (args.workload, args.dist):
                 line["other_configs"][spec] = short_run(torch, capi, name, local_rank, hbm_peak, fp64_peak, dist=dname)
+    line["config"]["global_batch"] = int(btot.item())
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()
@@ -676,6 +729,10 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU-port timing")
     ap.add_argument("--parity-k", type=int, default=8, help="problems per rank re-solved by the CPU oracle after the timed region (0: off)")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: every rank gets the config's batch; strong: the config's batch is split over the ranks")
+    ap.add_argument("--gather", default="auto", choices=["auto", "p2p", "nccl"],
+                    help="trajectory gather to rank 0: peer copies through CUDA IPC (no SMs) or NCCL; auto tries p2p first")
     ap.add_argument("--dist", default="ref", choices=["ref", "explicit", "explicit_psd"], help="synthetic distribution (SURVEY 8d)")
     ap.add_argument("--others", default="c2,c3,c5,c1b+explicit_psd,c2+explicit_psd,c1b+explicit", help="other BASELINE configs summarised in other_configs at N = 1 ('' = none)")
     ap.add_argument("--tune", action="append", default=[], help="diagnostic launcher knob key=value (garb200_set_tuning)")

@@ -57,6 +57,10 @@ extern "C" {
                                         explicit-dynamics.hxx:32): E is never read and the device-side
                                         check that garb200_backward otherwise runs after every change
                                         of the problem is skipped                                  */
+#define GARB200_DENSE_KERNEL 16      /* RiccatiSolverDense (dense-riccati.hpp:28-58): one Bunch-Kaufman
+                                        factorization of the (nu + nc + 2 nx)^2 stage KKT matrix per knot
+                                        (dense-kernel.hpp:56-212) instead of the proximal sweep; reads Gv
+                                        (garb200_upload_gv); the slow, sturdy path; num_legs must be 0   */
 #define GARB200_PHASE_TIMERS 4       /* diagnostic: per-phase clock64 timers in the specialised
                                         sweep (garb200_phase_cycles); slower instrumented kernel */
 
@@ -127,6 +131,10 @@ int garb200_stage_knot(garb200_solver *s, int problem, int t, const garb200_knot
 int garb200_stage_initial(garb200_solver *s, int problem, const double *G0, const double *g0);
 /* H2D of everything staged so far */
 int garb200_commit(garb200_solver *s);
+/* Gv of every knot for the DENSE solver (GARB200_DENSE_KERNEL; the proximal kernel never reads it,
+ * riccati-kernel.hxx:128,272 vs dense-kernel.hpp:76,134): host [batch][T+1][nc * nth], column-major nc x nth
+ * blocks with the solver's max nc as leading dimension, logical time order; NULL = zeros */
+int garb200_upload_gv(garb200_solver *s, const double *gv);
 /* raw device pointers of the resident problem (for upstream device producers) */
 int garb200_device_problem(garb200_solver *s, double **d_knots, double **d_G0, double **d_g0);
 /* ---- device-resident producer ------------------------------------------------
@@ -174,6 +182,31 @@ int garb200_forward_device(garb200_solver *s, const double *d_theta, double *d_x
 /* solver-owned device trajectory buffers (valid after forward*) */
 int garb200_device_trajectory(garb200_solver *s, double **d_xs, double **d_us, double **d_vs,
                               double **d_lbdas);
+
+/* solver-owned device buffer for theta, [batch][nth] (input of garb200_forward_device) */
+int garb200_device_theta(garb200_solver *s, double **d_theta);
+
+/* ---- several GPUs of one box behind ONE logical solver (SURVEY 8(b) "multi-GPU by opts.devices[]", 8(e)) ----
+ * The reference has no counterpart (its ParallelRiccatiSolver parallelises ONE problem over CPU threads);
+ * independent problems shard with no communication inside backward / forward.  cfg->batch is the GLOBAL
+ * batch, cfg->device is ignored; GPU g of devices[] owns problems [g B / G, (g + 1) B / G).  One host
+ * thread drives all devices (every call is asynchronous).  The only exchange is the gather of the
+ * trajectories in garb200_multi_forward: root_device < 0 -> HOST output pointers for the global batch (each
+ * device copies its slice to its offset); root_device >= 0 -> DEVICE pointers on that GPU, slices arrive by
+ * cudaMemcpyPeerAsync (copy engines over NVLink: no kernel competes with the next sweep for SMs).
+ * Parallel-in-time mode does not shard (one problem = one GPU): create one solver per device instead. */
+typedef struct garb200_multi garb200_multi;
+int garb200_multi_create(const garb200_config *cfg, const int *devices, int ndev, garb200_multi **out);
+void garb200_multi_destroy(garb200_multi *m);
+int garb200_multi_num_shards(const garb200_multi *m);
+int garb200_multi_shard(garb200_multi *m, int i, garb200_solver **solver, int *device, int *first, int *count);
+int garb200_multi_upload_packed(garb200_multi *m, const double *knots, const double *G0, const double *g0);
+int garb200_multi_generate(garb200_multi *m, uint64_t seed, int dist);
+int garb200_multi_backward(garb200_multi *m, double mudyn, double mueq);
+int garb200_multi_forward(garb200_multi *m, const double *theta, int root_device, double *xs, double *us,
+                          double *vs, double *lbdas);
+int garb200_multi_synchronize(garb200_multi *m);
+int garb200_multi_kkt_error(garb200_multi *m, double mudyn, double mueq, const double *theta, double *out);
 
 /* ---- device-resident consumers -----------------------------------------------
  * SolverProxDDPTpl::tryLinearStep (vector spaces)    solver-proxddp.hxx:104-148

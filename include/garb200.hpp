@@ -122,7 +122,7 @@ inline void check(int rc, const char *what) {
 /// Shared implementation: one problem (batch = 1) behind a garb200_solver handle.
 class GpuSolver : public RiccatiSolverBase {
 public:
-  GpuSolver(const LqrProblem &problem, int num_legs, int device) : problem_(&problem) {
+  GpuSolver(const LqrProblem &problem, int num_legs, int device, int extra_flags = 0) : problem_(&problem) {
     const int T = problem.horizon();
     if (T < 0) throw std::runtime_error("garb200: empty problem");
     nx_ = problem.stages[0].nx;
@@ -140,7 +140,7 @@ public:
     cfg.device = device;
     // datas[t].vm of every knot belongs to the serial solver's public state; the parallel-in-time solver
     // keeps the leg heads only (storing all of them would take it off the specialised leg sweep)
-    cfg.flags = num_legs >= 2 ? 0 : GARB200_STORE_ALL_VALUES;
+    cfg.flags = (num_legs >= 2 ? 0 : GARB200_STORE_ALL_VALUES) | extra_flags;
     cfg.nu_t = nu_t_.data(); cfg.nc_t = nc_t_.data();
     check(garb200_create(&cfg, &h_), "garb200_create");
     if (!h_) throw std::runtime_error(std::string("garb200_create: ") + garb200_last_error());
@@ -219,7 +219,8 @@ protected:
 /// proximal-riccati.hpp:12-45
 class ProximalRiccatiSolver : public detail::GpuSolver {
 public:
-  explicit ProximalRiccatiSolver(const LqrProblem &problem, int device = 0) : GpuSolver(problem, 0, device) {}
+  explicit ProximalRiccatiSolver(const LqrProblem &problem, int device = 0, int extra_flags = 0)
+      : GpuSolver(problem, 0, device, extra_flags) {}
   struct kkt0_t { Vec ff, fth; };
   kkt0_t kkt0() {
     const int s0 = nx_ + problem_->nc0();
@@ -231,20 +232,30 @@ public:
   Vec thHess() { Vec H((size_t)nth_ * nth_); detail::check(garb200_get_initial(h_, 0, nullptr, nullptr, nullptr, H.data()), "garb200_get_initial"); return H; }
 };
 
-/// dense-riccati.hpp:28-58 — same constructor and virtuals; on the GPU it runs the proximal sweep (the two
-/// reference solvers return the same solution).  Only the reference's dense kernel reads Gv
-/// (dense-kernel.hpp:76,134 vs riccati-kernel.hxx:128,272): a non-zero Gv is refused.
+/// dense-riccati.hpp:28-58 — same constructor and virtuals, GPU-backed by csrc/dense.cu: one Bunch-Kaufman
+/// factorization of the (nu + nc + 2 nx)^2 stage KKT matrix per knot (dense-kernel.hpp:56-212).  Reads Gv
+/// (dense-kernel.hpp:76,134), which the proximal kernel ignores (riccati-kernel.hxx:128,272).
 class RiccatiSolverDense : public ProximalRiccatiSolver {
 public:
-  explicit RiccatiSolverDense(const LqrProblem &problem, int device = 0) : ProximalRiccatiSolver(check_gv(problem), device) {}
+  explicit RiccatiSolverDense(const LqrProblem &problem, int device = 0)
+      : ProximalRiccatiSolver(problem, device, GARB200_DENSE_KERNEL) {}
+  bool backward(double mudyn, double mueq) override {
+    const LqrProblem &p = *problem_;
+    const int T = p.horizon();
+    if (nc_ * nth_ > 0) {                        // Gv is not part of the packed knot record
+      gv_.assign((size_t)(T + 1) * nc_ * nth_, 0.0);
+      for (int t = 0; t <= T; t++) {
+        const LqrKnot &k = p.stages[t];
+        for (int j = 0; j < nth_; j++)
+          for (int i = 0; i < k.nc; i++) gv_[(size_t)t * nc_ * nth_ + i + (size_t)j * nc_] = k.Gv(i, j);
+      }
+      detail::check(garb200_upload_gv(h_, gv_.data()), "garb200_upload_gv");
+    }
+    return ProximalRiccatiSolver::backward(mudyn, mueq);
+  }
 
 private:
-  static const LqrProblem &check_gv(const LqrProblem &p) {
-    for (const auto &k : p.stages)
-      for (double v : k.Gv.v)
-        if (v != 0.0) throw std::domain_error("RiccatiSolverDense (GPU): non-zero Gv is not read by the proximal sweep");
-    return p;
-  }
+  Vec gv_;
 };
 
 /// parallel-solver.hpp:24-108 — legs are CTAs instead of OpenMP threads.

@@ -149,6 +149,41 @@ int gar_oracle_prox_solve(int nx, int nu, int nc, int nth, int T, int nc0, const
   return 0;
 }
 
+/// RiccatiSolverDense backward + forward on one packed problem.  gv: [T+1][nc * nth] column-major blocks
+/// with the solver's MAX nc as leading dimension, or NULL (zeros) — Gv is not part of the packed knot record.
+int gar_oracle_dense_solve(int nx, int nu, int nc, int nth, int T, int nc0, const int *nu_t,
+                           const int *nc_t, const double *knots, const double *G0, const double *g0,
+                           const double *gv, double mudyn, double mueq, const double *theta, double *gains,
+                           double *values, double *kkt0_ff, double *kkt0_fth, double *thGrad, double *thHess,
+                           double *oxs, double *ous, double *ovs, double *olb, double *kkt_err) {
+  Problem p = unpack_problem(nx, nu, nc, nth, T, nc0, nu_t, nc_t, knots, G0, g0);
+  if (gv)
+    for (int t = 0; t <= T; t++) {
+      Knot &k = p.stages[t];
+      for (int j = 0; j < nth; j++)
+        for (int i = 0; i < k.nc; i++) k.Gv(i, j) = gv[(size_t)t * nc * nth + i + (size_t)j * nc];
+    }
+  RiccatiSolverDense solver(p);
+  solver.backward(mudyn, mueq);
+  std::vector<Mat> xs, us, vs, lbdas;
+  lqrInitializeSolution(p, xs, us, vs, lbdas);
+  if (us.size() < (size_t)T + 1) us.resize(T + 1);
+  Mat th(nth);
+  if (theta) th.load(theta);
+  solver.forward(xs, us, vs, lbdas, theta ? &th : nullptr);
+  export_factors(solver.datas, nx, nu, nc, nth, gains, values);
+  if (kkt0_ff) solver.kkt0.ff.store(kkt0_ff);
+  if (kkt0_fth && nth > 0) store_rowmajor(solver.kkt0.fth, kkt0_fth);
+  if (thGrad && nth > 0) solver.thGrad.store(thGrad);
+  if (thHess && nth > 0) solver.thHess.store(thHess);
+  if (oxs) export_traj(xs, us, vs, lbdas, nx, nu, nc, nc0, T, oxs, ous, ovs, olb);
+  if (kkt_err) {   // (lqrComputeKktError has no Gv term, utils.hxx:94-192: meaningful for Gv = 0 only)
+    auto e = lqrComputeKktError(p, xs, us, vs, lbdas, mudyn, mueq, theta ? &th : nullptr);
+    kkt_err[0] = e[0]; kkt_err[1] = e[1]; kkt_err[2] = e[2];
+  }
+  return 0;
+}
+
 /// ParallelRiccatiSolver (num_legs >= 2) on one packed problem with nth = 0.
 /// gains/values use the layout built with nth = nx (the legs' parameter dimension).
 /// info[0] = refinement steps taken, info[1] = block-tridiagonal solve ok.

@@ -95,6 +95,20 @@ struct ProximalRiccatiSolver {
                std::vector<Mat> &lbdas, const Mat *theta = nullptr) const;
 };
 
+/// dense-riccati.hpp:28-58 / dense-riccati.hxx, DenseKernel dense-kernel.hpp:56-212 (oracle/dense.cpp).
+/// Shares StageFactor::{ff, fb, fth} (block rows [K; Z; L; Y]) and Value {Pmat = Pxx, pvec = px, Vxt = Pxt,
+/// Vtt = Ptt, vt = pt} with the proximal solver.  Reads Gv.
+struct RiccatiSolverDense {
+  std::vector<StageFactor> datas;
+  Kkt0 kkt0;
+  Mat thGrad, thHess;
+  const Problem *problem;
+  explicit RiccatiSolverDense(const Problem &p);
+  bool backward(double mudyn, double mueq);
+  bool forward(std::vector<Mat> &xs, std::vector<Mat> &us, std::vector<Mat> &vs,
+               std::vector<Mat> &lbdas, const Mat *theta = nullptr) const;
+};
+
 /// work.hpp:17-22
 inline std::array<int, 2> get_work(int horz, int tid, int nthreads) {
   return {(int)((long)tid * (horz + 1) / nthreads), (int)((long)(tid + 1) * (horz + 1) / nthreads)};

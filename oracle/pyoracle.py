@@ -116,6 +116,32 @@ def prox_solve(pp, mudyn, mueq, theta=None, b=0):
     return out
 
 
+def dense_solve(pp, mudyn, mueq, theta=None, gv=None, b=0):
+    """RiccatiSolverDense (dense-kernel.hpp:56-212, dense-riccati.hxx:46-118) on problem ``b``.
+    gv: [T+1][nth][nc] array (column-major nc x nth blocks) or None; same outputs as prox_solve."""
+    nx, nu, nc, nth, T, nc0 = _dims(pp)
+    _, gs, vs_ = _strides(nx, nu, nc, nth)
+    out = {
+        "gains": np.zeros((T + 1, gs)), "values": np.zeros((T + 1, vs_)),
+        "kkt0_ff": np.zeros(nx + nc0), "kkt0_fth": np.zeros((nx + nc0, nth)),
+        "thGrad": np.zeros(nth), "thHess": np.zeros((nth, nth)),
+        "xs": np.zeros((T + 1, nx)), "us": np.zeros((T + 1, nu)), "vs": np.zeros((T + 1, nc)),
+        "lbdas": np.zeros(nc0 + T * nx), "kkt": np.zeros(3),
+    }
+    th = None if theta is None else np.ascontiguousarray(theta, dtype=np.float64)
+    g = None if gv is None else np.ascontiguousarray(gv, dtype=np.float64)
+    knots = np.ascontiguousarray(pp.knots[b]); G0 = np.ascontiguousarray(pp.G0[b])
+    g0 = np.ascontiguousarray(pp.g0[b])
+    rc = lib().gar_oracle_dense_solve(
+        nx, nu, nc, nth, T, nc0, _i(pp.nu_t), _i(pp.nc_t), _d(knots), _d(G0), _d(g0), _d(g),
+        C.c_double(mudyn), C.c_double(mueq), _d(th), _d(out["gains"]), _d(out["values"]),
+        _d(out["kkt0_ff"]), _d(out["kkt0_fth"]), _d(out["thGrad"]), _d(out["thHess"]),
+        _d(out["xs"]), _d(out["us"]), _d(out["vs"]), _d(out["lbdas"]), _d(out["kkt"]))
+    assert rc == 0
+    out["thHess"] = out["thHess"].T.copy()
+    return out
+
+
 def parallel_solve(pp, mudyn, mueq, num_legs, collapse=False, b=0):
     nx, nu, nc, nth, T, nc0 = _dims(pp)
     assert nth == 0

@@ -156,3 +156,38 @@ def test_linear_step_and_rollout_device(capi, dims):
                 assert np.abs(dl[b, nx + t * nx: nx + (t + 1) * nx] - ref).max() <= 1e-13 * scale
     assert np.isnan(dl[:, :nx]).all()        # dlams[0] is not written
     s.close()
+
+
+@pytest.mark.parametrize("ndev_same", [1, 2, 3])
+def test_multi_device_handle_shards_and_gathers(capi, oracle, ndev_same):
+    """garb200_multi_* (SURVEY 8(b) multi-GPU by devices[], 8(e)): contiguous batch slices, no communication
+    inside the solve, gather to host and to a root device.  On a 1-GPU box the shards share device 0 —
+    the slicing / offset logic is the same; with more GPUs visible the shards spread over them."""
+    import torch
+    ngpu = torch.cuda.device_count()
+    devices = [i % ngpu for i in range(ndev_same)]
+    nx, nu, nc, nth, T, B, mu = 12, 4, 2, 1, 9, 7, 1e-9
+    pp = generate_problems(B, T, nx, nu, nc, nth, seed=31)
+    theta = np.random.default_rng(3).standard_normal((B, nth))
+    m = capi.MultiSolver(nx, nu, nc, nth, horizon=T, batch=B, devices=devices)
+    sh = m.shards()
+    assert [f for _, f, _ in sh] == [g * B // ndev_same for g in range(ndev_same)] and sum(c for _, _, c in sh) == B
+    m.upload(pp)
+    m.backward(mu, mu)
+    xs, us, vs, lb = m.forward(theta)
+    for b in range(B):
+        ref = oracle.prox_solve(pp, mu, mu, theta=theta[b], b=b)
+        for got, key in ((xs[b], "xs"), (us[b], "us"), (vs[b], "vs"), (lb[b], "lbdas")):
+            assert relerr(got, ref[key]) < 1e-10, (b, key)
+    kkt = m.kkt_error(mu, mu, theta)
+    assert kkt.shape == (B, 3) and kkt.max() < 1e-8
+    # gather to the root device by peer copies
+    dev = [torch.full(a.shape, float("nan"), dtype=torch.float64, device="cuda:0") for a in (xs, us, vs, lb)]
+    m.forward_to_device(0, *[d.data_ptr() for d in dev], theta=theta)
+    m.synchronize()
+    torch.cuda.synchronize()
+    for d, h in zip(dev, (xs, us, vs, lb)):
+        assert np.array_equal(d.cpu().numpy(), h)
+    m.close()
+    with pytest.raises(capi.GarB200Error):
+        capi.MultiSolver(nx, nu, horizon=T, batch=1, devices=[0, 0])     # fewer problems than devices

@@ -200,23 +200,105 @@ def test_gar_mirror_api(capi, oracle):
 
 
 def test_gar_mirror_dense_solver(capi, oracle):
-    """RiccatiSolverDense (dense-riccati.hpp:28-58) through the host mirror: same API, same solution as
-    the proximal solver (tests/gar/riccati.cpp:143-157), non-zero Gv refused."""
+    """RiccatiSolverDense (dense-riccati.hpp:28-58) through the host mirror: same API and the same solution as
+    the proximal solver (tests/gar/riccati.cpp:143-157) — from a different kernel (csrc/dense.cu), compared
+    with the oracle's own restatement of the dense kernel; a non-zero Gv is READ (dense-kernel.hpp:76,134)."""
     from aligator_swk_b200 import gar
     from test_oracle import short_horz_pb
     prob = short_horz_pb()
     dense = gar.RiccatiSolverDense(prob)
     assert dense.backward(1e-14, 1e-14)
+    assert not dense._solver.used_fast_path()
     xs, us, vs, lbdas = gar.lqrInitializeSolution(prob)
     assert dense.forward(xs, us, vs, lbdas)
     assert gar.lqrComputeKktError(prob, xs, us, vs, lbdas, 0.0, 0.0).max() <= 1e-9
-    ref = oracle.prox_solve(prob.pack(), 1e-14, 1e-14)
+    ref = oracle.dense_solve(prob.pack(), 1e-14, 1e-14)
     assert relerr(np.array(xs), ref["xs"]) < RTOL
-    prob.stages[0].addParameterization(1)
-    if prob.stages[0].nc:
-        prob.stages[0].Gv[:] = 1.0
-        with pytest.raises(ValueError):
-            gar.RiccatiSolverDense(prob)
+    assert relerr(np.array(xs), oracle.prox_solve(prob.pack(), 1e-14, 1e-14)["xs"]) < 1e-9
+    # Gv != 0 changes the answer of the dense solver and only of the dense solver
+    prob.addParameterization(1)
+    rng = np.random.default_rng(3)
+    for k in prob.stages:
+        k.Gx[:] = rng.standard_normal(k.Gx.shape); k.Gu[:] = rng.standard_normal(k.Gu.shape)
+        k.Gth[:] = 1.0; k.gamma[:] = rng.standard_normal(1)
+        if k.nc:
+            k.Gv[:] = rng.standard_normal(k.Gv.shape)
+    theta = np.array([0.7])
+    dense = gar.RiccatiSolverDense(prob)
+    assert dense.backward(1e-10, 1e-10)
+    xs, us, vs, lbdas = gar.lqrInitializeSolution(prob)
+    dense.forward(xs, us, vs, lbdas, theta)
+    pp = prob.pack()
+    gv = np.zeros((len(prob.stages), 1, pp.layout.nc))
+    for t, k in enumerate(prob.stages):
+        gv[t, :, :k.nc] = np.asarray(k.Gv).reshape(k.nc, 1).T
+    ref = oracle.dense_solve(pp, 1e-10, 1e-10, theta=theta, gv=gv)
+    ref0 = oracle.dense_solve(pp, 1e-10, 1e-10, theta=theta, gv=None)
+    assert relerr(ref["vs"], ref0["vs"]) > 1e-6                      # Gv matters
+    assert relerr(np.array(xs), ref["xs"]) < RTOL
+    U = np.zeros_like(ref["us"])
+    for t, u in enumerate(us):
+        U[t, :len(u)] = u
+    assert relerr(U, ref["us"]) < RTOL
+    assert relerr(dense.thGrad, ref["thGrad"]) < 1e-9 and relerr(dense.thHess, ref["thHess"]) < 1e-9
+
+
+DENSE_CASES = [
+    # nx, nu, nc, nth, T, B, mu, dist
+    (12, 4, 0, 0, 50, 3, 1e-11, "ref"),
+    (36, 12, 0, 0, 100, 2, 1e-11, "ref"),          # C1 shape at its own size
+    (36, 12, 6, 4, 30, 2, 1e-9, "ref"),
+    (7, 5, 3, 2, 9, 3, 1e-6, "ref"),
+    (5, 0, 2, 0, 6, 2, 1e-6, "ref"),               # nu = 0
+    (2, 2, 0, 0, 0, 2, 1e-10, "ref"),              # horizon 0
+    (36, 12, 0, 0, 20, 2, 1e-9, "explicit"),       # indefinite stages: what the dense solver is for
+]
+
+
+@pytest.mark.parametrize("case", DENSE_CASES, ids=lambda c: "nx%d_nu%d_nc%d_nth%d_T%d_B%d_%g_%s" % c)
+def test_dense_kernel_parity(capi, oracle, case):
+    """csrc/dense.cu against the oracle's restatement of DenseKernel / RiccatiSolverDense (oracle/dense.cpp):
+    trajectories, gains knot by knot, value function, kkt0, thGrad / thHess; random non-zero Gv."""
+    nx, nu, nc, nth, T, B, mu, dist = case
+    pp = generate_problems(B, T, nx, nu, nc, nth, seed=nx + 7 * T, dist=dist)
+    rng = np.random.default_rng(2)
+    theta = rng.standard_normal((B, nth)) if nth else None
+    gv = rng.standard_normal((B, T + 1, nth, nc)) if nc * nth else None
+    s = capi.Solver.for_problems(pp, flags=capi.DENSE_KERNEL | capi.STORE_ALL_VALUES)
+    s.upload(pp)
+    if gv is not None:
+        s.upload_gv(gv)
+    s.backward(mu, mu)
+    assert not s.used_fast_path()
+    xs, us, vs, lb = s.forward(theta)
+    assert (s.get_flags() == 0).all()
+    G = GainLayout(nx, nu, nc, nth)
+    gains = s.download_gains()
+    from aligator_swk_b200.layout import ValueLayout
+    for b in range(B):
+        th = None if theta is None else theta[b]
+        ref = oracle.dense_solve(pp, mu, mu, theta=th, gv=None if gv is None else gv[b], b=b)
+        for got, key in ((xs[b], "xs"), (us[b], "us"), (vs[b], "vs"), (lb[b], "lbdas")):
+            assert relerr(got, ref[key]) < RTOL, (b, key, relerr(got, ref[key]))
+        for t in range(T + 1):
+            a = G.unpack(gains[b, t], pp.nu_t[t], pp.nc_t[t])
+            r = G.unpack(ref["gains"][t], pp.nu_t[t], pp.nc_t[t])
+            scale = max(np.abs(r[1]).max() if r[1].size else 0.0, np.abs(r[0]).max() if r[0].size else 0.0, 1e-300)
+            for x, y in zip(a, r):
+                if x.size:
+                    assert np.abs(x - y).max() / scale < RTOL_GAINS, (b, t)
+        v0, rv0 = s.get_value(b, 0), ValueLayout(nx, nth).unpack(ref["values"][0])
+        assert relerr(v0["Pmat"], rv0["Pmat"]) < RTOL_GAINS and relerr(v0["pvec"], rv0["pvec"]) < RTOL_GAINS
+        ff0, fth0, thg, thh = s.get_initial(b)
+        assert relerr(ff0, ref["kkt0_ff"]) < RTOL
+        if nth:
+            assert relerr(fth0, ref["kkt0_fth"]) < RTOL_GAINS
+            assert relerr(thg, ref["thGrad"]) < RTOL_GAINS and relerr(thh, ref["thHess"]) < RTOL_GAINS
+    s.close()
+    with pytest.raises(capi.GarB200Error):           # no parallel-in-time mode, stage matrix must fit shared memory
+        capi.Solver(12, 4, horizon=8, num_legs=2, flags=capi.DENSE_KERNEL)
+    with pytest.raises(capi.GarB200Error):
+        capi.Solver(76, 32, horizon=4, flags=capi.DENSE_KERNEL)
 
 
 def test_error_conventions(capi):

@@ -200,3 +200,23 @@ def test_golden_vectors(oracle):
             assert relerr(out[k], gold[k]) < 1e-12, (f, k)
             if theta is None:
                 assert relerr(out[k], gold["dense_" + k]) < 1e-9, (f, k)
+
+
+@pytest.mark.parametrize("dims", [(36, 12, 0, 0, 100, 1e-14), (12, 4, 3, 2, 30, 1e-10), (3, 2, 0, 1, 100, 1e-12)],
+                         ids=lambda d: "nx%d_nu%d_nc%d_nth%d_T%d_mu%g" % d)
+def test_dense_solver_restatement(oracle, dims):
+    """RiccatiSolverDense (dense-kernel.hpp:56-212, dense-riccati.hxx:46-118) restated in oracle/dense.cpp: the
+    reference's own check (tests/gar/riccati.cpp:143-157) — KKT <= 1e-9 and the same solution as the proximal
+    solver — plus agreement with the dense LAPACK solve of the lqrDenseMatrix KKT system."""
+    nx, nu, nc, nth, T, mu = dims
+    pp = generate_problems(2, T, nx, nu, nc, nth, seed=nx + T, same_knot=(nx == 36), **({"x0": np.zeros(nx)} if nx == 36 else {}))
+    th = np.random.default_rng(1).standard_normal(nth) if nth else None
+    for b in range(2):
+        d = oracle.dense_solve(pp, mu, mu, theta=th, b=b)
+        a = oracle.prox_solve(pp, mu, mu, theta=th, b=b)
+        assert d["kkt"].max() <= 1e-9
+        for k in ("xs", "us", "vs", "lbdas"):
+            assert relerr(d[k], a[k]) < 1e-9, (dims, b, k)
+        if nth == 0:
+            xs, us, vs, lb = dense_solve(oracle, pp, mu, b)
+            assert relerr(d["xs"], xs) < 1e-9 and relerr(d["us"], us) < 1e-9
