@@ -731,8 +731,10 @@ def main():
     ap.add_argument("--parity-k", type=int, default=8, help="problems per rank re-solved by the CPU oracle after the timed region (0: off)")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak: every rank gets the config's batch; strong: the config's batch is split over the ranks")
-    ap.add_argument("--gather", default="auto", choices=["auto", "p2p", "nccl"],
-                    help="trajectory gather to rank 0: peer copies through CUDA IPC (no SMs) or NCCL; auto tries p2p first")
+    ap.add_argument("--gather", default="nccl", choices=["auto", "p2p", "nccl"],
+                    help="trajectory gather to rank 0: NCCL (default, the north_star's single gather) or peer copies through a "
+                         "CUDA IPC mapping (no SMs; measured on 2 B200s: no gain on c1b, 6.4 vs 3.8 ms/step on c2 — torch's "
+                         "cross-process peer copy does not overlap like the NCCL kernel does); auto tries p2p first")
     ap.add_argument("--dist", default="ref", choices=["ref", "explicit", "explicit_psd"], help="synthetic distribution (SURVEY 8d)")
     ap.add_argument("--others", default="c2,c3,c5,c1b+explicit_psd,c2+explicit_psd,c1b+explicit", help="other BASELINE configs summarised in other_configs at N = 1 ('' = none)")
     ap.add_argument("--tune", action="append", default=[], help="diagnostic launcher knob key=value (garb200_set_tuning)")
