@@ -20,6 +20,7 @@ FORCE_GENERIC = 2
 PHASE_TIMERS = 4
 EXPLICIT_DYNAMICS = 8
 DENSE_KERNEL = 16
+NO_PADDING = 32
 
 _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int)
@@ -66,7 +67,7 @@ SYMBOLS = [
     "garb200_kkt_error", "garb200_upload_trajectory", "garb200_kernel_launches", "garb200_last_timings",
     "garb200_fp64_peak", "garb200_timing_log_start", "garb200_timing_log_read",
     "garb200_used_fast_path", "garb200_phase_cycles", "garb200_set_tuning",
-    "garb200_kkt_error_noalloc", "garb200_used_explicit_path",
+    "garb200_kkt_error_noalloc", "garb200_used_explicit_path", "garb200_padded_shape",
     "garb200_pack_from_device", "garb200_linear_step", "garb200_rollout_device", "garb200_device_theta",
     "garb200_upload_gv",
     "garb200_multi_create", "garb200_multi_destroy", "garb200_multi_num_shards", "garb200_multi_shard",
@@ -135,6 +136,7 @@ def lib():
         L.garb200_fp64_peak.argtypes = [C.c_int, C.c_int, C.c_void_p]
         L.garb200_used_fast_path.argtypes = [C.c_void_p]
         L.garb200_used_explicit_path.argtypes = [C.c_void_p]
+        L.garb200_padded_shape.argtypes = [C.c_void_p, C.c_void_p]
         L.garb200_phase_cycles.argtypes = [C.c_void_p, C.c_void_p]
         L.garb200_timing_log_start.argtypes = [C.c_void_p, C.c_int]
         L.garb200_timing_log_read.argtypes = [C.c_void_p] * 4
@@ -397,6 +399,12 @@ class Solver:
 
     def used_explicit_path(self) -> bool:
         return bool(lib().garb200_used_explicit_path(self._h))
+
+    def padded_shape(self):
+        """(nx, nu, nc, nth) of the instantiated sweep this problem shape is embedded in (exact zero /
+        identity padding, csrc/pad.cu), or None if the shape runs natively / on the generic kernel."""
+        out = (C.c_int * 4)()
+        return tuple(out) if lib().garb200_padded_shape(self._h, out) else None
 
     def phase_cycles(self):
         out = np.zeros(16, np.int64)

@@ -57,6 +57,12 @@ struct garb200_solver {
   double *h_gains = nullptr;     // pinned mirror of the gains records (getFeedback/getFeedforward cache)
   bool gains_fresh = false;
   bool problem_dirty = true;     // the resident problem changed since E == -I was last checked
+  // shape generality (pad.cu): this solver keeps the USER-shaped problem / gains / trajectories and owns an
+  // inner solver of the covering instantiated shape that does the work
+  garb200_solver *inner = nullptr;
+  bool inner_dirty = true;       // the user-shaped problem changed since it was last padded into the inner one
+  bool user_gains_fresh = false; // p.gains (user layout) mirrors the inner gains of the last factorization
+  int pad_shape[4] = {0, 0, 0, 0};
   int *d_expl = nullptr;         // device flag written by detect_explicit_kernel
   cudaStream_t side = nullptr;   // leg mode: the last leg runs beside the coupled legs
   cudaEvent_t side_e0 = nullptr, side_e1 = nullptr;
@@ -87,6 +93,16 @@ template <class T> static int dmalloc(garb200_solver *s, T **ptr, size_t count) 
   return GARB200_OK;
 }
 #define TRY(x) do { int rc_ = (x); if (rc_ != GARB200_OK) return rc_; } while (0)
+// padded shape: the user-layout gains records are produced from the inner solver's on first use after a
+// factorization (one kernel), then every reader below works on them unchanged
+static int sync_user_gains(garb200_solver *s) {
+  if (!s->inner || s->user_gains_fresh) return GARB200_OK;
+  const int rc = launch_unpad_gains(s->p, s->inner->p, s->stream);
+  if (rc < 0) return fail(GARB200_ERR_CUDA, "unpad_gains launch failed");
+  s->launches += rc;
+  s->user_gains_fresh = true;
+  return GARB200_OK;
+}
 
 extern "C" {
 
@@ -107,6 +123,7 @@ void garb200_layouts(int nx, int nu, int nc, int nth, int *knot, int *gain, int 
 
 void garb200_destroy(garb200_solver *s) {
   if (!s) return;
+  if (s->inner) { garb200_destroy(s->inner); s->inner = nullptr; }
   cudaSetDevice(s->cfg.device);
   if (s->stream) cudaStreamSynchronize(s->stream); else cudaDeviceSynchronize();
   for (void *q : s->dev_allocs) cudaFree(q);
@@ -180,10 +197,18 @@ int garb200_create(const garb200_config *cfg, garb200_solver **out) {
     delete s;
     return fail(GARB200_ERR_INVALID, buf);
   }
-  const bool want_fast = !p.dense && !(c.flags & GARB200_FORCE_GENERIC) && fast_path_available(c.nx, c.nu, c.nc, c.nth, c.num_legs);
+  // Shape generality (pad.cu): no instantiated sweep for these dims, or ragged per-knot dims -> the work is
+  // done by an inner solver of the covering instantiated shape; this one keeps the user-shaped buffers.
+  bool padded = false;
+  if (!p.dense && !legs && !(c.flags & (GARB200_FORCE_GENERIC | GARB200_NO_PADDING)) && T >= 1 &&
+      s->nu_t[T] == 0 && s->nc_t[T] == 0 &&
+      !(p.uniform_knots && fast_path_available(c.nx, c.nu, c.nc, c.nth, 0)))
+    padded = padded_shape_for(c.nx, c.nu, c.nc, c.nth, s->pad_shape) &&
+             fast_path_available(s->pad_shape[0], s->pad_shape[1], s->pad_shape[2], s->pad_shape[3], 0);
+  const bool want_fast = !padded && !p.dense && !(c.flags & GARB200_FORCE_GENERIC) && fast_path_available(c.nx, c.nu, c.nc, c.nth, c.num_legs);
   // (a shape with a specialised sweep may exceed the generic kernel's shared-memory plan: it then has
   //  no generic fallback and ragged knots are refused at backward())
-  if (!want_fast && !p.dense && backward_smem_bytes(p) > 227u * 1024u) {
+  if (!want_fast && !padded && !p.dense && backward_smem_bytes(p) > 227u * 1024u) {
     char buf[256];
     snprintf(buf, sizeof buf, "dimensions need %zu bytes of shared memory per CTA (> 227 KB): "
              "nx=%d nu=%d nc=%d nth=%d not supported by this kernel generation",
@@ -278,13 +303,30 @@ int garb200_create(const garb200_config *cfg, garb200_solver **out) {
       return bail(fail(GARB200_ERR_CUDA, "side stream creation failed"));
     p.side_stream = s->side; p.side_e0 = s->side_e0; p.side_e1 = s->side_e1;
   }
+  if (padded) {
+    garb200_config ic = c;
+    ic.nx = s->pad_shape[0]; ic.nu = s->pad_shape[1]; ic.nc = s->pad_shape[2]; ic.nth = s->pad_shape[3];
+    ic.nc0 = c.nc0 + (ic.nx - c.nx);          // the padded states are pinned to zero by G0' = [G0 0; 0 I]
+    ic.nu_t = nullptr; ic.nc_t = nullptr; ic.nu_term = 0; ic.nc_term = 0;
+    ic.flags = c.flags | GARB200_NO_PADDING;
+    TRYB(garb200_create(&ic, &s->inner));
+    // numerical flags and refinement counters are per problem: read the inner solver's
+    p.flags = s->inner->p.flags; p.refine_steps = s->inner->p.refine_steps;
+  }
 #undef TRYB
   *out = s;
   return GARB200_OK;
 }
 
+int garb200_padded_shape(const garb200_solver *s, int shape4[4]) {
+  if (!s || !s->inner) return 0;
+  if (shape4) for (int i = 0; i < 4; i++) shape4[i] = s->pad_shape[i];
+  return 1;
+}
+
 int garb200_set_tuning(garb200_solver *s, const char *name, int value) {
   if (!s || !name) return fail(GARB200_ERR_INVALID, "null argument");
+  if (s->inner) TRY(garb200_set_tuning(s->inner, name, value));
   Tune &t = s->p.tune;
   const std::string k(name);
   if (k == "group") t.group = value;
@@ -294,7 +336,7 @@ int garb200_set_tuning(garb200_solver *s, const char *name, int value) {
   else if (k == "condensed") t.condensed = value;
   else if (k == "c3_eg") t.c3_eg = value;
   else if (k == "legs_generic") t.legs_generic = value;
-  else if (k == "explicit_dyn") { t.explicit_dyn = value; s->problem_dirty = true; }
+  else if (k == "explicit_dyn") { t.explicit_dyn = value; s->problem_dirty = s->inner_dirty = true; }
   else return fail(GARB200_ERR_INVALID, "unknown tuning knob: " + k);
   return GARB200_OK;
 }
@@ -302,6 +344,7 @@ int garb200_set_tuning(garb200_solver *s, const char *name, int value) {
 int garb200_set_stream(garb200_solver *s, void *cuda_stream) {
   if (!s) return fail(GARB200_ERR_INVALID, "null solver");
   s->stream = static_cast<cudaStream_t>(cuda_stream);
+  if (s->inner) s->inner->stream = s->stream;
   return GARB200_OK;
 }
 
@@ -370,7 +413,7 @@ int garb200_upload_packed(garb200_solver *s, const double *knots, const double *
   if (G0) CK(cudaMemcpyAsync(p.G0, G0, B * p.nc0 * n * sizeof(double), cudaMemcpyHostToDevice, s->stream));
   if (g0) CK(cudaMemcpyAsync(p.g0, g0, B * p.nc0 * sizeof(double), cudaMemcpyHostToDevice, s->stream));
   s->has_problem = true;
-  s->problem_dirty = true;
+  s->problem_dirty = s->inner_dirty = true;
   return GARB200_OK;
 }
 
@@ -446,7 +489,7 @@ int garb200_commit(garb200_solver *s) {
     CK(cudaEventRecord(s->ev_h2d, s->stream));
     s->h2d_pending = true;
     s->any_dirty = false;
-    s->problem_dirty = true;
+    s->problem_dirty = s->inner_dirty = true;
   }
   s->has_problem = true;
   return GARB200_OK;
@@ -471,7 +514,7 @@ int garb200_device_problem(garb200_solver *s, double **d_knots, double **d_G0, d
   if (d_G0) *d_G0 = s->p.G0;
   if (d_g0) *d_g0 = s->p.g0;
   s->has_problem = true;  // the caller fills it on device
-  s->problem_dirty = true;
+  s->problem_dirty = s->inner_dirty = true;
   return GARB200_OK;
 }
 
@@ -483,7 +526,7 @@ int garb200_pack_from_device(garb200_solver *s, const garb200_device_problem_vie
   if (rc < 0) return fail(GARB200_ERR_CUDA, "pack_from_device launch failed");
   s->launches += rc;
   s->has_problem = true;
-  s->problem_dirty = true;
+  s->problem_dirty = s->inner_dirty = true;
   return GARB200_OK;
 }
 
@@ -508,6 +551,7 @@ int garb200_rollout_device(garb200_solver *s, double alpha, const double *d_dxs,
   if (!s->did_backward) return fail(GARB200_ERR_STATE, "no factorization yet");
   if (s->p.num_legs >= 2) return fail(GARB200_ERR_STATE, "the nonlinear rollout is not supported with the parallel-in-time solver (solver-proxddp.hxx:170-173)");
   CK(cudaSetDevice(s->cfg.device));
+  TRY(sync_user_gains(s));
   const int rc = launch_rollout(s->p, alpha, d_dxs, d_dus, d_dvs, d_dlbdas, s->stream);
   if (rc < 0) return fail(rc == -1 ? GARB200_ERR_INVALID : GARB200_ERR_CUDA, "rollout launch failed");
   s->launches += rc;
@@ -521,7 +565,7 @@ int garb200_generate(garb200_solver *s, uint64_t seed, int dist) {
   if (rc < 0) return fail(rc == -1 ? GARB200_ERR_INVALID : GARB200_ERR_CUDA, "generate kernel launch failed");
   s->launches += rc;
   s->has_problem = true;
-  s->problem_dirty = true;
+  s->problem_dirty = s->inner_dirty = true;
   return GARB200_OK;
 }
 
@@ -547,6 +591,33 @@ int garb200_backward(garb200_solver *s, double mudyn, double mueq) {
   CK(cudaSetDevice(s->cfg.device));
   DevParams &p = s->p;
   p.mudyn = mudyn; p.mueq = mueq;
+  if (s->inner) {   // padded shape: re-embed the problem if it changed, then the inner solver's sweep
+    garb200_solver *in = s->inner;
+    if (mueq == 0.0)   // an empty padded constraint row has the pivot -mueq
+      for (int t = 0; t < p.T; t++)
+        if (s->nc_t[t] < in->p.nc)
+          return fail(GARB200_ERR_INVALID, "mueq == 0 with constraint rows padded to the instantiated shape: use mueq > 0 or GARB200_NO_PADDING");
+    CK(cudaEventRecord(s->ev[0], s->stream));
+    const bool logp = s->tlog_bwd < s->tlog_cap;
+    if (logp) CK(cudaEventRecord(s->tlog[4 * s->tlog_bwd + 0], s->stream));
+    if (s->inner_dirty) {
+      in->p.shift = p.shift;
+      const int rcp = launch_pad_problem(p, in->p, s->stream);
+      if (rcp < 0) return fail(GARB200_ERR_CUDA, "pad_problem launch failed");
+      s->launches += rcp;
+      in->has_problem = true; in->problem_dirty = true;
+      s->inner_dirty = false;
+    }
+    const int64_t l0 = in->launches;
+    TRY(garb200_backward(in, mudyn, mueq));
+    s->launches += in->launches - l0;
+    s->used_fast = in->used_fast;
+    p.explicit_dyn = in->p.explicit_dyn;
+    CK(cudaEventRecord(s->ev[1], s->stream));
+    if (logp) { CK(cudaEventRecord(s->tlog[4 * s->tlog_bwd + 1], s->stream)); s->tlog_bwd++; }
+    s->did_backward = true; s->did_forward = false; s->gains_fresh = false; s->user_gains_fresh = false;
+    return GARB200_OK;
+  }
   CK(cudaMemsetAsync(p.flags, 0, (size_t)p.batch * sizeof(int32_t), s->stream));
   // Explicit dynamics (E_t == -I for every knot, explicit-dynamics.hxx:32): checked on the device whenever
   // the resident problem changed (one pass over the E blocks + a 4-byte read back), or promised by the
@@ -600,6 +671,27 @@ int garb200_forward_device(garb200_solver *s, const double *d_theta, double *d_x
   CK(cudaEventRecord(s->ev[2], s->stream));
   const bool logf = s->tlog_fwd < s->tlog_cap;
   if (logf) CK(cudaEventRecord(s->tlog[4 * s->tlog_fwd + 2], s->stream));
+  if (s->inner) {   // padded shape: theta -> internal width, inner rollout, trajectories back to the user's widths
+    garb200_solver *in = s->inner;
+    const double *th_in = nullptr;
+    if (d_theta && p.nth > 0) {
+      const int rt = launch_pad_theta(d_theta, in->p.theta, p.batch, p.nth, in->p.nth, s->stream);
+      if (rt < 0) return fail(GARB200_ERR_CUDA, "pad_theta launch failed");
+      s->launches += rt;
+      th_in = in->p.theta;
+    }
+    const int64_t l0 = in->launches;
+    TRY(garb200_forward_device(in, th_in, nullptr, nullptr, nullptr, nullptr));
+    s->launches += in->launches - l0;
+    const int ru = launch_unpad_traj(p, in->p, d_xs ? d_xs : p.xs, d_us ? d_us : p.us, d_vs ? d_vs : p.vs,
+                                     d_lbdas ? d_lbdas : p.lbdas, s->stream);
+    if (ru < 0) return fail(GARB200_ERR_CUDA, "unpad_traj launch failed");
+    s->launches += ru;
+    CK(cudaEventRecord(s->ev[3], s->stream));
+    if (logf) { CK(cudaEventRecord(s->tlog[4 * s->tlog_fwd + 3], s->stream)); s->tlog_fwd++; }
+    s->did_forward = (!d_xs && !d_us && !d_vs && !d_lbdas);
+    return GARB200_OK;
+  }
   const int rc = launch_forward(p, (p.nth > 0 && p.num_legs < 2) ? d_theta : nullptr,
                                 d_xs ? d_xs : p.xs, d_us ? d_us : p.us, d_vs ? d_vs : p.vs,
                                 d_lbdas ? d_lbdas : p.lbdas, s->stream);
@@ -662,6 +754,7 @@ int garb200_get_gains(garb200_solver *s, int problem, int t, double *ff, double 
   if (!s->did_backward) return fail(GARB200_ERR_STATE, "no factorization yet");
   if (problem < 0 || problem >= p.batch || t < 0 || t > p.T) return fail(GARB200_ERR_INVALID, "index out of range");
   CK(cudaSetDevice(s->cfg.device));
+  TRY(sync_user_gains(s));
   // updateGains() reads every knot of a problem right after backward (solver-proxddp.hxx:316-334): the
   // first read after a factorization mirrors ALL gains records in one bulk D2H, the others are memcpys
   const size_t slot = (size_t)problem * (p.T + 1) + phys_t(p, t);
@@ -690,6 +783,7 @@ int garb200_download_gains(garb200_solver *s, int first, int count, double *gain
   if (!s->did_backward) return fail(GARB200_ERR_STATE, "no factorization yet");
   if (first < 0 || count < 0 || first + count > p.batch) return fail(GARB200_ERR_INVALID, "range");
   CK(cudaSetDevice(s->cfg.device));
+  TRY(sync_user_gains(s));
   const size_t ps = (size_t)(p.T + 1) * p.GL.stride;
   if (p.shift == 0) return fetch(s, gains, p.gains + first * ps, count * ps);
   for (int b = first; b < first + count; b++)      // undo the ring offset: logical time order out
@@ -703,6 +797,7 @@ int garb200_download_gains(garb200_solver *s, int first, int count, double *gain
 
 int garb200_device_gains(garb200_solver *s, double **d_gains) {
   if (!s || !d_gains) return fail(GARB200_ERR_INVALID, "null argument");
+  if (s->inner && s->did_backward) { CK(cudaSetDevice(s->cfg.device)); TRY(sync_user_gains(s)); }
   *d_gains = s->p.gains;
   return GARB200_OK;
 }
@@ -715,6 +810,25 @@ int garb200_get_value(garb200_solver *s, int problem, int t, double *value_recor
   const int slot = value_slot(p, t);
   if (slot < 0) return fail(GARB200_ERR_STATE, "value function of this knot was not kept: create with GARB200_STORE_ALL_VALUES");
   CK(cudaSetDevice(s->cfg.device));
+  if (s->inner) {   // padded shape: the real part of the inner value function, in the user's record layout
+    const DevParams &q = s->inner->p;
+    std::vector<double> rec(q.VL.stride);
+    TRY(fetch(s, rec.data(), q.values + ((size_t)problem * q.nslots + slot) * q.VL.stride, q.VL.stride));
+    const int n = p.nx, N = q.nx, h = p.VL.nth, H = q.VL.nth;
+    const garb200_value_layout &U = p.VL, &I = q.VL;
+    for (int j = 0; j < n; j++)
+      for (int i = 0; i < n; i++) {
+        value_record[U.Pmat + i + j * n] = rec[I.Pmat + i + j * N];
+        value_record[U.Vxx + i + j * n] = rec[I.Vxx + i + j * N];
+      }
+    for (int i = 0; i < n; i++) { value_record[U.pvec + i] = rec[I.pvec + i]; value_record[U.vx + i] = rec[I.vx + i]; }
+    for (int a = 0; a < h; a++) {
+      for (int i = 0; i < n; i++) value_record[U.Vxt + i + a * n] = rec[I.Vxt + i + a * N];
+      for (int b2 = 0; b2 < h; b2++) value_record[U.Vtt + b2 + a * h] = rec[I.Vtt + b2 + a * H];
+      value_record[U.vt + a] = rec[I.vt + a];
+    }
+    return GARB200_OK;
+  }
   return fetch(s, value_record, p.values + ((size_t)problem * p.nslots + slot) * p.VL.stride, p.VL.stride);
 }
 
@@ -727,6 +841,27 @@ int garb200_get_initial(garb200_solver *s, int problem, double *kkt0_ff, double 
   if (problem < 0 || problem >= p.batch) return fail(GARB200_ERR_INVALID, "index out of range");
   CK(cudaSetDevice(s->cfg.device));
   const size_t s0 = p.nx + p.nc0, h = p.nth, b = problem;
+  if (s->inner) {   // padded shape: rows [x0(n) | pad | lambda0(c0) | pad] x (H columns) -> the user's
+    const DevParams &q = s->inner->p;
+    const size_t N = q.nx, S0 = q.nx + q.nc0, H = q.nth, n = p.nx, c0 = p.nc0;
+    std::vector<double> ff(S0), fth(S0 * H + 1), tg(H + 1), thh(H * H + 1);
+    TRY(fetch(s, ff.data(), q.kkt0_ff + b * S0, S0));
+    if (h) {
+      TRY(fetch(s, fth.data(), q.kkt0_fth + b * S0 * H, S0 * H));
+      TRY(fetch(s, tg.data(), q.thGrad + b * H, H));
+      TRY(fetch(s, thh.data(), q.thHess + b * H * H, H * H));
+    }
+    auto irow = [&](size_t r) { return r < n ? r : N + (r - n); };
+    for (size_t r = 0; r < n + c0; r++) {
+      if (kkt0_ff) kkt0_ff[r] = ff[irow(r)];
+      if (kkt0_fth) for (size_t a = 0; a < h; a++) kkt0_fth[r * h + a] = fth[irow(r) * H + a];
+    }
+    for (size_t a = 0; a < h; a++) {
+      if (thGrad) thGrad[a] = tg[a];
+      if (thHess) for (size_t c2 = 0; c2 < h; c2++) thHess[c2 + a * h] = thh[c2 + a * H];
+    }
+    return GARB200_OK;
+  }
   if (kkt0_ff) TRY(fetch(s, kkt0_ff, p.kkt0_ff + b * s0, s0));
   if (kkt0_fth && h) TRY(fetch(s, kkt0_fth, p.kkt0_fth + b * s0 * h, s0 * h));
   if (thGrad && h) TRY(fetch(s, thGrad, p.thGrad + b * h, h));
@@ -802,9 +937,21 @@ int garb200_cycle_append(garb200_solver *s, const garb200_knot_view *knots, int 
   CK(cudaMemsetAsync(p.kkt0_ff, 0, std::max<size_t>(B * (p.nx + p.nc0), 1) * sizeof(double), s->stream));
   CK(cudaMemsetAsync(p.thGrad, 0, std::max<size_t>(B * p.nth, 1) * sizeof(double), s->stream));
   CK(cudaMemsetAsync(p.thHess, 0, std::max<size_t>(B * p.nth * p.nth, 1) * sizeof(double), s->stream));
+  if (s->inner) {   // same ring offset and fresh StageFactor / kkt0 in the inner solver; user gains follow it
+    garb200_solver *in = s->inner;
+    DevParams &q = in->p;
+    q.shift = p.shift;
+    s->user_gains_fresh = false; // re-derived from the inner records (new offset, zeroed slot) on next use
+    const size_t pq = (size_t)(q.T + 1) * q.GL.stride * sizeof(double);
+    CK(cudaMemset2DAsync(q.gains + (size_t)slot * q.GL.stride, pq, 0, q.GL.stride * sizeof(double), q.batch, s->stream));
+    CK(cudaMemsetAsync(q.kkt0_ff, 0, std::max<size_t>(B * (q.nx + q.nc0), 1) * sizeof(double), s->stream));
+    CK(cudaMemsetAsync(q.thGrad, 0, std::max<size_t>(B * q.nth, 1) * sizeof(double), s->stream));
+    CK(cudaMemsetAsync(q.thHess, 0, std::max<size_t>(B * q.nth * q.nth, 1) * sizeof(double), s->stream));
+    in->did_forward = false; in->gains_fresh = false;
+  }
   s->did_forward = false;
   s->gains_fresh = false;
-  s->problem_dirty = true;
+  s->problem_dirty = s->inner_dirty = true;
   return GARB200_OK;
 }
 
@@ -859,6 +1006,7 @@ int garb200_used_explicit_path(const garb200_solver *s) { return s && s->used_fa
 
 int garb200_phase_cycles(garb200_solver *s, long long *out16) {
   if (!s || !out16) return fail(GARB200_ERR_INVALID, "null argument");
+  if (s->inner) return garb200_phase_cycles(s->inner, out16);
   if (!s->p.phase_cycles) return fail(GARB200_ERR_STATE, "create the solver with GARB200_PHASE_TIMERS in garb200_config.flags");
   CK(cudaSetDevice(s->cfg.device));
   CK(cudaStreamSynchronize(s->stream));

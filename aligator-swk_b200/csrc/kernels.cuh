@@ -95,6 +95,12 @@ int launch_detect_explicit(const DevParams &p, int *d_flag, cudaStream_t st);
 int fp64_peak(int kind, double *tflops);
 // dense.cu: RiccatiSolverDense (one BK of the (nu + nc + 2 nx)^2 stage KKT matrix per knot)
 int launch_backward_dense(const DevParams &p, cudaStream_t st);
+// pad.cu: exact embedding of a shape without an instantiated sweep into the next instantiated one
+bool padded_shape_for(int nx, int nu, int nc, int nth, int out[4]);
+int launch_pad_problem(const DevParams &u, const DevParams &p, cudaStream_t st);
+int launch_unpad_gains(const DevParams &u, const DevParams &p, cudaStream_t st);
+int launch_unpad_traj(const DevParams &u, const DevParams &p, double *xs, double *us, double *vs, double *lbdas, cudaStream_t st);
+int launch_pad_theta(const double *th, double *thp, int batch, int h, int H, cudaStream_t st);
 size_t dense_smem_bytes(const DevParams &p);
 // consumer.cu: device-side producer / consumers around the solve
 int launch_pack_from_device(const DevParams &p, const garb200_device_problem_view &v, double preg, cudaStream_t st);

@@ -61,6 +61,8 @@ extern "C" {
                                         factorization of the (nu + nc + 2 nx)^2 stage KKT matrix per knot
                                         (dense-kernel.hpp:56-212) instead of the proximal sweep; reads Gv
                                         (garb200_upload_gv); the slow, sturdy path; num_legs must be 0   */
+#define GARB200_NO_PADDING 32        /* do not embed a shape without an instantiated sweep into the next
+                                        instantiated one (testing; see garb200_padded_shape)            */
 #define GARB200_PHASE_TIMERS 4       /* diagnostic: per-phase clock64 timers in the specialised
                                         sweep (garb200_phase_cycles); slower instrumented kernel */
 
@@ -289,6 +291,11 @@ int64_t garb200_kernel_launches(const garb200_solver *s);
 int garb200_last_timings(garb200_solver *s, float *backward_ms, float *forward_ms);
 /* 1 if the last backward ran the dimension-specialised (DMMA) sweep, 0 for the generic kernel */
 int garb200_used_fast_path(const garb200_solver *s);
+/* Shape generality: a problem whose (nx, nu, nc, nth) — or whose ragged per-knot nu_t / nc_t — has no
+ * instantiated sweep is solved by the specialised sweep of the next instantiated shape through EXACT
+ * zero / identity padding (csrc/pad.cu); layouts seen by the caller stay the caller's.  Returns 1 and the
+ * internal shape {nx, nu, nc, nth} if this solver is padded, else 0. */
+int garb200_padded_shape(const garb200_solver *s, int shape4[4]);
 /* 1 if it ran with the explicit-dynamics path (every E_t == -I: no E^-1 pre-pass, E never read) */
 int garb200_used_explicit_path(const garb200_solver *s);
 /* Diagnostic: accumulated clock64() cycles of thread 0 of every CTA per phase of the specialised

