@@ -681,6 +681,19 @@ __device__ __forceinline__ void ldlt_solve_lanes(int tid, const double *S, const
 // and the final store un-permutes:  X(step(r), spiv[c]) = a_r[c].
 // Returns false on an exactly zero pivot.
 // ------------------------------------------------------------------------------------------
+// Reciprocal of a Gauss-Jordan pivot: the 20-bit hardware seed (MUFU.RCP64H) and two Newton steps,
+// ~1 ulp, no slow-path branch (a zero / non-finite pivot is caught by the caller's singularity flag).
+// The pivot reciprocal sits on the dependent chain of every elimination step: this is shorter than
+// __drcp_rn and keeps the unrolled pivot loops free of branches.
+__device__ __forceinline__ double rcp_pivot(double x) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  double e = fma(-x, r, 1.0);
+  r = fma(r, e, r);
+  e = fma(-x, r, 1.0);
+  return fma(r, e, r);
+}
+
 template <int N> struct GjShape {
 #ifndef GARB200_GJ_LPM_SMALL
 #define GARB200_GJ_LPM_SMALL 8
@@ -739,7 +752,7 @@ __device__ __forceinline__ bool gj_inverse_regs(int sub, unsigned mask, const do
     for (int s = 1; s < RPL; s++) if (rs == s) pcand = a[s][0];
     const double pval = __shfl_sync(mask, pcand, rl, LPM);
     if (pval == 0.0) ok = false;
-    const double pinv = __drcp_rn(pval);
+    const double pinv = rcp_pivot(pval);
     if (sub == rl) {
 #pragma unroll
       for (int s = 0; s < RPL; s++)
@@ -794,31 +807,46 @@ __device__ __forceinline__ bool gj_inverse_regs(int sub, unsigned mask, const do
 }
 
 // ------------------------------------------------------------------------------------------
-// Block Gauss-Jordan inverse on the FP64 tensor pipe: one warp per N x N matrix (N % 4 == 0),
-// the whole (padded) matrix lives in registers as m8n8k4 accumulator tiles for all N/4 block
-// steps.  Block step kb (columns c0 = 4 kb .. c0 + 3):
-//   1. the 4-column panel leaves the tiles through shared memory and is reduced row-per-lane by
-//      an ordinary in-place Gauss-Jordan with partial pivoting over ALL not-yet-pivoted rows;
-//      afterwards panel row i holds W_i = -A[i,panel] B^{-1} (other rows) or the rows of B^{-1}
-//      (the 4 pivot rows R), B = A[R, panel].
-//   2. the 4 raw pivot rows are copied out of the tiles, panel columns replaced by I_4.
-//   3. one rank-4 update  C += W * pivot_rows  = 1 DMMA per tile, with W = 0 for the pivot rows.
+// Block Gauss-Jordan inverse on the FP64 tensor pipe: one warp per N x N matrix (N % 4 == 0).
+// The (padded) matrix lives in REGISTERS as m8n8k4 accumulator tiles for all N/4 block steps (the
+// master copy: the rank-4 updates never reload it) and is MIRRORED row-major in shared memory after
+// every update (one double2 store per tile), so that everything indexed by a run-time row -- the
+// 4-column panel of the next step, the raw pivot rows of this one, the rows in pivot order at the
+// end -- is a plain shared-memory read instead of a compare/select walk over the register tiles
+// (that walk was ~30 % of the instructions of the register-only version, which was issue/latency bound).
+// Block step kb (columns c0 = 4 kb .. c0 + 3):
+//   1. the panel is read row-per-lane from the mirror and eliminated LU style with partial pivoting over
+//      ALL not-yet-pivoted rows: pivot ss clears column ss from the columns to its right only and leaves
+//      the multiplier in place, for every row alike (a pivot row just stops being a candidate).  With
+//      B = A[R, panel] = L_B U (R = the 4 pivot rows) the multipliers l_i of row i give
+//      A[i, panel] B^{-1} = l_i L_B^{-1}: W_i = -A[i, panel] B^{-1} is one 4 x 4 unit-triangular back
+//      substitution per row.
+//   2. W goes to shared memory (A operand), with W = 0 for the pivot rows; the B operand rows are the
+//      RAW pivot rows read straight from the mirror, panel columns replaced by I_4 in the fragment.
+//   3. one rank-4 update  C += W * pivot_rows  = 1 DMMA per tile (panel columns zeroed first, so they
+//      become W), tiles stored to the mirror, the pivot rows' own panel entries patched to e_s there
+//      and re-read into the tiles of that tile column.
 // The pivot rows themselves are NOT transformed at their block step: they stay raw (panel
 // columns e_s) and keep being updated like any other row, which commutes with the pending
-// left-multiplication by B^{-1}; all N/4 block transforms are applied at the end as one
-// block-diagonal DMMA product on the rows sorted by pivot step, which is also where the row
+// left-multiplication by B^{-1}; all N/4 block transforms are applied at the end (the raw 4 x 4 blocks B
+// are kept and inverted then, one lane per block, in the row order the pivoting chose) as one
+// block-diagonal DMMA product on the mirror rows taken in pivot order, which is also where the row
 // permutation is undone.  The column permutation is undone by the final store:
 //   X(step(r), piv[c]) = (B_kb^{-1} C[R_kb, :])(r, c).
+// Mirror layout: element (row, col) at Y[row * PLD + (col ^ swz(row))], PLD == 8 (mod 16) so that the
+// double2 tile stores of a quarter warp (rows g, g + 1) cover all 32 banks, swz(row) = 4 * bit1(row) so
+// that the row-per-lane panel reads of 8 consecutive rows spread over 4 bank groups instead of 2.
 // Shared memory per warp: GjDmma<N>::SMEM doubles + GjDmma<N>::SINTS ints.
 // ------------------------------------------------------------------------------------------
 template <int N> struct GjDmma {
   static_assert(N % 4 == 0 && N <= 64, "block Gauss-Jordan: N % 4 == 0, N <= 64");
   static constexpr int NTL = (N + 7) / 8, NP = NTL * 8, NB = N / 4;
-  static constexpr int PLD = (NP % 16 == 8) ? NP + 4 : NP + 12;   // == 12 (mod 16): conflict-free B fragments
+  static constexpr int PLD = (NP % 16 == 8) ? NP : NP + 8;
+  static constexpr int WLD = (NP % 16 == 8) ? NP + 4 : NP + 12;   // W panel, column-major: == 12 (mod 16), conflict-free A fragments
   static constexpr int RPL = (NP + 31) / 32;
-  static constexpr int PAN = 0, PROW = NP * 4, BINV = PROW + 4 * PLD, YS = BINV + 16 * (2 * NTL);
-  static constexpr int SMEM = YS + N * PLD;     // Y: the N rows sorted by pivot step
-  static constexpr int SINTS = 2 * NP;     // piv[c] | step[r]
+  static constexpr int PAN = 0, BINV = 4 * WLD, YS = BINV + 16 * (2 * NTL);
+  static constexpr int SMEM = YS + N * PLD;     // Y: row-major mirror of the matrix
+  static constexpr int SINTS = NP;              // piv[c]
 };
 
 template <int N>
@@ -826,10 +854,13 @@ __device__ __forceinline__ bool gj_inverse_dmma(int lane, const double *__restri
                                                 double *__restrict__ Xg, bool do_store,
                                                 double *sw, int *si) {
   using G = GjDmma<N>;
-  constexpr int NTL = G::NTL, NP = G::NP, NB = G::NB, PLD = G::PLD, RPL = G::RPL;
-  double *pan = sw + G::PAN, *prow = sw + G::PROW, *sbinv = sw + G::BINV, *Y = sw + G::YS;
-  int *spiv = si, *sstep = si + NP;
+  constexpr int NTL = G::NTL, NP = G::NP, NB = G::NB, PLD = G::PLD, WLD = G::WLD, RPL = G::RPL;
+  double *pan = sw + G::PAN, *sbinv = sw + G::BINV, *Y = sw + G::YS;
+  int *spiv = si;
   const int g = lane >> 2, q = lane & 3;
+  const int swg = ((g >> 1) & 1) << 2;          // swizzle of this lane's tile rows g + 8 mt
+  const int swl = ((lane >> 1) & 1) << 2;       // ... and of its panel rows lane + 32 s
+  double *ytile = Y + g * PLD + ((2 * q) ^ swg);   // tile (mt, nt): ytile[8 * mt * PLD + 8 * nt]
   double c[NTL][NTL][2];
 #pragma unroll
   for (int mt = 0; mt < NTL; mt++)
@@ -838,37 +869,33 @@ __device__ __forceinline__ bool gj_inverse_dmma(int lane, const double *__restri
       const int row = g + 8 * mt, col = 8 * nt + 2 * q;
       c[mt][nt][0] = (row < N && col < N) ? Eg[row + col * N] : 0.0;
       c[mt][nt][1] = (row < N && col + 1 < N) ? Eg[row + (col + 1) * N] : 0.0;
+      if (row < N) *reinterpret_cast<double2 *>(ytile + 8 * mt * PLD + 8 * nt) = make_double2(c[mt][nt][0], c[mt][nt][1]);
     }
-  // block-inverse slots past the last block (padding of the final product) are zero
+  // block slots past the last block (padding of the final product) are zero
   for (int e = lane; e < 16 * (2 * NTL - NB); e += 32) sbinv[16 * NB + e] = 0.0;
   bool act[RPL];
 #pragma unroll
   for (int s = 0; s < RPL; s++) act[s] = lane + 32 * s < N;
   bool ok = true;
+  __syncwarp();
 #pragma unroll
   for (int kb = 0; kb < NB; kb++) {
     const int ntp = kb >> 1, h = kb & 1, c0 = 4 * kb;
-    // 1. panel out of the tiles (and zero it there)
-    if ((q >> 1) == h) {
-#pragma unroll
-      for (int mt = 0; mt < NTL; mt++) {
-        *reinterpret_cast<double2 *>(pan + (g + 8 * mt) * 4 + 2 * (q & 1)) = make_double2(c[mt][ntp][0], c[mt][ntp][1]);
-        c[mt][ntp][0] = 0.0; c[mt][ntp][1] = 0.0;
-      }
-    }
-    __syncwarp();
+    // 1. the panel, row per lane, from the mirror
     double a[RPL][4];
 #pragma unroll
     for (int s = 0; s < RPL; s++) {
       const int row = lane + 32 * s;
-      if (row < NP) {
-        const double2 lo = *reinterpret_cast<const double2 *>(pan + row * 4), hi = *reinterpret_cast<const double2 *>(pan + row * 4 + 2);
+      if (row < N) {
+        const double *yp = Y + row * PLD + (c0 ^ swl);
+        const double2 lo = *reinterpret_cast<const double2 *>(yp), hi = *reinterpret_cast<const double2 *>(yp + 2);
         a[s][0] = lo.x; a[s][1] = lo.y; a[s][2] = hi.x; a[s][3] = hi.y;
       } else {
         a[s][0] = a[s][1] = a[s][2] = a[s][3] = 0.0;
       }
     }
     int rsel[4];
+    double lb10 = 0.0, lb20 = 0.0, lb21 = 0.0, lb30 = 0.0, lb31 = 0.0, lb32 = 0.0;
 #pragma unroll
     for (int ss = 0; ss < 4; ss++) {
       // pivot search on a 32-bit key: top 25 bits of |a| (exponent + 13 mantissa bits), row in
@@ -893,82 +920,112 @@ __device__ __forceinline__ bool gj_inverse_dmma(int lane, const double *__restri
         pr[j] = __shfl_sync(0xffffffffu, v, rl);
       }
       if (mx == 0u || pr[ss] == 0.0) ok = false;
-      const double pinv = __drcp_rn(pr[ss]);
-#pragma unroll
-      for (int j = 0; j < 4; j++) pr[j] *= pinv;        // scaled pivot row
+      const double pinv = rcp_pivot(pr[ss]);
+      // (the broadcast of pivot row ss carries its multipliers for the earlier pivots: row ss of L_B)
+      if (ss == 1) lb10 = pr[0];
+      if (ss == 2) { lb20 = pr[0]; lb21 = pr[1]; }
+      if (ss == 3) { lb30 = pr[0]; lb31 = pr[1]; lb32 = pr[2]; }
 #pragma unroll
       for (int s = 0; s < RPL; s++) {
-        const bool isp = (lane + 32 * s) == r;
-        const double m = a[s][ss];
+        const double m = a[s][ss] * pinv;
+        a[s][ss] = m;
 #pragma unroll
-        for (int j = 0; j < 4; j++)
-          if (j != ss) a[s][j] = isp ? pr[j] : fma(-m, pr[j], a[s][j]);
-        a[s][ss] = isp ? pinv : -m * pinv;
-        if (isp) act[s] = false;
+        for (int j = ss + 1; j < 4; j++) a[s][j] = fma(-m, pr[j], a[s][j]);
+        if ((lane + 32 * s) == r) act[s] = false;
       }
     }
-    // transformed panel back: W (A operand of the update); the pivot rows hold B^{-1}
+    // W_i = -l_i L_B^{-1}: back substitution with the unit lower 4 x 4 factor; 2. W (A operand) to shared memory
 #pragma unroll
     for (int s = 0; s < RPL; s++) {
+      const double w3 = -a[s][3];
+      const double w2 = -fma(w3, lb32, a[s][2]);
+      const double w1 = -fma(w3, lb31, fma(w2, lb21, a[s][1]));
+      const double w0 = -fma(w3, lb30, fma(w2, lb20, fma(w1, lb10, a[s][0])));
       const int row = lane + 32 * s;
-      if (row < NP) {
-        *reinterpret_cast<double2 *>(pan + row * 4) = make_double2(a[s][0], a[s][1]);
-        *reinterpret_cast<double2 *>(pan + row * 4 + 2) = make_double2(a[s][2], a[s][3]);
-      }
+      if (row < NP) { pan[row] = w0; pan[WLD + row] = w1; pan[2 * WLD + row] = w2; pan[3 * WLD + row] = w3; }
     }
-    if (lane < 4) {
-      const int r = lane == 0 ? rsel[0] : lane == 1 ? rsel[1] : lane == 2 ? rsel[2] : rsel[3];
-      spiv[c0 + lane] = r;
-      sstep[r] = c0 + lane;
-    }
-    // 2. raw pivot rows out of the tiles; the pivot rows' own panel entries become e_s
+    if (lane < 4) spiv[c0 + lane] = lane == 0 ? rsel[0] : lane == 1 ? rsel[1] : lane == 2 ? rsel[2] : rsel[3];
+    // (the pivot rows' own panel entries were patched to e_s in the mirror at the end of the previous
+    //  step: bring that tile column of the register copy up to date before it is updated again)
+    if (kb > 0) {
+      const int ntq = (kb - 1) >> 1, hq = (kb - 1) & 1;
+      if ((q >> 1) == hq) {
 #pragma unroll
-    for (int mt = 0; mt < NTL; mt++) {
-      const int row = g + 8 * mt;
-      const int sidx = row == rsel[0] ? 0 : row == rsel[1] ? 1 : row == rsel[2] ? 2 : row == rsel[3] ? 3 : -1;
-      if (sidx >= 0) {
-#pragma unroll
-        for (int nt = 0; nt < NTL; nt++)
-          *reinterpret_cast<double2 *>(prow + sidx * PLD + 8 * nt + 2 * q) = make_double2(c[mt][nt][0], c[mt][nt][1]);
-      }
-      if ((q >> 1) == h) {
-        if (sidx == 2 * (q & 1)) c[mt][ntp][0] = 1.0;
-        if (sidx == 2 * (q & 1) + 1) c[mt][ntp][1] = 1.0;
+        for (int mt = 0; mt < NTL; mt++) {
+          if (g + 8 * mt < N) {
+            const double2 v = *reinterpret_cast<const double2 *>(ytile + 8 * mt * PLD + 8 * ntq);
+            c[mt][ntq][0] = v.x; c[mt][ntq][1] = v.y;
+          }
+        }
       }
     }
     __syncwarp();
     if (lane < 16) {
       const int sr = lane >> 2, sc = lane & 3;
       const int r = sr == 0 ? rsel[0] : sr == 1 ? rsel[1] : sr == 2 ? rsel[2] : rsel[3];
-      prow[sr * PLD + c0 + sc] = (sr == sc) ? 1.0 : 0.0;
-      sbinv[16 * kb + lane] = pan[r * 4 + sc];       // B^{-1}(sr, sc)
-      pan[r * 4 + sc] = 0.0;                         // W = 0 for the pivot rows
+      sbinv[16 * kb + lane] = Y[r * PLD + ((c0 + sc) ^ (((r >> 1) & 1) << 2))];   // B(sr, sc) = A[R, panel], raw
+      pan[sc * WLD + r] = 0.0;                                                     // W = 0 for the pivot rows
     }
     __syncwarp();
-    // 3. rank-4 update, one DMMA per tile
+    // 3. rank-4 update, one DMMA per tile.  B rows: the raw pivot rows from the mirror (k = q)
     double af[NTL], bf[NTL];
+    const int rq = q == 0 ? rsel[0] : q == 1 ? rsel[1] : q == 2 ? rsel[2] : rsel[3];
+    const double *yq = Y + rq * PLD + (g ^ (((rq >> 1) & 1) << 2));
 #pragma unroll
-    for (int mt = 0; mt < NTL; mt++) af[mt] = pan[(g + 8 * mt) * 4 + q];
+    for (int mt = 0; mt < NTL; mt++) af[mt] = pan[q * WLD + g + 8 * mt];
 #pragma unroll
-    for (int nt = 0; nt < NTL; nt++) bf[nt] = prow[q * PLD + g + 8 * nt];
+    for (int nt = 0; nt < NTL; nt++) bf[nt] = yq[8 * nt];
+    if ((g >> 2) == h) bf[ntp] = (g & 3) == q ? 1.0 : 0.0;        // panel columns of the pivot rows: I_4
+    if ((q >> 1) == h) {
+#pragma unroll
+      for (int mt = 0; mt < NTL; mt++) { c[mt][ntp][0] = 0.0; c[mt][ntp][1] = 0.0; }
+    }
 #pragma unroll
     for (int mt = 0; mt < NTL; mt++)
 #pragma unroll
       for (int nt = 0; nt < NTL; nt++) dmma_884(c[mt][nt][0], c[mt][nt][1], af[mt], bf[nt]);
-    __syncwarp();
-  }
-  // rows sorted by pivot step -> Y, then X rows = blockdiag(B_kb^{-1}) Y
+    __syncwarp();     // every lane has read its B rows before the mirror is overwritten
 #pragma unroll
-  for (int mt = 0; mt < NTL; mt++) {
-    const int row = g + 8 * mt;
-    if (row < N) {
-      const int sg = sstep[row];
+    for (int mt = 0; mt < NTL; mt++)
 #pragma unroll
       for (int nt = 0; nt < NTL; nt++)
-        *reinterpret_cast<double2 *>(Y + sg * PLD + 8 * nt + 2 * q) = make_double2(c[mt][nt][0], c[mt][nt][1]);
+        if (g + 8 * mt < N) *reinterpret_cast<double2 *>(ytile + 8 * mt * PLD + 8 * nt) = make_double2(c[mt][nt][0], c[mt][nt][1]);
+    __syncwarp();
+    if (lane < 16) {
+      const int sr = lane >> 2, sc = lane & 3;
+      const int r = sr == 0 ? rsel[0] : sr == 1 ? rsel[1] : sr == 2 ? rsel[2] : rsel[3];
+      Y[r * PLD + ((c0 + sc) ^ (((r >> 1) & 1) << 2))] = (sr == sc) ? 1.0 : 0.0;
     }
+    __syncwarp();
+  }
+  // B_kb^{-1} for all block steps at once, one lane per 4 x 4 block: Gauss-Jordan without pivoting in the
+  // row order the partial pivoting above chose (= the LU order of B, so it is as stable as that was)
+  if (lane < NB) {
+    double bm[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+      for (int j2 = 0; j2 < 4; j2++) bm[i][j2] = sbinv[16 * lane + 4 * i + j2];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const double pinv = rcp_pivot(bm[k][k]);
+#pragma unroll
+      for (int j2 = 0; j2 < 4; j2++) bm[k][j2] = (j2 == k) ? pinv : bm[k][j2] * pinv;
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        if (i == k) continue;
+        const double m = bm[i][k];
+#pragma unroll
+        for (int j2 = 0; j2 < 4; j2++) bm[i][j2] = (j2 == k) ? -m * pinv : fma(-m, bm[k][j2], bm[i][j2]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+      for (int j2 = 0; j2 < 4; j2++) sbinv[16 * lane + 4 * i + j2] = bm[i][j2];
   }
   __syncwarp();
+  // X rows = blockdiag(B_kb^{-1}) (mirror rows in pivot order)
   int pc[NTL][2];
 #pragma unroll
   for (int nt = 0; nt < NTL; nt++) {
@@ -982,15 +1039,14 @@ __device__ __forceinline__ bool gj_inverse_dmma(int lane, const double *__restri
 #pragma unroll
     for (int nt = 0; nt < NTL; nt++) x[nt][0] = x[nt][1] = 0.0;
 #pragma unroll
-    for (int j = 0; j < 2; j++) {
-      if (2 * mt + j < NB) {
+    for (int j2 = 0; j2 < 2; j2++) {
+      if (2 * mt + j2 < NB) {
         // A(row g, k q) = B_{2mt+j}^{-1}(g - 4j, q) on rows 4j..4j+3, zero elsewhere
-        const double av = ((g >> 2) == j) ? sbinv[16 * (2 * mt + j) + 4 * (g & 3) + q] : 0.0;
+        const double av = ((g >> 2) == j2) ? sbinv[16 * (2 * mt + j2) + 4 * (g & 3) + q] : 0.0;
+        const int rr = spiv[8 * mt + 4 * j2 + q];                      // the row pivoted at step 8 mt + 4 j + q
+        const double *yr = Y + rr * PLD + (g ^ (((rr >> 1) & 1) << 2));
 #pragma unroll
-        for (int nt = 0; nt < NTL; nt++) {
-          const double bv = Y[(8 * mt + 4 * j + q) * PLD + g + 8 * nt];
-          dmma_884(x[nt][0], x[nt][1], av, bv);
-        }
+        for (int nt = 0; nt < NTL; nt++) dmma_884(x[nt][0], x[nt][1], av, yr[8 * nt]);
       }
     }
     const int row = g + 8 * mt;
@@ -1088,7 +1144,7 @@ __device__ __forceinline__ bool gj_inverse_cta(int tid, const double *__restrict
           pr[j] = __shfl_sync(0xffffffffu, v, rl);
         }
         if (mx == 0u || pr[ss] == 0.0) bad = 1;
-        const double pinv = __drcp_rn(pr[ss]);
+        const double pinv = rcp_pivot(pr[ss]);
 #pragma unroll
         for (int j = 0; j < 4; j++) pr[j] *= pinv;
 #pragma unroll

@@ -49,6 +49,8 @@ WORKLOADS = {
                desc="configs[3]: parallel-in-time T=4096, 64 legs, single problem"),
     "c5": dict(nx=76, nu=32, nc=0, nth=0, T=100, batch=1024, legs=0,
                desc="configs[4]: Talos-shaped nx=76 nu=32 T=100 batch 1024"),
+    "p30": dict(nx=30, nu=10, nc=0, nth=0, T=100, batch=4096, legs=0,
+                desc="off-grid shape nx=30 nu=10 T=100 batch 4096: no instantiated sweep, embedded in (36, 12) by exact padding"),
 }
 
 
@@ -736,7 +738,7 @@ def main():
                          "CUDA IPC mapping (no SMs; measured on 2 B200s: no gain on c1b, 6.4 vs 3.8 ms/step on c2 — torch's "
                          "cross-process peer copy does not overlap like the NCCL kernel does); auto tries p2p first")
     ap.add_argument("--dist", default="ref", choices=["ref", "explicit", "explicit_psd"], help="synthetic distribution (SURVEY 8d)")
-    ap.add_argument("--others", default="c2,c3,c5,c1b+explicit_psd,c2+explicit_psd,c1b+explicit", help="other BASELINE configs summarised in other_configs at N = 1 ('' = none)")
+    ap.add_argument("--others", default="c2,c3,c5,c1b+explicit_psd,c2+explicit_psd,c1b+explicit,p30", help="other BASELINE configs summarised in other_configs at N = 1 ('' = none)")
     ap.add_argument("--tune", action="append", default=[], help="diagnostic launcher knob key=value (garb200_set_tuning)")
     ap.add_argument("--horizons", action="store_true", help="the reference's own latency sweep over horizons (one GPU)")
     args = ap.parse_args()
