@@ -985,11 +985,13 @@ __device__ __forceinline__ bool gj_inverse_dmma(int lane, const double *__restri
 #pragma unroll
       for (int nt = 0; nt < NTL; nt++) dmma_884(c[mt][nt][0], c[mt][nt][1], af[mt], bf[nt]);
     __syncwarp();     // every lane has read its B rows before the mirror is overwritten
+    // (columns >= N of the last tile column are padding: zero in the mirror since the initial store, never
+    //  rewritten -- the shared-memory pipe is what bounds this kernel)
 #pragma unroll
     for (int mt = 0; mt < NTL; mt++)
 #pragma unroll
       for (int nt = 0; nt < NTL; nt++)
-        if (g + 8 * mt < N) *reinterpret_cast<double2 *>(ytile + 8 * mt * PLD + 8 * nt) = make_double2(c[mt][nt][0], c[mt][nt][1]);
+        if (g + 8 * mt < N && 8 * nt + 2 * q < N) *reinterpret_cast<double2 *>(ytile + 8 * mt * PLD + 8 * nt) = make_double2(c[mt][nt][0], c[mt][nt][1]);
     __syncwarp();
     if (lane < 16) {
       const int sr = lane >> 2, sc = lane & 3;

@@ -41,7 +41,7 @@ __global__ void __launch_bounds__(32 * WPB, MINB) einv_kernel(const DevParams p)
 
 // Same pre-pass on the tensor pipe (block Gauss-Jordan, fast.cuh): one warp per matrix.
 template <int N, int WPB>
-__global__ void __launch_bounds__(32 * WPB, 3) einv_dmma_kernel(const DevParams p) {
+__global__ void __launch_bounds__(32 * WPB, 12 / WPB) einv_dmma_kernel(const DevParams p) {
   using G = GjDmma<N>;
   extern __shared__ __align__(16) double s_dyn[];
   double *s_w = s_dyn + (threadIdx.x >> 5) * G::SMEM;
