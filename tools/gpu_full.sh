@@ -7,10 +7,10 @@ timeout 900 python -m pytest tests -m gpu -q > gpurun_out/pytest_gpu.log 2>&1; e
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -4 gpurun_out/smoke.log
 timeout 600 python bench.py > gpurun_out/bench_default.json 2> gpurun_out/bench_default.err; echo "default rc=$?"; tail -3 gpurun_out/bench_default.err; cat gpurun_out/bench_default.json
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err; echo "reference rc=$?"; cat gpurun_out/bench_reference.json
-timeout 600 python bench.py --workload c1b > gpurun_out/bench_c1b.json 2> gpurun_out/bench_c1b.err; echo "c1b rc=$?"; tail -3 gpurun_out/bench_c1b.err; cat gpurun_out/bench_c1b.json
-for wl in c1 c3 c4 c5; do
-  timeout 300 python bench.py --workload $wl --steps 5 --warmup 3 --no-e2e --cpu-budget 3 > gpurun_out/bench_$wl.json 2> gpurun_out/bench_$wl.err; echo "$wl rc=$?"
+for wl in c2 c1 c3 c4 c5; do
+  timeout 300 python bench.py --workload $wl --steps 10 --warmup 3 --no-e2e --cpu-budget 3 --others '' > gpurun_out/bench_$wl.json 2> gpurun_out/bench_$wl.err; echo "$wl rc=$?"
 done
+timeout 600 python bench.py --horizons > gpurun_out/bench_horizons.json 2> gpurun_out/bench_horizons.err; echo "horizons rc=$?"
 fi
 if [ "$1" == "ncu" ] || [ "$1" == "ncuonly" ]; then
   # name:bench-arguments  (short runs: no e2e, no parity sample, no other_configs -> only the timed kernels launch)

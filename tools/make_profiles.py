@@ -74,13 +74,13 @@ def launch_list(wl):
 
 
 summary = {"round": RR, "bench": {}, "ncu": {}}
-for name in ("default", "reference", "c1b", "c1", "c3", "c4", "c5"):
+for name in ("default", "reference", "c2", "c1", "c3", "c4", "c5", "horizons"):
     p = os.path.join(GO, f"bench_{name}.json")
     if os.path.exists(p) and os.path.getsize(p):
         line = open(p).read().strip().splitlines()[-1]
         open(os.path.join(PR, f"{RR}_bench_{name}.json"), "w").write(line + "\n")
         summary["bench"][name] = json.loads(line)
-for wl in ("c2", "c1b", "c3", "c5"):
+for wl in ("c1b", "c2", "c3", "c5", "c1bx", "c2x"):
     summary["ncu"][wl] = {"full": ncu_full(wl), "launches": launch_list(wl)}
 for f in ("pytest_gpu.log", "smoke.log"):
     if os.path.exists(os.path.join(GO, f)):
@@ -88,7 +88,10 @@ for f in ("pytest_gpu.log", "smoke.log"):
 json.dump(summary["ncu"], open(os.path.join(PR, f"{RR}_ncu_digest.json"), "w"), indent=1)
 for wl, d in summary["ncu"].items():
     print(wl, json.dumps(d, indent=1))
+subprocess.run([sys.executable, os.path.join(ROOT, "tools", "sass_summary.py"), RR], stdout=subprocess.DEVNULL)
 for k, b in summary["bench"].items():
+    if "value" not in b:
+        continue
     r = b.get("roofline") or {}
     print(k, "%.0f %s" % (b["value"], b["unit"]), "ms/step %.3f" % b["ms_per_step"], r.get("bound"), r.get("frac"),
           "e2e", (b.get("e2e") or {}).get("value"))
