@@ -1,11 +1,12 @@
 #!/bin/bash
 # Multi-GPU A/B (run under gpurun --gpus N): gather modes, strong scaling, multi-device handle test.
-# usage: gpu_multi.sh N
-N=${1:-2}
+# usage: gpu_multi.sh N ["bench args" ...]   (default: the full list of modes)
+N=${1:-2}; shift
 mkdir -p gpurun_out
 Q="--steps 10 --warmup 3 --no-e2e --parity-k 0 --cpu-budget 1"
 i=0
-for spec in "" "--gather p2p" "--scaling strong" "--workload c2" "--workload c2 --gather p2p" "--workload c2 --scaling strong" "--workload c5 --scaling strong"; do
+if [ $# -eq 0 ]; then set -- "" "--gather p2p" "--scaling strong" "--workload c2" "--workload c2 --gather p2p" "--workload c2 --scaling strong" "--workload c5 --scaling strong"; fi
+for spec in "$@"; do
   i=$((i+1))
   timeout 300 python bench.py --gpus $N $Q --others "" $spec > gpurun_out/multi_${N}_$i.json 2> gpurun_out/multi_${N}_$i.err; echo "[$i] N=$N $spec rc=$?"
   python - "$N" "$i" <<'PY'
