@@ -15,11 +15,12 @@ fi
 if [ "$1" == "ncu" ] || [ "$1" == "ncuonly" ]; then
   # name:bench-arguments  (short runs: no e2e, no parity sample, no other_configs -> only the timed kernels launch)
   for spec in "c1b:--workload c1b" "c2:--workload c2" "c3:--workload c3" "c5:--workload c5" "c1bx:--workload c1b --dist explicit_psd" "c2x:--workload c2 --dist explicit_psd"; do
-    wl=${spec%%:*}; args="${spec#*:} --no-e2e --cpu-budget 1 --parity-k 0 --others ''"
+    wl=${spec%%:*}; skip=3; case $wl in *x) skip=2;; esac   # kernels per step: pre-pass + sweep + forward (no pre-pass for E = -I)
+    args="${spec#*:} --no-e2e --cpu-budget 1 --parity-k 0 --others ''"
     eval timeout 300 python bench.py $args --steps 2 --warmup 3 > gpurun_out/plain_$wl.log 2>&1 && \
     eval timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches_$wl.csv \
       python bench.py $args --steps 2 --warmup 3 > gpurun_out/ncu_launch_$wl.log 2>&1; echo "launch list $wl rc=$?"
-    eval timeout 900 ncu --set full --clock-control none --import-source on -k regex:"sweep_\|einv_\|forward_" -s 3 -c 3 -f -o gpurun_out/full_$wl \
+    eval timeout 900 ncu --set full --clock-control none --import-source on -k regex:"sweep_\|einv_\|forward_" -s $skip -c $skip -f -o gpurun_out/full_$wl \
       python bench.py $args --steps 1 --warmup 1 > gpurun_out/ncu_full_$wl.log 2>&1; echo "set full $wl rc=$?"
     # the .ncu-rep files (with source) exceed what gpurun copies back: keep the raw-page CSV (+ the source page of c1b)
     ncu -i gpurun_out/full_$wl.ncu-rep --page raw --csv > gpurun_out/full_$wl.raw.csv 2>/dev/null
