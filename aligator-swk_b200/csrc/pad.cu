@@ -134,7 +134,7 @@ int launch_pad_theta(const double *th, double *thp, int batch, int h, int H, cud
 
 /// Smallest instantiated shape that covers (nx, nu, nc, nth); false if none.
 bool padded_shape_for(int nx, int nu, int nc, int nth, int out[4]) {
-  static const int shapes[][4] = {{12, 4, 0, 0}, {36, 12, 0, 0}, {36, 12, 6, 4}, {76, 32, 0, 0}};
+  static const int shapes[][4] = {{12, 4, 0, 0}, {36, 12, 0, 0}, {76, 32, 0, 0}, {36, 12, 6, 4}, {36, 12, 12, 8}};
   for (const auto &s : shapes)
     if (nx <= s[0] && nu <= s[1] && nc <= s[2] && nth <= s[3]) { for (int i = 0; i < 4; i++) out[i] = s[i]; return true; }
   return false;

@@ -1032,6 +1032,7 @@ int launch_backward_fast(const DevParams &p, const int *h_nu_t, const int *h_nc_
     if (p.nx == 12 && p.nu == 4 && p.nc == 0 && p.nth == 0) return launch_fast_t<12, 4, 0, 0, 1, false, 1, true>(p, st);
     if (p.nx == 36 && p.nu == 12 && p.nc == 0 && p.nth == 0) return launch_fast_t<36, 12, 0, 0, 5, false, 1, true>(p, st);
     if (p.nx == 36 && p.nu == 12 && p.nc == 6 && p.nth == 4) return launch_fast_t<36, 12, 6, 4, 5, true, 1, true>(p, st);
+    if (p.nx == 36 && p.nu == 12 && p.nc == 12 && p.nth == 8) return launch_fast_t<36, 12, 12, 8, 5, true, 1, true>(p, st);
   }
   if (p.nx == 12 && p.nu == 4 && p.nc == 0 && p.nth == 0) return launch_fast_t<12, 4, 0, 0, 1>(p, st);
   if (p.nx == 36 && p.nu == 12 && p.nc == 0 && p.nth == 0) {
@@ -1042,6 +1043,8 @@ int launch_backward_fast(const DevParams &p, const int *h_nu_t, const int *h_nc_
   if (p.nx == 36 && p.nu == 12 && p.nc == 6 && p.nth == 4) {   // C3: E^{-1} from L2 -> 75 KB of shared memory, 3 CTAs per SM
     return p.tune.c3_eg ? launch_fast_t<36, 12, 6, 4, 5, true>(p, st) : launch_fast_t<36, 12, 6, 4, 5, false>(p, st);
   }
+  // the widest constrained / parametric instantiation: the covering shape of everything with nc <= 12, nth <= 8 (pad.cu)
+  if (p.nx == 36 && p.nu == 12 && p.nc == 12 && p.nth == 8) return launch_fast_t<36, 12, 12, 8, 5, true>(p, st);
   if (big_path_available(p.nx, p.nu, p.nc, p.nth)) return launch_backward_big(p, st);                     // C5
   return -3;
 }
@@ -1049,7 +1052,8 @@ int launch_backward_fast(const DevParams &p, const int *h_nu_t, const int *h_nc_
 bool fast_path_available(int nx, int nu, int nc, int nth, int num_legs) {
   if (num_legs >= 2) return nx == 36 && nu == 12 && nc == 0 && nth == 0;
   return (nx == 12 && nu == 4 && nc == 0 && nth == 0) || (nx == 36 && nu == 12 && nc == 0 && nth == 0) ||
-         (nx == 36 && nu == 12 && nc == 6 && nth == 4) || big_path_available(nx, nu, nc, nth);
+         (nx == 36 && nu == 12 && nc == 6 && nth == 4) || (nx == 36 && nu == 12 && nc == 12 && nth == 8) ||
+         big_path_available(nx, nu, nc, nth);
 }
 
 } // namespace garb200
