@@ -183,11 +183,15 @@ sweep_kernel(const DevParams p) {
     }
   };
 
-  if (tid == 0) { mbar_init(bar, 1); fence_mbar_init(); }
+  // two transaction barriers per knot: `bar` for what the first products need (E^{-1}; everything for the
+  // terminal knot and for E = -I), `bar2` for the rest of the record ([Q..B], [f..]), first read in step (3):
+  // its 30 KB arrive from L2 while the two E^{-1} products run
+  uint64_t *bar2 = bar + 1;
+  if (tid == 0) { mbar_init(bar, 1); mbar_init(bar2, 1); fence_mbar_init(); }
   for (int e = tid; e < PL::gpart; e += NT) Gs[e] = 0.0;
   for (int e = tid; e < PL::gthsz; e += NT) fth[e] = 0.0;
   cta_sync<NT, GRP>();
-  uint32_t phase = 0;
+  uint32_t phase = 0, phase2 = 0;
   const size_t pbase = (size_t)b * (T + 1);
   auto issue_load = [&](int t) {      // thread 0 only
     const int pt = phys_t(p, t);
@@ -200,19 +204,20 @@ sweep_kernel(const DevParams p) {
       return;
     }
     if constexpr (EG) {                 // [Q..B] and [f..], the E block is never staged
-      mbar_expect_tx(bar, (uint32_t)(PL::kstride - PL::esh) * 8u);
-      tma_load_1d(rec, src, (uint32_t)PL::oE * 8u, bar);
-      tma_load_1d(rec + PL::oE, src + PL::of, (uint32_t)(PL::kstride - PL::of) * 8u, bar);
+      mbar_expect_tx(bar2, (uint32_t)(PL::kstride - PL::esh) * 8u);
+      tma_load_1d(rec, src, (uint32_t)PL::oE * 8u, bar2);
+      tma_load_1d(rec + PL::oE, src + PL::of, (uint32_t)(PL::kstride - PL::of) * 8u, bar2);
       return;
     }
     if (t == tl) {                      // terminal / leg-end knot: E is not used
       mbar_expect_tx(bar, (uint32_t)PL::kstride * 8u);
       tma_load_1d(rec, src, (uint32_t)PL::kstride * 8u, bar);
     } else {
-      mbar_expect_tx(bar, (uint32_t)PL::kstride * 8u);
-      tma_load_1d(rec, src, (uint32_t)PL::oE * 8u, bar);
+      mbar_expect_tx(bar, (uint32_t)(n * n) * 8u);
       tma_load_1d(Einv, p.einv + ((size_t)b * T + pt) * (size_t)(n * n), (uint32_t)(n * n) * 8u, bar);
-      tma_load_1d(rec + PL::of, src + PL::of, (uint32_t)(PL::kstride - PL::of) * 8u, bar);
+      mbar_expect_tx(bar2, (uint32_t)(PL::kstride - n * n) * 8u);
+      tma_load_1d(rec, src, (uint32_t)PL::oE * 8u, bar2);
+      tma_load_1d(rec + PL::of, src + PL::of, (uint32_t)(PL::kstride - PL::of) * 8u, bar2);
     }
   };
   auto store_gains = [&](int t) {     // all threads; Gs complete
@@ -251,7 +256,8 @@ sweep_kernel(const DevParams p) {
 
   // ---- terminal knot (nu = nc = 0): Pmat = Q, pvec = q, empty gains  (riccati-kernel.hxx:90-150)
   if (tid == 0) issue_load(tl);
-  mbar_wait(bar, phase); phase ^= 1;
+  if constexpr (EG && !EX) { mbar_wait(bar2, phase2); phase2 ^= 1; }     // (EG stages every knot through bar2)
+  else { mbar_wait(bar, phase); phase ^= 1; }
   if constexpr (LEG && h > 0) {
     // ---- leg-end knot of a coupled leg: terminalSolve with nu > 0 and the parameter block
     //      Gx = A^T, Gu = B^T, Gth = -mudyn I, gamma = f     (riccati-kernel.hxx:110-149, parallel-solver.hpp:43-51)
@@ -341,7 +347,7 @@ sweep_kernel(const DevParams p) {
       tma_store_wait_read();
     }
     if constexpr (EG && !EX) gE = p.einv + ((size_t)b * T + phys_t(p, t)) * (size_t)(n * n);
-    mbar_wait(bar, phase); phase ^= 1;
+    if constexpr (EX || !EG) { mbar_wait(bar, phase); phase ^= 1; }
     cta_sync<NT, GRP>();
     PH(0);
     double fro = 0.0;
@@ -413,6 +419,7 @@ sweep_kernel(const DevParams p) {
     const double xnorm = mudyn * sqrt(fro);
     const int order = xnorm <= 1e-9 ? 1 : xnorm <= 1e-6 ? 2 : xnorm <= 3e-5 ? 3 : 0;
     const bool neumann = order > 0;
+    if constexpr (!EX) { mbar_wait(bar2, phase2); phase2 ^= 1; }     // the rest of the record is here
     // (3) w = ptilde + Ptilde f -> pv                                                   (:182-187)
     gemv4<n, n, NT>(tid, [&](int i, int j) { return P[i + j * n]; }, [&](int j) { return f[j]; },
                     [&](int i) { return EX ? pv[i] : -x1v[i]; }, [&](int i, double v) { pv[i] = v; });   // ptilde = -x1v (EX: = pvec)
