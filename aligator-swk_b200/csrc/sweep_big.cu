@@ -90,7 +90,9 @@ template <int NX, int NU> struct BigPlan {
   static_assert(total * 8 <= 227 * 1024, "shared-memory plan exceeds 227 KB");
 };
 
-template <int NX, int NU, int NW, int MINB, bool PROF = false>
+// EX: explicit dynamics, E_t == -I for every knot (explicit-dynamics.hxx:32; checked on the device or promised by
+// the caller): no pre-pass, E^{-1} is never read, Ptilde = Pmat, -E^{-1} [A_pre | tv] = [A_pre | tv] (see sweep_fast.cu).
+template <int NX, int NU, int NW, int MINB, bool PROF = false, bool EX = false>
 __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParams p) {
   extern __shared__ __align__(16) double sm[];
   using PL = BigPlan<NX, NU>;
@@ -142,7 +144,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
     const char *k = reinterpret_cast<const char *>(knot_ptr(t));
     constexpr uint32_t kb = (uint32_t)PL::kstride * 8u, CH = 32768u;
     for (uint32_t o = 0; o < kb; o += CH) l2_prefetch(k + o, (kb - o < CH) ? (kb - o) : CH);
-    if (t < T) {
+    if (!EX && t < T) {
       const char *e = reinterpret_cast<const char *>(einv_ptr(t));
       constexpr uint32_t eb = (uint32_t)(n * n) * 8u;
       for (uint32_t o = 0; o < eb; o += CH) l2_prefetch(e + o, (eb - o < CH) ? (eb - o) : CH);
@@ -188,13 +190,27 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
 #pragma unroll 1
   for (int t = T - 1; t >= 0; t--) {
     const double *kn = knot_ptr(t);
-    const double *gQS = kn + PL::oQ, *gAB = kn + PL::oA, *gB = kn + PL::oB, *gE = einv_ptr(t);
+    const double *gQS = kn + PL::oQ, *gAB = kn + PL::oA, *gB = kn + PL::oB, *gE = EX ? nullptr : einv_ptr(t);
+    (void)gE;
     if (tid == 0) {
       issue_small(t);
       if (t > 0) prefetch_knot(t - 1);
       tma_store_wait_read();
     }
     PH(0);
+    double fro = 0.0;
+    if constexpr (EX) {
+      // E^{-1} = -I: Ptilde = Pmat, lower-symmetrised (:179-180, exact); ptilde = pvec
+      for (int e = tid; e < n * n; e += NT) {
+        const int i = e % n, j = e / n;
+        if (i >= j) {
+          const double v = P[e];
+          if (i > j) P[j + i * n] = v;
+          fro = fma(i == j ? v : 2.0 * v, v, fro);
+        }
+      }
+      PH(1);
+    } else {
     // (1) [X1 | x1v] = Einv^T [P | pvec]          EinvP, -ptilde      (:175-178)
     strip_gemm<n, na, n, NW, true, false>(warp, lane,
         [&](int i, int k) { return __ldg(gE + k + i * n); },
@@ -205,7 +221,6 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
     PH(1);
     // (2) Ptilde^T = Einv^T X1^T; the upper triangle of the transposed product IS the reference's
     //     lower triangle of Ptilde = X1 Einv, mirrored; ||Ptilde||_F^2 on the fly      (:179-180)
-    double fro = 0.0;
     strip_gemm<n, n, n, NW, true, false>(warp, lane,
         [&](int i, int k) { return __ldg(gE + k + i * n); },
         [&](int k, int j) { return X1[j + k * n]; },
@@ -213,6 +228,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
         [&](int i, int j, double v) {
           if (i <= j) { P[j + i * n] = v; P[i + j * n] = v; fro = fma(i == j ? v : 2.0 * v, v, fro); }
         });
+    }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) fro += __shfl_xor_sync(0xffffffffu, fro, o);
     if (lane == 0) red[warp] = fro;
@@ -221,11 +237,16 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
     fro = 0.0;
 #pragma unroll
     for (int w = 0; w < NW; w++) fro += red[w];
-    const bool neumann = mudyn * sqrt(fro) <= 1e-9;     // see sweep_fast.cu
+    // order of the Neumann series for Lambda^{-1} (see sweep_fast.cu): truncation x^(order+1) <= 1e-18
+    const double xnorm = mudyn * sqrt(fro);
+    // (orders 2 and 3 are compiled into the explicit-dynamics kernel only, where Ptilde = Pmat is not scaled
+    //  down by |E|^-2: the general kernel sits at the 168-register cap and the extra loop costs it 6 %)
+    const int order = xnorm <= 1e-9 ? 1 : !EX ? 0 : xnorm <= 1e-6 ? 2 : xnorm <= 3e-5 ? 3 : 0;
+    const bool neumann = order > 0;
     PH(2);
     // (3) w = ptilde + Ptilde f -> pv                                                   (:182-187)
     gemv4<n, n, NT>(tid, [&](int i, int j) { return P[i + j * n]; }, [&](int j) { return f[j]; },
-                    [&](int i) { return -x1v[i]; }, [&](int i, double v) { pv[i] = v; });
+                    [&](int i) { return EX ? pv[i] : -x1v[i]; }, [&](int i, double v) { pv[i] = v; });   // ptilde = -x1v (EX: = pvec)
     if (!neumann) {
       for (int e = tid; e < n * n; e += NT) {
         const int i = e % n, j = e / n;
@@ -241,6 +262,17 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
           [&](int k, int j) { return P[k + j * n]; },
           [&](int i, int j) { return P[i + j * n]; },
           [&](int i, int j, double v) { X1[i + j * n] = v; });
+      if constexpr (EX) {
+#pragma unroll 1
+        for (int it = 1; it < order; it++) {                  // Y <- [Ptilde | w] - mudyn Ptilde Y, in place (column strips)
+          cta_sync<NT>();
+          mma_gemm_colstrips<n, na, n, NW>(warp, lane,
+              [&](int i, int k) { return -mudyn * P[i + k * n]; },
+              [&](int k, int j) { return X1[k + j * n]; },
+              [&](int i, int j) { return P[i + j * n]; },
+              [&](int i, int j, double v) { X1[i + j * n] = v; });
+        }
+      }
       cta_sync<NT>();
       for (int e = tid; e < n * na; e += NT) {                // back into P, mirrored from the lower triangle
         const int i = e % n, j = e / n;
@@ -390,6 +422,10 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
     cta_sync<NT>();
     PH(10);
     // (10) [Afb | yff] = -Einv [A_pre | tv]                                              (:243-245)
+    if constexpr (EX) {                 // -E^{-1} = I: the block itself, row-major into the A rows of fb
+      for (int e = tid; e < n * n; e += NT) { const int i = e / n, j = e % n; gfbg[(rA + i) * n + j] = P[i + j * n]; }
+      for (int i = tid; i < n; i += NT) ff[rA + i] = pv[i];
+    } else {
     strip_gemm<n, na, n, NW, true, false>(warp, lane,
         [&](int i, int k) { return -__ldg(gE + i + k * n); },
         [&](int k, int j) { return P[k + j * n]; },
@@ -398,6 +434,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
           if (j < n) gfbg[(rA + i) * n + j] = v;
           else ff[rA + i] = v;
         });
+    }
     cta_sync<NT>();
     PH(11);
     // (11) [Pmat | pvec] = [Qhat | qhat] + Shat [K | kff]                                 (:249-250)
@@ -491,7 +528,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
   }
 }
 
-template <int NX, int NU, int NW>
+template <int NX, int NU, int NW, bool EX = false>
 static int launch_big_t(const DevParams &p, cudaStream_t st) {
   using PL = BigPlan<NX, NU>;
   if (p.KL.stride != PL::kstride || p.GL.stride != PL::gstride || p.KL.E != PL::oE || p.KL.f != PL::of ||
@@ -500,7 +537,9 @@ static int launch_big_t(const DevParams &p, cudaStream_t st) {
   const long long total = (long long)p.batch * p.T;
   int launched = 0;
   const bool lu_prepass = p.tune.einv_mode == 2;
-  if (total > 0 && !lu_prepass) {
+  if (EX) {
+    // explicit dynamics: no E^{-1}, no pre-pass
+  } else if (total > 0 && !lu_prepass) {
     constexpr int EW = 5;
     constexpr size_t esm = (size_t)GjCta<NX>::SMEM * sizeof(double) + (size_t)GjCta<NX>::SINTS * sizeof(int);
     if (cudaFuncSetAttribute(einv_cta_dmma_kernel<NX, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)esm) != cudaSuccess) return -2;
@@ -516,7 +555,7 @@ static int launch_big_t(const DevParams &p, cudaStream_t st) {
     launched++;
   }
   const size_t smem = (size_t)PL::total * sizeof(double);
-  auto ks = p.phase_cycles ? sweep_big_kernel<NX, NU, NW, 1, true> : sweep_big_kernel<NX, NU, NW, 1, false>;
+  auto ks = p.phase_cycles ? sweep_big_kernel<NX, NU, NW, 1, true, EX> : sweep_big_kernel<NX, NU, NW, 1, false, EX>;
   if (cudaFuncSetAttribute(ks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return -2;
   ks<<<p.batch, 32 * NW, smem, st>>>(p);
   if (cudaGetLastError() != cudaSuccess) return -2;
@@ -526,7 +565,8 @@ static int launch_big_t(const DevParams &p, cudaStream_t st) {
 bool big_path_available(int nx, int nu, int nc, int nth) { return nx == 76 && nu == 32 && nc == 0 && nth == 0; }
 
 int launch_backward_big(const DevParams &p, cudaStream_t st) {
-  if (p.nx == 76 && p.nu == 32 && p.nc == 0 && p.nth == 0) return launch_big_t<76, 32, 10>(p, st);
+  if (p.nx == 76 && p.nu == 32 && p.nc == 0 && p.nth == 0)
+    return p.explicit_dyn ? launch_big_t<76, 32, 10, true>(p, st) : launch_big_t<76, 32, 10>(p, st);
   return -3;
 }
 

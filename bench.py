@@ -738,7 +738,7 @@ def main():
                          "CUDA IPC mapping (no SMs; measured on 2 B200s: no gain on c1b, 6.4 vs 3.8 ms/step on c2 — torch's "
                          "cross-process peer copy does not overlap like the NCCL kernel does); auto tries p2p first")
     ap.add_argument("--dist", default="ref", choices=["ref", "explicit", "explicit_psd"], help="synthetic distribution (SURVEY 8d)")
-    ap.add_argument("--others", default="c2,c3,c5,c1b+explicit_psd,c2+explicit_psd,c1b+explicit,p30", help="other BASELINE configs summarised in other_configs at N = 1 ('' = none)")
+    ap.add_argument("--others", default="c2,c3,c5,c1b+explicit_psd,c2+explicit_psd,c5+explicit_psd,c1b+explicit,p30", help="other BASELINE configs summarised in other_configs at N = 1 ('' = none)")
     ap.add_argument("--tune", action="append", default=[], help="diagnostic launcher knob key=value (garb200_set_tuning)")
     ap.add_argument("--horizons", action="store_true", help="the reference's own latency sweep over horizons (one GPU)")
     args = ap.parse_args()
