@@ -672,6 +672,100 @@ __device__ __forceinline__ void ldlt_solve_lanes(int tid, const double *S, const
 }
 
 // ------------------------------------------------------------------------------------------
+// ldlt_solve_dmma: the same two substitutions BLOCKED on the tensor pipe.  A warp owns whole 8-column
+// tiles of the right-hand sides and keeps all N rows of its tile in registers as m8n8k4 accumulator
+// fragments (lane (g, q): rows g + 8 mt, columns 2q, 2q + 1).  Per 4-row block: (a) the 4 x 4 unit
+// triangular block is substituted in registers (the four rows sit in four lanes of equal q: one
+// shuffle + one FMA per dependent step), (b) the finished block becomes the B fragment of ONE rank-4
+// DMMA per row tile still to be updated (C -> B layout by one shuffle pair + select), the A fragments
+// (-L) come straight from the factor in shared memory.  2 N / 4 dependent block steps of ~10
+// instructions instead of 2 N shuffle + FMA steps, and no barrier: column tiles are independent.
+// S: unit lower factor (col-major, leading dimension N, N % 4 == 0), dinv: 1 / d.
+// ------------------------------------------------------------------------------------------
+template <int N, int NR, int NT, class RH>
+__device__ __forceinline__ void ldlt_solve_dmma(int tid, const double *S, const double *dinv, RH R) {
+  static_assert(N % 4 == 0, "ldlt_solve_dmma: N % 4 == 0");
+  constexpr int NW = NT / 32, TM = (N + 7) / 8, TN = (NR + 7) / 8, NB = N / 4;
+  const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, q = lane & 3;
+#pragma unroll 1
+  for (int tj = warp; tj < TN; tj += NW) {
+    const int jc = tj * 8 + 2 * q;
+    double c[TM][2];
+#pragma unroll
+    for (int mt = 0; mt < TM; mt++) {
+      const int row = g + 8 * mt;
+      c[mt][0] = (row < N && jc < NR) ? R.get(row, jc) : 0.0;
+      c[mt][1] = (row < N && jc + 1 < NR) ? R.get(row, jc + 1) : 0.0;
+    }
+    // forward: L Y = R
+#pragma unroll
+    for (int kb = 0; kb < NB; kb++) {
+      const int mt0 = kb >> 1, h = kb & 1, r0 = 4 * kb;
+#pragma unroll
+      for (int i = 0; i < 3; i++) {                // (a) rows r0 + i + 1 .. r0 + 3 -= L(., r0 + i) y_i
+        const int src = ((4 * h + i) << 2) | q;
+        const double y0 = __shfl_sync(0xffffffffu, c[mt0][0], src), y1 = __shfl_sync(0xffffffffu, c[mt0][1], src);
+        if (g > 4 * h + i && g <= 4 * h + 3) {
+          const double l = S[(r0 + g - 4 * h) + (r0 + i) * N];
+          c[mt0][0] = fma(-l, y0, c[mt0][0]); c[mt0][1] = fma(-l, y1, c[mt0][1]);
+        }
+      }
+      if (kb + 1 < NB) {                           // (b) rows below -= L(below, block) Y_block
+        const int srcb = ((4 * h + q) << 2) | (g >> 1);
+        const double b0 = __shfl_sync(0xffffffffu, c[mt0][0], srcb), b1 = __shfl_sync(0xffffffffu, c[mt0][1], srcb);
+        const double bv = (g & 1) ? b1 : b0;
+#pragma unroll
+        for (int mt = mt0; mt < TM; mt++) {
+          if (mt == mt0 && h == 1) continue;
+          const int row = 8 * mt + g;
+          const double a = (row > r0 + 3 && row < N) ? -S[row + (r0 + q) * N] : 0.0;
+          dmma_884(c[mt][0], c[mt][1], a, bv);
+        }
+      }
+    }
+#pragma unroll
+    for (int mt = 0; mt < TM; mt++) {
+      const int row = g + 8 * mt;
+      if (row < N) { const double d = dinv[row]; c[mt][0] *= d; c[mt][1] *= d; }
+    }
+    // backward: L^T X = D^{-1} Y
+#pragma unroll
+    for (int kb = NB - 1; kb >= 0; kb--) {
+      const int mt0 = kb >> 1, h = kb & 1, r0 = 4 * kb;
+#pragma unroll
+      for (int i = 3; i > 0; i--) {                // (a) rows r0 .. r0 + i - 1 -= L(r0 + i, .)^T x_i
+        const int src = ((4 * h + i) << 2) | q;
+        const double x0 = __shfl_sync(0xffffffffu, c[mt0][0], src), x1 = __shfl_sync(0xffffffffu, c[mt0][1], src);
+        if (g >= 4 * h && g < 4 * h + i) {
+          const double l = S[(r0 + i) + (r0 + g - 4 * h) * N];
+          c[mt0][0] = fma(-l, x0, c[mt0][0]); c[mt0][1] = fma(-l, x1, c[mt0][1]);
+        }
+      }
+      if (kb > 0) {                                // (b) rows above -= L(block, above)^T X_block
+        const int srcb = ((4 * h + q) << 2) | (g >> 1);
+        const double b0 = __shfl_sync(0xffffffffu, c[mt0][0], srcb), b1 = __shfl_sync(0xffffffffu, c[mt0][1], srcb);
+        const double bv = (g & 1) ? b1 : b0;
+#pragma unroll
+        for (int mt = 0; mt <= mt0; mt++) {
+          if (mt == mt0 && h == 0) continue;
+          const int row = 8 * mt + g;
+          const double a = (row < r0) ? -S[(r0 + q) + row * N] : 0.0;
+          dmma_884(c[mt][0], c[mt][1], a, bv);
+        }
+      }
+    }
+#pragma unroll
+    for (int mt = 0; mt < TM; mt++) {
+      const int row = g + 8 * mt;
+      if (row < N) {
+        if (jc < NR) R.set(row, jc, c[mt][0]);
+        if (jc + 1 < NR) R.set(row, jc + 1, c[mt][1]);
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // X = E^{-1} entirely in REGISTERS: in-place Gauss-Jordan elimination with row partial
 // pivoting (same pivot rule as PartialPivLU: largest |entry| of the column among the rows not
 // yet used).  LPM lanes own one matrix (8 for N <= 16: four matrices per warp), lane `sub`

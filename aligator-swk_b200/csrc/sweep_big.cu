@@ -346,7 +346,7 @@ __global__ void __launch_bounds__(32 * NW, MINB) sweep_big_kernel(const DevParam
     {
       const bool okk = *kkt_ok != 0;
       if (okk) {
-        ldlt_solve_lanes<sp, na, NT>(tid, kkt, dinv, RhsGainsTh<n, 0, s>{ff, fb, nullptr});
+        ldlt_solve_dmma<sp, na, NT>(tid, kkt, dinv, RhsGainsTh<n, 0, s>{ff, fb, nullptr});
         cta_sync<NT>();
       } else {
         build_kkt();

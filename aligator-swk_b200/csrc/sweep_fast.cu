@@ -555,7 +555,10 @@ sweep_kernel(const DevParams p) {
     {
       const bool okk = *kkt_ok != 0;
       if (okk) {
-        ldlt_solve_lanes<sp, na, NT>(tid, kkt, dinv, RhsGainsTh<n, h, s>{ff, fb, fth});
+        // small systems (12 x 12, 4 x 4): one lane group per column; larger ones (constraints: 20, 24): blocked on
+        // the tensor pipe (measured: c1b 21.95 vs 22.09 ms with lanes / DMMA, c3 68.3 vs 65.1 ms)
+        if constexpr (sp >= 16) ldlt_solve_dmma<sp, na, NT>(tid, kkt, dinv, RhsGainsTh<n, h, s>{ff, fb, fth});
+        else ldlt_solve_lanes<sp, na, NT>(tid, kkt, dinv, RhsGainsTh<n, h, s>{ff, fb, fth});
         cta_sync<NT, GRP>();
       } else {                        // uniform: rebuild and factorise with the reference's Bunch-Kaufman pivoting
         kkt_matrix(std::integral_constant<int, NW>{}, warp, tid, NT);
