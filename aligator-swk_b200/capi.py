@@ -293,6 +293,60 @@ class Solver:
         """device-resident producer (updateLQSubproblem, solver-proxddp.hxx:802-873)"""
         check(lib().garb200_pack_from_device(self._h, C.byref(view), float(preg)))
 
+    def pack_from_tensors(self, fields, preg=0.0):
+        """Zero-copy producer input from device tensors (torch CUDA tensors, or anything with
+        ``__cuda_array_interface__``): ``fields`` maps the knot field names (Q S R q r A B E f C D d Gth Gx Gu gamma,
+        plus G0 g0) to float64 arrays of shape [B, T+1, rows, cols] (matrices), [B, T+1, rows] (vectors),
+        [B, c0, nx] / [B, c0] (G0 / g0).  Any batch / knot strides are taken as they are; inside a block the
+        ROW stride must be 1 (the solver's blocks are column-major: element (i, j) at i + j * ld), i.e. a tensor
+        made as ``x.transpose(-1, -2).contiguous().transpose(-1, -2)`` or a [B, T+1, cols, rows] buffer viewed
+        transposed; anything else is refused rather than copied.  A missing ``E`` means explicit dynamics (E = -I).
+        Returns the view (keep the tensors alive until the stream has run the packing kernel)."""
+        view = DeviceProblemView()
+        for name, a in fields.items():
+            if a is None:
+                continue
+            if hasattr(a, "data_ptr"):                       # torch
+                if str(a.dtype) not in ("torch.float64",) or not a.is_cuda:
+                    raise TypeError(f"{name}: float64 CUDA tensor expected")
+                ptr, shape, strides = a.data_ptr(), tuple(a.shape), tuple(a.stride())
+            else:
+                cai = a.__cuda_array_interface__
+                if cai["typestr"] not in ("<f8", "=f8"):
+                    raise TypeError(f"{name}: float64 expected")
+                ptr, shape = cai["data"][0], tuple(cai["shape"])
+                st = cai.get("strides")
+                if st is None:
+                    st, acc = [], 1
+                    for d in reversed(shape):
+                        st.insert(0, acc); acc *= d
+                    strides = tuple(st)
+                else:
+                    strides = tuple(x // 8 for x in st)
+            f = getattr(view, name)
+            if name in ("G0", "g0"):
+                if name == "G0":
+                    if len(shape) != 3 or (shape[1] > 1 and strides[1] != 1):
+                        raise ValueError("G0: [B, c0, nx] with unit stride along c0 (column-major block)")
+                    f.ptr, f.stride_b, f.stride_t, f.ld = ptr, strides[0], 0, strides[2]
+                else:
+                    if len(shape) != 2 or (shape[1] > 1 and strides[1] != 1):
+                        raise ValueError("g0: [B, c0] contiguous along c0")
+                    f.ptr, f.stride_b, f.stride_t, f.ld = ptr, strides[0], 0, max(shape[1], 1)
+                continue
+            if len(shape) == 4:
+                if shape[2] > 1 and strides[2] != 1:
+                    raise ValueError(f"{name}: the row stride inside a block must be 1 (column-major blocks); got strides {strides}")
+                f.ptr, f.stride_b, f.stride_t, f.ld = ptr, strides[0], strides[1], strides[3] if shape[3] > 1 else max(shape[2], 1)
+            elif len(shape) == 3:
+                if shape[2] > 1 and strides[2] != 1:
+                    raise ValueError(f"{name}: vectors must be contiguous along their last axis")
+                f.ptr, f.stride_b, f.stride_t, f.ld = ptr, strides[0], strides[1], max(shape[2], 1)
+            else:
+                raise ValueError(f"{name}: [B, T+1, rows, cols] or [B, T+1, rows] expected, got {shape}")
+        self.pack_from_device(view, preg)
+        return view
+
     def linear_step(self, alpha, cur, trial):
         """trial = cur + alpha * (solver-owned direction); cur / trial: 4-tuples of device pointers"""
         check(lib().garb200_linear_step(self._h, float(alpha), *[_ptr(a) for a in cur], *[_ptr(a) for a in trial]))

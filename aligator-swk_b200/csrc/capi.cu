@@ -208,6 +208,12 @@ int garb200_create(const garb200_config *cfg, garb200_solver **out) {
   const bool want_fast = !padded && !p.dense && !(c.flags & GARB200_FORCE_GENERIC) && fast_path_available(c.nx, c.nu, c.nc, c.nth, c.num_legs);
   // (a shape with a specialised sweep may exceed the generic kernel's shared-memory plan: it then has
   //  no generic fallback and ragged knots are refused at backward())
+  // A shape that neither a specialised sweep (native or by padding) nor the generic proximal kernel's
+  // shared-memory plan can hold still has the dense per-knot KKT solver (csrc/dense.cu: same interface, same
+  // records, same solution to round-off; slow but sturdy) as long as ITS matrix fits: taken automatically.
+  if (!want_fast && !padded && !p.dense && !legs && !(c.flags & GARB200_FORCE_GENERIC) &&
+      backward_smem_bytes(p) > 227u * 1024u && dense_smem_bytes(p) <= 227u * 1024u)
+    p.dense = 1;
   if (!want_fast && !padded && !p.dense && backward_smem_bytes(p) > 227u * 1024u) {
     char buf[256];
     snprintf(buf, sizeof buf, "dimensions need %zu bytes of shared memory per CTA (> 227 KB): "

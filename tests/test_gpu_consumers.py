@@ -87,6 +87,52 @@ def test_pack_from_device_equals_host_staging(capi, oracle, dims):
     s.close()
 
 
+def test_pack_from_torch_tensors_zero_copy(capi, oracle):
+    """The Python producer path (VERDICT r1 missing #9): torch CUDA tensors in, no host staging, no copy -- batch and
+    knot strides as they come (here: views into larger buffers), column-major blocks."""
+    import torch
+    nx, nu, nc, nth, T, B, mu = 12, 4, 2, 1, 7, 3, 1e-9
+    pp = generate_problems(B, T, nx, nu, nc, nth, seed=41)
+    L = pp.layout
+    fields, keep = {}, []
+    for name, (rows, cols) in L.shapes().items():
+        if rows * cols == 0:
+            continue
+        host = np.zeros((B, T + 1, rows, cols))
+        for b in range(B):
+            for t in range(T + 1):
+                blk = L.unpack(pp.knots[b, t], int(pp.nu_t[t]), int(pp.nc_t[t]))[name]
+                host[b, t, :blk.shape[0], :blk.shape[1]] = blk
+        if cols == 1 and name in ("q", "r", "f", "d", "gamma"):
+            big = torch.full((B + 1, T + 3, rows), float("nan"), dtype=torch.float64, device="cuda")
+            v = big[1:, 2:, :]                                   # a strided view: batch / knot strides are not packed
+            v.copy_(torch.as_tensor(host[..., 0]))
+            fields[name] = v
+        else:
+            buf = torch.full((B, T + 1, cols, rows + 2), float("nan"), dtype=torch.float64, device="cuda")   # ld = rows + 2
+            v = buf[..., :rows].transpose(-1, -2)                # [B, T+1, rows, cols], row stride 1
+            v.copy_(torch.as_tensor(host))
+            fields[name] = v
+        keep.append(fields[name])
+    fields["G0"] = torch.as_tensor(np.ascontiguousarray(pp.G0.reshape(B, nx, pp.nc0)), device="cuda").transpose(-1, -2)
+    fields["g0"] = torch.as_tensor(pp.g0, device="cuda")
+    torch.cuda.synchronize()
+    s = capi.Solver.for_problems(pp)
+    s.pack_from_tensors(fields)
+    k, G0, g0 = s.download_packed(0, B)
+    # (knots with a smaller own nu / nc use the top-left corner: the terminal knot here)
+    assert np.array_equal(k, pp.knots) and np.array_equal(G0, pp.G0) and np.array_equal(g0, pp.g0)
+    theta = np.random.default_rng(0).standard_normal((B, nth))
+    s.backward(mu, mu)
+    xs, us, vs, lb = s.forward(theta)
+    for b in range(B):
+        ref = oracle.prox_solve(pp, mu, mu, theta=theta[b], b=b)
+        assert relerr(xs[b], ref["xs"]) < 1e-10 and relerr(lb[b], ref["lbdas"]) < 1e-10
+    with pytest.raises(ValueError):                              # row-major blocks are refused, not silently copied
+        s.pack_from_tensors({"Q": torch.zeros((B, T + 1, nx, nx), dtype=torch.float64, device="cuda")})
+    s.close()
+
+
 def test_pack_from_device_without_Jy_is_explicit_dynamics(capi, oracle):
     """No E array: explicit dynamics, E = -I (explicit-dynamics.hxx:32) -> the explicit path, same answer as
     the host-staged problem with E = -I."""

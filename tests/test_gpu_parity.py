@@ -382,6 +382,32 @@ DENSE_CASES = [
 ]
 
 
+@pytest.mark.parametrize("dims", [(50, 20, 4, 0, 6, 2), (52, 12, 3, 1, 5, 2)],
+                         ids=lambda d: "nx%d_nu%d_nc%d_nth%d_T%d_B%d" % d)
+def test_shapes_nothing_else_holds_take_the_dense_kernel(capi, oracle, dims):
+    """nx > 36 with constraints / parameters (no covering instantiation, beyond the generic kernel's shared-memory
+    plan): garb200_create falls back to the dense per-knot KKT solver on its own -- slow, but nothing that fits it is
+    rejected.  Same interface and records; checked against the proximal oracle."""
+    nx, nu, nc, nth, T, B = dims
+    mu = 1e-8
+    pp = generate_problems(B, T, nx, nu, nc, nth, seed=3 * nx + T)
+    theta = np.random.default_rng(4).standard_normal((B, nth)) if nth else None
+    s = capi.Solver.for_problems(pp)
+    assert s.padded_shape() is None
+    s.upload(pp); s.backward(mu, mu)
+    assert not s.used_fast_path()
+    xs, us, vs, lb = s.forward(theta)
+    assert (s.get_flags() == 0).all()
+    for b in range(B):
+        ref = oracle.prox_solve(pp, mu, mu, theta=None if theta is None else theta[b], b=b)
+        for got, key in ((xs[b], "xs"), (us[b], "us"), (vs[b], "vs"), (lb[b], "lbdas")):
+            assert relerr(got, ref[key]) < 1e-9, (b, key, relerr(got, ref[key]))
+    assert s.kkt_error(mu, mu, theta).max() < 1e-7
+    s.close()
+    with pytest.raises(capi.GarB200Error):          # ... and what does not fit it still says so
+        capi.Solver(76, 32, 6, 0, horizon=4)
+
+
 @pytest.mark.parametrize("case", DENSE_CASES, ids=lambda c: "nx%d_nu%d_nc%d_nth%d_T%d_B%d_%g_%s" % c)
 def test_dense_kernel_parity(capi, oracle, case):
     """csrc/dense.cu against the oracle's restatement of DenseKernel / RiccatiSolverDense (oracle/dense.cpp):
