@@ -150,17 +150,44 @@ def cpu_port_throughput(w, budget_s=12.0, dist="ref"):
 
 def reference_arm(args, w, rank, world):
     """--impl reference: the reference's CPU path.  The real reference needs Eigen 3.4 (absent,
-    no network): the Eigen-free oracle port is timed instead (kind = "port")."""
+    no network): the Eigen-free oracle port is timed instead (kind = "port").
+    One bounded sample of the workload is generated ONCE; every step is one timed pass over it with all host
+    threads, sized so that the whole --steps K --warmup W run stays within ~2 minutes whatever K is."""
     if rank != 0:
         return
+    import garb200_pkg
+    garb200_pkg.load()
+    from aligator_swk_b200.synth import generate_problems
+    import pyoracle as po
+    po.build()
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except AttributeError:
+        cores = os.cpu_count() or 1
+    nx, nu, nc, nth, T, legs = w["nx"], w["nu"], w["nc"], w["nth"], w["T"], w["legs"]
+    theta = np.random.default_rng(3).standard_normal(nth) if nth else None
+    single = legs >= 2 or w["batch"] == 1
+    nsteps = max(1, args.steps + args.warmup)
+    per_step_budget = max(0.25, min(15.0, 90.0 / nsteps))          # seconds of CPU work per step
+    n0 = 1 if single else max(cores, 8)
+    pp = generate_problems(n0, T, nx, nu, nc, nth, seed=42, dist=args.dist)
+    secs, used = po.bench(pp, MU, MU, theta=theta, num_legs=legs, reps=1, nthreads=cores)   # calibration (+ warm caches)
+    if single:
+        nprob, reps = 1, int(max(1, min(500, per_step_budget / max(secs, 1e-6))))
+    else:
+        per = secs / n0                                             # wall seconds per solve at full thread count
+        nprob = int(max(n0, min(w["batch"], 1024, per_step_budget / max(per, 1e-9))))
+        reps = int(max(1, min(50, per_step_budget / max(per * nprob, 1e-9))))
+        if nprob != n0:
+            pp = generate_problems(nprob, T, nx, nu, nc, nth, seed=42, dist=args.dist)
     per_step = []
-    sample = ""
-    cores = 1
-    budget = max(3.0, min(15.0, 60.0 / max(1, args.steps + args.warmup)))
     for i in range(args.warmup + args.steps):
-        v, cores, sample = cpu_port_throughput(w, budget_s=budget, dist=args.dist)
+        secs, used = po.bench(pp, MU, MU, theta=theta, num_legs=legs, reps=reps, nthreads=cores)
         if i >= args.warmup:
-            per_step.append(v)
+            per_step.append(nprob * reps / secs)
+    cores = used
+    sample = (f"{nprob} of {w['batch']} problems x {reps} repetition(s) per step, generated once; OpenMP over problems, {used} threads"
+              if not single else f"1 problem x {reps} repetitions per step, {used} threads" + (f" ({legs} legs)" if legs >= 2 else ""))
     v = float(np.mean(per_step))
     ms = 1e3 * w["batch"] * world / v
     line = {
