@@ -612,8 +612,9 @@ def e2e_run(torch, capi, s_dev, w, K, W, dist, world, theta):
     nx, nu, nc, nth, T, B, legs = w["nx"], w["nu"], w["nc"], w["nth"], w["T"], w["batch"], w["legs"]
     stride = s_dev.download_packed(0, 1)[0].shape[-1]
     per_problem = (T + 1) * stride * 8
-    Be = int(min(B, max(1, (8 << 30) // per_problem)))       # cap pinned staging at 8 GiB
-    note = None if Be == B else f"e2e on a {Be}-problem slice (pinned staging capped at 8 GiB)"
+    cap = max(1 << 30, (8 << 30) // max(1, world))           # pinned staging: 8 GiB per box, at least 1 GiB per rank
+    Be = int(min(B, max(1, cap // per_problem)))
+    note = None if Be == B else f"e2e on a {Be}-problem slice per rank (pinned staging capped at {cap / 2**30:.0f} GiB per rank)"
 
     def pinned(*shape):
         return torch.empty(shape, dtype=torch.float64, pin_memory=True).numpy()
