@@ -1330,4 +1330,234 @@ __device__ __forceinline__ bool gj_inverse_cta(int tid, const double *__restrict
   return __syncthreads_or(bad) == 0;
 }
 
+// ------------------------------------------------------------------------------------------
+// The block Gauss-Jordan of gj_inverse_dmma for matrices too large for ONE warp's registers (nx = 76), with
+// the tiles still in REGISTERS: a CTA of NWARP warps per matrix, warp w owns the tile columns
+// [w CPW, (w + 1) CPW) as accumulator fragments for all N / 4 block steps; the row-major swizzled mirror in
+// shared memory (same layout as gj_inverse_dmma) carries everything indexed by a run-time row.  Per step:
+// warp 0 eliminates the 4-column panel (row-per-lane from the mirror, LU style, partial pivoting over all
+// unpivoted rows) and publishes W and the pivot rows' indices; after one barrier every warp updates ITS tile
+// columns with one rank-4 DMMA per tile (B rows: the raw pivot rows of its own columns from the mirror),
+// stores them to the mirror, the owner of the panel's tile column patches the pivot rows' panel entries to e_s
+// and re-reads them; one more barrier.  Against gj_inverse_cta (matrix in shared memory: every update loads
+// AND stores all of it) this halves the shared-memory traffic, which is what bounds that kernel.
+// ------------------------------------------------------------------------------------------
+template <int N, int NWARP> struct GjCtaRegs {
+  static_assert(N % 4 == 0 && N <= 124, "CTA block Gauss-Jordan: N % 4 == 0, N <= 124 (7-bit row key)");
+  static constexpr int NTL = (N + 7) / 8, NP = NTL * 8, NB = N / 4;
+  static_assert(NTL % NWARP == 0, "tile columns must divide evenly over the warps");
+  static constexpr int CPW = NTL / NWARP;
+  static constexpr int PLD = (NP % 16 == 8) ? NP : NP + 8;          // == 8 (mod 16)
+  static constexpr int WLD = (NP % 16 == 8) ? NP + 4 : NP + 12;     // == 12 (mod 16)
+  static constexpr int RPL = (NP + 31) / 32;
+  static constexpr int PAN = 0, BINV = 4 * WLD, YS = BINV + 16 * (2 * NTL);
+  static constexpr int SMEM = YS + N * PLD;
+  static constexpr int SINTS = NP + 8;                               // piv[c] | rsel[4] | bad
+};
+
+template <int N, int NWARP>
+__device__ __forceinline__ bool gj_inverse_cta_regs(int tid, const double *__restrict__ Eg, double *__restrict__ Xg,
+                                                    double *sw, int *si) {
+  using G = GjCtaRegs<N, NWARP>;
+  constexpr int NTL = G::NTL, NP = G::NP, NB = G::NB, PLD = G::PLD, WLD = G::WLD, RPL = G::RPL, CPW = G::CPW;
+  double *pan = sw + G::PAN, *sbinv = sw + G::BINV, *Y = sw + G::YS;
+  int *spiv = si, *srsel = si + NP, *sbad = si + NP + 4;
+  const int warp = tid >> 5, lane = tid & 31, g = lane >> 2, q = lane & 3;
+  const int swg = ((g >> 1) & 1) << 2, swl = ((lane >> 1) & 1) << 2;
+  const int nt0 = warp * CPW;                                        // first tile column of this warp
+  double *ytile = Y + g * PLD + ((2 * q) ^ swg);                     // tile (mt, nt): ytile[8 mt PLD + 8 nt]
+  double c[NTL][CPW][2];
+#pragma unroll
+  for (int mt = 0; mt < NTL; mt++)
+#pragma unroll
+    for (int u = 0; u < CPW; u++) {
+      const int row = g + 8 * mt, col = 8 * (nt0 + u) + 2 * q;
+      c[mt][u][0] = (row < N && col < N) ? Eg[row + col * N] : 0.0;
+      c[mt][u][1] = (row < N && col + 1 < N) ? Eg[row + (col + 1) * N] : 0.0;
+      if (row < N) *reinterpret_cast<double2 *>(ytile + 8 * mt * PLD + 8 * (nt0 + u)) = make_double2(c[mt][u][0], c[mt][u][1]);
+    }
+  for (int e = tid; e < 16 * (2 * NTL - NB); e += 32 * NWARP) sbinv[16 * NB + e] = 0.0;
+  if (tid == 0) *sbad = 0;
+  bool act[RPL];
+#pragma unroll
+  for (int s = 0; s < RPL; s++) act[s] = lane + 32 * s < N;
+#pragma unroll 1
+  for (int kb = 0; kb < NB; kb++) {
+    const int ntp = kb >> 1, h = kb & 1, c0 = 4 * kb;
+    __syncthreads();                              // mirror current (tiles + the previous step's patch)
+    if (warp == 0) {
+      double a[RPL][4];
+#pragma unroll
+      for (int s = 0; s < RPL; s++) {
+        const int row = lane + 32 * s;
+        if (row < N) {
+          const double *yp = Y + row * PLD + (c0 ^ swl);
+          const double2 lo = *reinterpret_cast<const double2 *>(yp), hi = *reinterpret_cast<const double2 *>(yp + 2);
+          a[s][0] = lo.x; a[s][1] = lo.y; a[s][2] = hi.x; a[s][3] = hi.y;
+        } else {
+          a[s][0] = a[s][1] = a[s][2] = a[s][3] = 0.0;
+        }
+      }
+      int rsel[4];
+      double lb10 = 0.0, lb20 = 0.0, lb21 = 0.0, lb30 = 0.0, lb31 = 0.0, lb32 = 0.0;
+#pragma unroll
+      for (int ss = 0; ss < 4; ss++) {
+        unsigned best = 0u;
+#pragma unroll
+        for (int s = 0; s < RPL; s++) {
+          const unsigned hi32 = (unsigned)__double2hiint(a[s][ss]) & 0x7fffffffu;
+          const unsigned key = (hi32 & ~0x7Fu) | (unsigned)(127 - (lane + 32 * s));
+          if (act[s] && key > best) best = key;
+        }
+        const unsigned mx = __reduce_max_sync(0xffffffffu, best);
+        const int r = 127 - (int)(mx & 0x7Fu);
+        const int rl = r & 31, rs = r >> 5;
+        rsel[ss] = r;
+        double pr[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          double v = a[0][j];
+#pragma unroll
+          for (int s = 1; s < RPL; s++) if (rs == s) v = a[s][j];
+          pr[j] = __shfl_sync(0xffffffffu, v, rl);
+        }
+        if ((mx == 0u || pr[ss] == 0.0) && lane == 0) *sbad = 1;
+        const double pinv = rcp_pivot(pr[ss]);
+        if (ss == 1) lb10 = pr[0];
+        if (ss == 2) { lb20 = pr[0]; lb21 = pr[1]; }
+        if (ss == 3) { lb30 = pr[0]; lb31 = pr[1]; lb32 = pr[2]; }
+#pragma unroll
+        for (int s = 0; s < RPL; s++) {
+          const double m = a[s][ss] * pinv;
+          a[s][ss] = m;
+#pragma unroll
+          for (int j = ss + 1; j < 4; j++) a[s][j] = fma(-m, pr[j], a[s][j]);
+          if ((lane + 32 * s) == r) act[s] = false;
+        }
+      }
+#pragma unroll
+      for (int s = 0; s < RPL; s++) {
+        const double w3 = -a[s][3];
+        const double w2 = -fma(w3, lb32, a[s][2]);
+        const double w1 = -fma(w3, lb31, fma(w2, lb21, a[s][1]));
+        const double w0 = -fma(w3, lb30, fma(w2, lb20, fma(w1, lb10, a[s][0])));
+        const int row = lane + 32 * s;
+        if (row < NP) { pan[row] = w0; pan[WLD + row] = w1; pan[2 * WLD + row] = w2; pan[3 * WLD + row] = w3; }
+      }
+      if (lane < 4) {
+        const int r = lane == 0 ? rsel[0] : lane == 1 ? rsel[1] : lane == 2 ? rsel[2] : rsel[3];
+        spiv[c0 + lane] = r; srsel[lane] = r;
+      }
+      __syncwarp();
+      if (lane < 16) {
+        const int sr = lane >> 2, sc = lane & 3;
+        const int r = sr == 0 ? rsel[0] : sr == 1 ? rsel[1] : sr == 2 ? rsel[2] : rsel[3];
+        sbinv[16 * kb + lane] = Y[r * PLD + ((c0 + sc) ^ (((r >> 1) & 1) << 2))];   // B(sr, sc), raw
+        pan[sc * WLD + r] = 0.0;                                                     // W = 0 for the pivot rows
+      }
+    }
+    __syncthreads();
+    // rank-4 update of this warp's tile columns
+    const int rq = srsel[q];
+    const double *yq = Y + rq * PLD + (g ^ (((rq >> 1) & 1) << 2));
+    double bf[CPW];
+#pragma unroll
+    for (int u = 0; u < CPW; u++) {
+      bf[u] = yq[8 * (nt0 + u)];
+      if (nt0 + u == ntp && (g >> 2) == h) bf[u] = (g & 3) == q ? 1.0 : 0.0;       // panel columns of the pivot rows: I_4
+    }
+#pragma unroll
+    for (int u = 0; u < CPW; u++)
+      if (nt0 + u == ntp && (q >> 1) == h) {
+#pragma unroll
+        for (int mt = 0; mt < NTL; mt++) { c[mt][u][0] = 0.0; c[mt][u][1] = 0.0; }
+      }
+#pragma unroll
+    for (int mt = 0; mt < NTL; mt++) {
+      const double af = pan[q * WLD + g + 8 * mt];
+#pragma unroll
+      for (int u = 0; u < CPW; u++) dmma_884(c[mt][u][0], c[mt][u][1], af, bf[u]);
+    }
+    __syncwarp();     // every lane has read its B rows before this warp overwrites its mirror columns
+#pragma unroll
+    for (int mt = 0; mt < NTL; mt++)
+#pragma unroll
+      for (int u = 0; u < CPW; u++)
+        if (g + 8 * mt < N && 8 * (nt0 + u) + 2 * q < N)
+          *reinterpret_cast<double2 *>(ytile + 8 * mt * PLD + 8 * (nt0 + u)) = make_double2(c[mt][u][0], c[mt][u][1]);
+    if (ntp >= nt0 && ntp < nt0 + CPW) {          // the owner of the panel's tile column (warp-uniform)
+      __syncwarp();
+      if (lane < 16) {
+        const int sr = lane >> 2, sc = lane & 3;
+        const int r = srsel[sr];
+        Y[r * PLD + ((c0 + sc) ^ (((r >> 1) & 1) << 2))] = (sr == sc) ? 1.0 : 0.0;
+      }
+      __syncwarp();
+#pragma unroll
+      for (int u = 0; u < CPW; u++)
+        if (nt0 + u == ntp && (q >> 1) == h) {
+#pragma unroll
+          for (int mt = 0; mt < NTL; mt++)
+            if (g + 8 * mt < N) {
+              const double2 v = *reinterpret_cast<const double2 *>(ytile + 8 * mt * PLD + 8 * ntp);
+              c[mt][u][0] = v.x; c[mt][u][1] = v.y;
+            }
+        }
+    }
+  }
+  __syncthreads();
+  // B_kb^{-1} for all block steps, one thread per 4 x 4 block: Gauss-Jordan in the pivoting's row order
+  if (tid < NB) {
+    double bm[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+      for (int j2 = 0; j2 < 4; j2++) bm[i][j2] = sbinv[16 * tid + 4 * i + j2];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const double pinv = rcp_pivot(bm[k][k]);
+#pragma unroll
+      for (int j2 = 0; j2 < 4; j2++) bm[k][j2] = (j2 == k) ? pinv : bm[k][j2] * pinv;
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        if (i == k) continue;
+        const double m = bm[i][k];
+#pragma unroll
+        for (int j2 = 0; j2 < 4; j2++) bm[i][j2] = (j2 == k) ? -m * pinv : fma(-m, bm[k][j2], bm[i][j2]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+      for (int j2 = 0; j2 < 4; j2++) sbinv[16 * tid + 4 * i + j2] = bm[i][j2];
+  }
+  __syncthreads();
+  // X rows = blockdiag(B_kb^{-1}) (mirror rows in pivot order); row tiles over the warps
+  for (int mt = warp; mt < NTL; mt += NWARP) {
+    double x[NTL][2];
+#pragma unroll
+    for (int nt = 0; nt < NTL; nt++) x[nt][0] = x[nt][1] = 0.0;
+#pragma unroll
+    for (int j2 = 0; j2 < 2; j2++) {
+      if (2 * mt + j2 < NB) {
+        const double av = ((g >> 2) == j2) ? sbinv[16 * (2 * mt + j2) + 4 * (g & 3) + q] : 0.0;
+        const int rr = spiv[8 * mt + 4 * j2 + q];
+        const double *yr = Y + rr * PLD + (g ^ (((rr >> 1) & 1) << 2));
+#pragma unroll
+        for (int nt = 0; nt < NTL; nt++) dmma_884(x[nt][0], x[nt][1], av, yr[8 * nt]);
+      }
+    }
+    const int row = g + 8 * mt;
+    if (row < N) {
+#pragma unroll
+      for (int nt = 0; nt < NTL; nt++) {
+        const int col = 8 * nt + 2 * q;
+        if (col < N) Xg[row + spiv[col] * N] = x[nt][0];
+        if (col + 1 < N) Xg[row + spiv[col + 1] * N] = x[nt][1];
+      }
+    }
+  }
+  return *sbad == 0;
+}
+
 } // namespace garb200

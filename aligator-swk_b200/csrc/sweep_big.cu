@@ -53,6 +53,20 @@ __global__ void __launch_bounds__(32 * NWARP, 3) einv_cta_dmma_kernel(const DevP
   if (!ok && threadIdx.x == 0) atomicOr(reinterpret_cast<int *>(p.flags) + b, GARB200_FLAG_LU_SINGULAR);
 }
 
+// The same with the tiles in registers (gj_inverse_cta_regs): half the shared-memory traffic per matrix.
+template <int N, int NWARP>
+__global__ void __launch_bounds__(32 * NWARP, 3) einv_cta_regs_kernel(const DevParams p) {
+  using G = GjCtaRegs<N, NWARP>;
+  extern __shared__ __align__(16) double sm[];
+  int *si = reinterpret_cast<int *>(sm + G::SMEM);
+  const long long w = blockIdx.x;
+  const int b = (int)(w / p.T), t = (int)(w % p.T);
+  const double *Eg = p.knots + ((size_t)b * (p.T + 1) + phys_t(p, t)) * p.KL.stride + p.KL.E;
+  double *Xg = p.einv + ((size_t)b * p.T + phys_t(p, t)) * (size_t)(N * N);
+  const bool ok = gj_inverse_cta_regs<N, NWARP>(threadIdx.x, Eg, Xg, sm, si);
+  if (!ok && threadIdx.x == 0) atomicOr(reinterpret_cast<int *>(p.flags) + b, GARB200_FLAG_LU_SINGULAR);
+}
+
 // ---- record offsets (identical to garb200_make_knot_layout / garb200_make_gain_layout) ---------
 template <int NX, int NU> struct BigPlan {
   static constexpr int n = NX, m = NU, s = NU, na = NX + 1;
@@ -539,6 +553,15 @@ static int launch_big_t(const DevParams &p, cudaStream_t st) {
   const bool lu_prepass = p.tune.einv_mode == 2;
   if (EX) {
     // explicit dynamics: no E^{-1}, no pre-pass
+  } else if (total > 0 && p.tune.einv_mode != 2 && p.tune.einv_mode != 4) {   // default: tiles in registers, mirror in shared memory
+    // (einv_mode 4: the matrix-in-shared-memory version below, 14.9 vs 11.1 ms on c5; 2: LU in shared memory; 10 warps
+    //  per matrix measured slower: 57.7 vs 54.8 ms backward)
+    constexpr int EW = 5;
+    constexpr size_t esm = (size_t)GjCtaRegs<NX, EW>::SMEM * sizeof(double) + (size_t)GjCtaRegs<NX, EW>::SINTS * sizeof(int);
+    if (cudaFuncSetAttribute(einv_cta_regs_kernel<NX, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)esm) != cudaSuccess) return -2;
+    einv_cta_regs_kernel<NX, EW><<<(unsigned)total, 32 * EW, esm, st>>>(p);
+    if (cudaGetLastError() != cudaSuccess) return -2;
+    launched++;
   } else if (total > 0 && !lu_prepass) {
     constexpr int EW = 5;
     constexpr size_t esm = (size_t)GjCta<NX>::SMEM * sizeof(double) + (size_t)GjCta<NX>::SINTS * sizeof(int);
