@@ -89,8 +89,7 @@ __device__ __forceinline__ void mma_gemm(int warp, int lane, FA a, FB b, FC cin,
           if (jc + 1 < N) store(ic, jc + 1, acc[r][u][1]);
         }
       }
-    return;
-  }
+  } else {
   double acc[NSLOT][2];
   int ia[NSLOT], jb[NSLOT];
 #pragma unroll
@@ -129,6 +128,7 @@ __device__ __forceinline__ void mma_gemm(int warp, int lane, FA a, FB b, FC cin,
         if (jc + 1 < N) store(ic, jc + 1, acc[u][1]);
       }
     }
+  }
   }
 }
 
