@@ -220,3 +220,52 @@ def test_dense_solver_restatement(oracle, dims):
         if nth == 0:
             xs, us, vs, lb = dense_solve(oracle, pp, mu, b)
             assert relerr(d["xs"], xs) < 1e-9 and relerr(d["us"], us) < 1e-9
+
+
+@pytest.mark.parametrize("dims", [(5, 2, 1, 1, 7, 12, 4, 3, 2), (7, 3, 0, 0, 9, 12, 4, 0, 0), (6, 2, 2, 0, 5, 8, 5, 4, 1)],
+                         ids=lambda d: "nx%d_nu%d_nc%d_nth%d_T%d_into_%d_%d_%d_%d" % d)
+def test_padding_embedding_is_exact(oracle, dims):
+    """The embedding csrc/pad.cu uses for shapes without an instantiated sweep, checked on the CPU
+    independently of any kernel: pad a problem with E' = [E 0; 0 -I], Q' = [Q 0; 0 I], R' = [R 0; 0 I], empty
+    constraint rows, zero theta columns, G0' = [G0 0; 0 I]; the oracle's solution of the padded problem restricted
+    to the original rows IS the oracle's solution of the original problem (to round-off), the padded parts are 0."""
+    nx, nu, nc, nth, T, NX, NU, NC, NTH = dims
+    mu = 1e-8
+    pp = generate_problems(1, T, nx, nu, nc, nth, seed=17)
+    L, LP = pp.layout, KnotLayout(NX, NU, NC, NTH)
+    knots = np.zeros((1, T + 1, LP.stride))
+    for t in range(T + 1):
+        m, c = int(pp.nu_t[t]), int(pp.nc_t[t])
+        M, Cc = (NU, NC) if t < T else (0, 0)
+        f = L.unpack(pp.knots[0, t], m, c)
+        g = {k: np.zeros(s) for k, s in LP.shapes(M, Cc).items()}
+        for k, a in f.items():
+            g[k][:a.shape[0], :a.shape[1]] = a
+        for i in range(nx, NX):
+            g["Q"][i, i] = 1.0
+            g["E"][i, i] = -1.0
+        for i in range(m, M):
+            g["R"][i, i] = 1.0
+        LP.pack(knots[0, t], g, M, Cc)
+    c0 = pp.nc0
+    C0 = c0 + NX - nx
+    G0 = np.zeros((C0, NX)); G0[:c0, :nx] = pp.G0[0].reshape(nx, c0).T
+    G0[c0:, nx:] = np.eye(NX - nx)
+    g0 = np.concatenate([pp.g0[0], np.zeros(NX - nx)])
+    nu_t = np.array([NU] * T + [0], np.int32); nc_t = np.array([NC] * T + [0], np.int32)
+    padded = type(pp)(LP, T, C0, nu_t, nc_t, knots, np.ascontiguousarray(G0.T).reshape(1, -1), g0.reshape(1, -1))
+    theta = np.random.default_rng(2).standard_normal(nth) if nth else None
+    thp = None if NTH == 0 else np.concatenate([theta if theta is not None else np.zeros(0), np.zeros(NTH - nth)])
+    a = oracle.prox_solve(pp, mu, mu, theta=theta)
+    b = oracle.prox_solve(padded, mu, mu, theta=thp)
+    xs, us, vs = b["xs"], b["us"], b["vs"]
+    assert relerr(xs[:, :nx], a["xs"]) < 1e-11 and np.abs(xs[:, nx:]).max(initial=0.0) < 1e-12
+    if nu:
+        assert relerr(us[:, :nu], a["us"]) < 1e-11
+    assert np.abs(us[:, nu:]).max(initial=0.0) < 1e-12
+    if nc:
+        assert relerr(vs[:, :nc], a["vs"]) < 1e-10
+    lb = b["lbdas"]
+    assert relerr(lb[:c0], a["lbdas"][:c0]) < 1e-10
+    assert relerr(lb[C0:].reshape(T, NX)[:, :nx], a["lbdas"][c0:].reshape(T, nx)) < 1e-10
+    assert np.abs(lb[C0:].reshape(T, NX)[:, nx:]).max(initial=0.0) < 1e-12
