@@ -226,7 +226,7 @@ def test_dense_solver_restatement(oracle, dims):
                          ids=lambda d: "nx%d_nu%d_nc%d_nth%d_T%d_into_%d_%d_%d_%d" % d)
 def test_padding_embedding_is_exact(oracle, dims):
     """The embedding csrc/pad.cu uses for shapes without an instantiated sweep, checked on the CPU
-    independently of any kernel: pad a problem with E' = [E 0; 0 -I], Q' = [Q 0; 0 I], R' = [R 0; 0 I], empty
+    independently of any kernel: pad a problem with E' = [E 0; 0 -I], no cost on the padded states, R' = [R 0; 0 I], empty
     constraint rows, zero theta columns, G0' = [G0 0; 0 I]; the oracle's solution of the padded problem restricted
     to the original rows IS the oracle's solution of the original problem (to round-off), the padded parts are 0."""
     nx, nu, nc, nth, T, NX, NU, NC, NTH = dims
@@ -242,7 +242,6 @@ def test_padding_embedding_is_exact(oracle, dims):
         for k, a in f.items():
             g[k][:a.shape[0], :a.shape[1]] = a
         for i in range(nx, NX):
-            g["Q"][i, i] = 1.0
             g["E"][i, i] = -1.0
         for i in range(m, M):
             g["R"][i, i] = 1.0
