@@ -74,3 +74,22 @@ def test_product_sources_never_touch_the_oracle():
                 if re.search(r"pyoracle|libgar_oracle|oracle/", txt):
                     bad.append(os.path.join(dp, f))
     assert not bad, bad
+
+
+def test_headers_are_plain_c(tmp_path):
+    """The drop-in boundary is a C ABI: include/garb200.h and garb200_layout.h must compile as C99 (no C++ types,
+    no default arguments, no references) with every warning on."""
+    import shutil
+    import subprocess
+    gcc = shutil.which("gcc")
+    if gcc is None:
+        pytest.skip("no gcc")
+    src = tmp_path / "hdr.c"
+    src.write_text('#include "garb200.h"\n#include "garb200_layout.h"\n'
+                   "int use(void) {\n  garb200_config cfg; garb200_solver *s = 0; garb200_multi *m = 0;\n"
+                   "  cfg.nx = 2; (void)m;\n"
+                   "  return garb200_create(&cfg, &s) + (int)sizeof(garb200_knot_view) + (int)sizeof(garb200_device_problem_view);\n}\n")
+    inc = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include")
+    r = subprocess.run([gcc, "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-I", inc, "-c", str(src), "-o", str(tmp_path / "hdr.o")],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
